@@ -1,0 +1,74 @@
+// K-CODEC: the GPU-plane meaning of the reference's "-c Y" switch.
+//
+// The reference gzips base64 text, which only undoes base64's own inflation.  On the
+// NVLink plane the lossless mode is therefore "send the fp32 words as they are" and needs no
+// kernel.  The opt-in lossy mode below ships a block-scaled fp8 (e4m3) DELTA against the last
+// global model with error feedback: what quantisation drops this round is added back next round,
+// so the bias does not accumulate.  32-element blocks, one fp32 scale each: 9 bits per weight.
+// The decoder is fused into K-AGG (fedavg.cu); fedb_codec_decode exists for tests and re-admission.
+#include "common.cuh"
+#include "../include/fedb200.h"
+#include <cuda_fp8.h>
+
+namespace {
+
+constexpr float kE4M3Max = 448.f;
+
+// one warp per 32-element block: lane i owns element i
+__global__ void __launch_bounds__(256) codec_encode_kernel(const float* __restrict__ cur,
+                                                          const float* __restrict__ base,
+                                                          float* __restrict__ residual, uint8_t* __restrict__ q,
+                                                          float* __restrict__ scale, long long n) {
+  const int lane = threadIdx.x & 31;
+  const long long warp = ((long long)blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  const long long nwarps = ((long long)gridDim.x * blockDim.x) >> 5;
+  const long long nblocks = (n + 31) >> 5;
+  for (long long b = warp; b < nblocks; b += nwarps) {
+    const long long i = b * 32 + lane;
+    float d = 0.f;
+    if (i < n) d = (cur[i] - base[i]) + residual[i];
+    const float amax = warp_max(fabsf(d));
+    const float s = amax > 0.f ? amax / kE4M3Max : 1.f;
+    const __nv_fp8_e4m3 f8(d / s);
+    const float back = static_cast<float>(f8) * s;
+    if (i < n) {
+      q[i] = f8.__x;
+      residual[i] = d - back;
+    }
+    if (lane == 0) scale[b] = s;
+  }
+}
+
+__global__ void __launch_bounds__(256) codec_decode_kernel(float* __restrict__ out, const float* __restrict__ base,
+                                                          const uint8_t* __restrict__ q,
+                                                          const float* __restrict__ scale, long long n) {
+  const long long stride = (long long)gridDim.x * blockDim.x;
+  for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
+    __nv_fp8_e4m3 f8;
+    f8.__x = q[i];
+    out[i] = base[i] + static_cast<float>(f8) * scale[i >> 5];
+  }
+}
+
+}  // namespace
+
+extern "C" int fedb_codec_encode(const float* cur, const float* base, float* residual, uint8_t* q, float* scale,
+                                 int64_t n, void* stream) {
+  FEDB_REQUIRE(n >= 0, "fedb_codec_encode: negative size");
+  if (n == 0) return 0;
+  int blocks = fedb_ceil_div((n + 31) / 32, 8);
+  if (blocks > fedb_num_sms() * 8) blocks = fedb_num_sms() * 8;
+  codec_encode_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(cur, base, residual, q, scale, n);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+
+extern "C" int fedb_codec_decode(float* out, const float* base, const uint8_t* q, const float* scale, int64_t n,
+                                 void* stream) {
+  if (n == 0) return 0;
+  int blocks = fedb_ceil_div(n, 256);
+  if (blocks > fedb_num_sms() * 8) blocks = fedb_num_sms() * 8;
+  codec_decode_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(out, base, q, scale, n);
+  FEDB_LAUNCH_OK();
+  return 0;
+}

@@ -1,0 +1,94 @@
+// K9 + K13: softmax cross-entropy forward+backward with device-side accuracy bookkeeping.
+// The reference does loss.item() and .sum().item() every step - two host syncs per step
+// (src/main.py:153-156); here the counters stay on the device and are read once per pass.
+#include "common.cuh"
+#include "../include/fedb200.h"
+
+namespace {
+
+// one warp per sample; C <= 1024
+__global__ void __launch_bounds__(128) ce_kernel(const float* __restrict__ logits, const int64_t* __restrict__ target,
+                                                float* __restrict__ dlogits, float* __restrict__ loss_rows,
+                                                float* __restrict__ correct_rows, int B, int C) {
+  const int lane = threadIdx.x & 31;
+  const int row = (blockIdx.x * blockDim.x + threadIdx.x) >> 5;
+  if (row >= B) return;
+  const float* z = logits + (long long)row * C;
+  float mx = -INFINITY;
+  int arg = 0;
+  for (int c = lane; c < C; c += 32) {
+    float v = z[c];
+    if (v > mx) { mx = v; arg = c; }
+  }
+  // argmax with first-index tie break, like torch.max(1)
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) {
+    float om = __shfl_xor_sync(0xffffffffu, mx, o);
+    int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+    if (om > mx || (om == mx && oa < arg)) { mx = om; arg = oa; }
+  }
+  float se = 0.f;
+  for (int c = lane; c < C; c += 32) se += expf(z[c] - mx);
+  se = warp_sum(se);
+  const float lse = logf(se) + mx;
+  const int t = (int)target[row];
+  if (dlogits != nullptr) {
+    const float invB = 1.f / (float)B;
+    for (int c = lane; c < C; c += 32) {
+      float sm = expf(z[c] - lse);
+      dlogits[(long long)row * C + c] = (sm - (c == t ? 1.f : 0.f)) * invB;
+    }
+  }
+  if (lane == 0) {
+    loss_rows[row] = lse - z[t];
+    correct_rows[row] = (arg == t) ? 1.f : 0.f;
+  }
+}
+
+// deterministic finish: one block sums the rows in a fixed tree
+__global__ void __launch_bounds__(256) ce_finish_kernel(const float* __restrict__ loss_rows,
+                                                       const float* __restrict__ correct_rows,
+                                                       float* __restrict__ loss_out, float* __restrict__ stats, int B) {
+  __shared__ float sl[256], sc[256];
+  float l = 0.f, c = 0.f;
+  for (int i = threadIdx.x; i < B; i += 256) { l += loss_rows[i]; c += correct_rows[i]; }
+  sl[threadIdx.x] = l;
+  sc[threadIdx.x] = c;
+  __syncthreads();
+  for (int s = 128; s > 0; s >>= 1) {
+    if (threadIdx.x < s) { sl[threadIdx.x] += sl[threadIdx.x + s]; sc[threadIdx.x] += sc[threadIdx.x + s]; }
+    __syncthreads();
+  }
+  if (threadIdx.x == 0) {
+    if (loss_out) *loss_out = sl[0] / (float)B;
+    if (stats) { stats[0] += sl[0] / (float)B; stats[1] += sc[0]; stats[2] += (float)B; stats[3] += 1.f; }
+  }
+}
+
+}  // namespace
+
+// scratch: two float rows of B, kept per device and grown on demand (never inside a capture the
+// first time: callers warm up once before capturing).
+static float* g_ce_rows[16] = {nullptr};
+static int g_ce_cap[16] = {0};
+
+extern "C" int fedb_cross_entropy(const float* logits, const int64_t* target, float* dlogits, float* loss_out,
+                                  float* stats, int B, int C, void* stream) {
+  FEDB_REQUIRE(B > 0 && C > 0 && C <= 4096, "fedb_cross_entropy: bad shape");
+  int dev = 0;
+  FEDB_CHECK(cudaGetDevice(&dev));
+  FEDB_REQUIRE(dev < 16, "fedb_cross_entropy: device index too large");
+  if (g_ce_cap[dev] < B) {
+    if (g_ce_rows[dev]) FEDB_CHECK(cudaFree(g_ce_rows[dev]));
+    int cap = B < 4096 ? 4096 : B;
+    FEDB_CHECK(cudaMalloc(&g_ce_rows[dev], sizeof(float) * 2 * cap));
+    g_ce_cap[dev] = cap;
+  }
+  float* rows = g_ce_rows[dev];
+  cudaStream_t s = (cudaStream_t)stream;
+  ce_kernel<<<fedb_ceil_div(B, 4), 128, 0, s>>>(logits, target, dlogits, rows, rows + g_ce_cap[dev], B, C);
+  FEDB_LAUNCH_OK();
+  ce_finish_kernel<<<1, 256, 0, s>>>(rows, rows + g_ce_cap[dev], loss_out, stats, B);
+  FEDB_LAUNCH_OK();
+  return 0;
+}

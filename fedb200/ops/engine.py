@@ -1,0 +1,210 @@
+"""GPU step engine behind ``LocalTrainer`` (SURVEY C12 on the device).
+
+Two paths, both hand-written kernels end to end:
+* LeNet - the fused four-kernel step of csrc/lenet.cu.  A whole local pass (every step of the
+  shard) is captured ONCE into a CUDA graph per (shard shape) and replayed each round: one graph
+  launch per round, no host syncs inside (K13), uint8 images normalised on the fly (K14).
+* any other zoo model - the model's own ``forward`` (which dispatches every op to
+  ``fedb200.ops.cuda_nn``) under autograd, CE + fused SGD kernels, the step captured in a CUDA
+  graph as well.
+
+Per pass the shard's images/labels are copied host->device from pinned memory on a side stream
+(overlapped with the previous work where possible); loss / accuracy counters are read back once.
+"""
+from __future__ import annotations
+
+from typing import Dict, List, Optional, Tuple
+
+import torch
+
+from ..utils import data as D
+from . import _lib
+from . import cuda as K
+
+
+class CudaEngine:
+    def __init__(self, trainer):
+        from ..control.trainer import TrainStats
+        self.TrainStats = TrainStats
+        self.t = trainer
+        self.dev = trainer.device
+        self.cfg = trainer.cfg
+        self.arena = trainer.arena
+        self.is_lenet = trainer.cfg.model == "LeNet"
+        self.copy_stream = torch.cuda.Stream(device=self.dev)
+        self._shards: Dict[Tuple[int, ...], dict] = {}
+        self._test_dev = None
+        self._eval_graph = None
+        self.h2d_bytes_last = 0
+        self.d2h_bytes_last = 0
+        self.seed_dev = torch.zeros(1, dtype=torch.int64, device=self.dev)
+        self.eval_stats = torch.zeros(4, dtype=torch.float32, device=self.dev)
+        self._pinned_stats = torch.zeros(8, dtype=torch.float32).pin_memory()
+        self.rebind_arena(self.arena)
+
+    def rebind_arena(self, arena) -> None:
+        """(Re)attach to an arena - called again when the trainer's state moves into peer memory.
+        Captured graphs hold raw pointers, so they are dropped."""
+        self.arena = arena
+        for sh in self._shards.values():
+            sh["graph"] = None
+        self._eval_graph = None
+        with torch.cuda.device(self.dev):
+            if self.is_lenet:
+                self.plan = K.LeNetPlan(arena, self.cfg.lr, self.cfg.momentum, self.cfg.weight_decay,
+                                        augment=self.cfg.augment, max_batch=self.cfg.batch_size)
+                self.plan.desc.seed_dev = self.seed_dev.data_ptr()
+                self.stats = self.plan.stats
+            else:
+                self.stats = torch.zeros(4, dtype=torch.float32, device=self.dev)
+
+    # ------------------------------------------------------------------ data staging
+    def _shard(self, batches: List[int]) -> dict:
+        key = tuple(batches)
+        sh = self._shards.get(key)
+        if sh is None:
+            bs = self.cfg.batch_size
+            ds = self.t.dataset
+            idx = torch.cat([torch.arange(b * bs, min((b + 1) * bs, ds.train_x.shape[0])) for b in batches]) \
+                if batches else torch.zeros(0, dtype=torch.long)
+            hx = ds.train_x[idx].contiguous()
+            hy = ds.train_y[idx].contiguous()
+            if torch.cuda.is_available():
+                hx, hy = hx.pin_memory(), hy.pin_memory()
+            sizes = [min((b + 1) * bs, ds.train_x.shape[0]) - b * bs for b in batches]
+            sh = {"hx": hx, "hy": hy, "sizes": sizes,
+                  "dx": torch.empty_like(hx, device=self.dev), "dy": torch.empty_like(hy, device=self.dev),
+                  "graph": None}
+            if len(self._shards) > 8:
+                self._shards.clear()
+            self._shards[key] = sh
+        return sh
+
+    def _upload(self, sh: dict) -> None:
+        """H2D of this pass's inputs from pinned memory (counted by bench.py's e2e figure)."""
+        cur = torch.cuda.current_stream(self.dev)
+        self.copy_stream.wait_stream(cur)
+        with torch.cuda.stream(self.copy_stream):
+            sh["dx"].copy_(sh["hx"], non_blocking=True)
+            sh["dy"].copy_(sh["hy"], non_blocking=True)
+        cur.wait_stream(self.copy_stream)
+        self.h2d_bytes_last = sh["hx"].numel() + sh["hy"].numel() * 8
+
+    # ------------------------------------------------------------------ training pass
+    def _issue_steps(self, sh: dict) -> None:
+        off = 0
+        for i, n in enumerate(sh["sizes"]):
+            x, y = sh["dx"][off:off + n], sh["dy"][off:off + n]
+            if self.is_lenet:
+                self.plan.train_step(x, y, step_seed=i + 1)
+            else:
+                self._generic_step(x, y, i + 1)
+            off += n
+
+    def _generic_step(self, x_u8, y, seed):
+        a, cfg = self.arena, self.cfg
+        x = K.prepare_batch(x_u8, nhwc=True, augment=cfg.augment, seed=seed)
+        a.grad.zero_()
+        out = self.t.model(x)
+        dlogits = torch.empty_like(out)
+        K.cross_entropy_raw(out.detach().contiguous(), y, dlogits, None, self.stats)
+        out.backward(dlogits)
+        n = a.manifest.n_param
+        K.sgd_step(a.f32[:n], a.grad, a.momentum, cfg.lr, cfg.momentum, cfg.weight_decay)
+
+    def train_pass(self, batches: List[int], upload: bool = True, sync: bool = True):
+        with torch.cuda.device(self.dev):
+            self.t.model.train()
+            sh = self._shard(batches)
+            if not sh["sizes"]:
+                return self.TrainStats()
+            if upload:
+                self._upload(sh)
+            self.stats.zero_()
+            self.seed_dev += 1
+            if self.cfg.use_cuda_graph:
+                if sh["graph"] is None:
+                    self._issue_steps(sh)                      # warm-up (also sizes every workspace)
+                    torch.cuda.synchronize(self.dev)
+                    g = torch.cuda.CUDAGraph()
+                    # the warm-up already trained one pass; that is a real pass, so count it and
+                    # capture the graph for the following rounds
+                    with torch.cuda.graph(g, stream=torch.cuda.Stream(device=self.dev)):
+                        self._issue_steps(sh)
+                    sh["graph"] = g
+                else:
+                    sh["graph"].replay()
+                    _lib.count_launch(self._launches_per_pass(sh))
+            else:
+                self._issue_steps(sh)
+            self.arena.sgd_steps += len(sh["sizes"])
+            return self.read_stats() if sync else None
+
+    def _launches_per_pass(self, sh) -> int:
+        return (4 if self.is_lenet else 0) * len(sh["sizes"])
+
+    def read_stats(self, which: str = "train"):
+        """One D2H read per pass: loss, correct, samples, steps."""
+        s = (self.stats if which == "train" else self.eval_stats).cpu()
+        self.d2h_bytes_last = s.numel() * 4
+        return self._to_stats(s)
+
+    def _to_stats(self, s):
+        st = self.TrainStats()
+        st.loss_sum, st.correct, st.samples, st.steps = float(s[0]), int(s[1]), int(s[2]), int(s[3])
+        return st
+
+    def read_round_stats(self):
+        """Train + eval counters of a round in ONE pinned D2H copy (32 bytes) and one sync."""
+        self._pinned_stats[:4].copy_(self.stats, non_blocking=True)
+        self._pinned_stats[4:].copy_(self.eval_stats, non_blocking=True)
+        torch.cuda.current_stream(self.dev).synchronize()
+        self.d2h_bytes_last = 32
+        return self._to_stats(self._pinned_stats[:4]), self._to_stats(self._pinned_stats[4:])
+
+    # ------------------------------------------------------------------ evaluation pass
+    def eval_pass(self, upload: bool = True, sync: bool = True, chunk: int = 2000):
+        with torch.cuda.device(self.dev):
+            self.t.model.eval()
+            ds = self.t.dataset
+            if self._test_dev is None:
+                hx, hy = ds.test_x.contiguous(), ds.test_y.contiguous()
+                if torch.cuda.is_available():
+                    hx, hy = hx.pin_memory(), hy.pin_memory()
+                self._test_host = (hx, hy)
+                self._test_dev = (torch.empty_like(hx, device=self.dev), torch.empty_like(hy, device=self.dev))
+            if upload:
+                cur = torch.cuda.current_stream(self.dev)
+                self.copy_stream.wait_stream(cur)
+                with torch.cuda.stream(self.copy_stream):
+                    self._test_dev[0].copy_(self._test_host[0], non_blocking=True)
+                    self._test_dev[1].copy_(self._test_host[1], non_blocking=True)
+                cur.wait_stream(self.copy_stream)
+                self.h2d_bytes_last += self._test_host[0].numel() + self._test_host[1].numel() * 8
+            self.eval_stats.zero_()
+            n = ds.test_x.shape[0]
+            if self.is_lenet:
+                if self.cfg.use_cuda_graph and self._eval_graph is not None:
+                    self._eval_graph.replay()
+                    _lib.count_launch(3 * ((n + chunk - 1) // chunk))
+                else:
+                    def issue():
+                        for lo in range(0, n, chunk):
+                            self.plan.eval_batch(self._test_dev[0][lo:lo + chunk], self._test_dev[1][lo:lo + chunk],
+                                                 self.eval_stats)
+                    issue()
+                    if self.cfg.use_cuda_graph:
+                        torch.cuda.synchronize(self.dev)
+                        g = torch.cuda.CUDAGraph()
+                        with torch.cuda.graph(g, stream=torch.cuda.Stream(device=self.dev)):
+                            issue()
+                        self._eval_graph = g
+            else:
+                bs = self.cfg.test_batch_size
+                with torch.no_grad():
+                    for lo in range(0, n, bs):
+                        x = K.prepare_batch(self._test_dev[0][lo:lo + bs], nhwc=True)
+                        out = self.t.model(x)
+                        K.cross_entropy_raw(out.contiguous(), self._test_dev[1][lo:lo + bs], None, None,
+                                            self.eval_stats)
+            return self.read_stats("eval") if sync else None

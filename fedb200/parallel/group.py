@@ -1,0 +1,142 @@
+"""GPU data plane of a federation on one NVSwitch box: one process per GPU, every worker's arena
+peer-mapped, FedAvg + broadcast (+ replica) as ONE kernel launch per rank per round.
+
+What the reference does per round with 2N+1 RPCs carrying base64 checkpoints and a CPU mean over
+files (src/server.py:113-179) happens here as:
+
+    train pass (CUDA graph) -> K-AGG two-shot (csrc/fedavg.cu) -> [K-REPL on a side stream] -> eval pass
+
+* every rank owns the shard ``split_ranges(n_f32, live)[i]`` of the flat arena: it pulls that shard from
+  every live peer over NVLink, reduces it in the reference's order, and pushes the result into every
+  peer's arena, the primary's global model and (fused mode) the backup's replica;
+* the device-flag protocol inside the kernel replaces both thread-join barriers; spins are bounded and
+  surface as ``FedbError`` instead of a hang when a peer died;
+* with NVLS the push is one ``multimem.st`` and (opt-in, order not bit-reproducible) the pull is one
+  ``multimem.ld_reduce``;
+* ``codec="fp8"`` ships block-scaled e4m3 deltas with error feedback instead of fp32 words (K-CODEC).
+"""
+from __future__ import annotations
+
+from typing import List, Optional, Sequence
+
+import torch
+
+from ..ops import _lib
+from ..ops import cuda as K
+from .arena import Arena, split_ranges
+from .mem import PeerGroup, PeerLayout
+
+
+class FedGroup:
+    def __init__(self, trainer, rank: int, world: int, tag: str, *, use_multicast: bool = True,
+                 nvls_reduce: bool = False, codec: str = "none", primary_rank: int = 0,
+                 backup_rank: Optional[int] = None, repl_mode: str = "overlap", dist_barrier=None,
+                 timeout_ns: int = K.DEFAULT_TIMEOUT_NS):
+        assert trainer.device.type == "cuda"
+        self.trainer, self.rank, self.world = trainer, rank, world
+        self.device = trainer.device.index or 0
+        self.man = trainer.arena.manifest
+        self.codec, self.nvls_reduce, self.repl_mode = codec, nvls_reduce, repl_mode
+        self.primary_rank = primary_rank
+        self.backup_rank = (primary_rank + 1) % world if backup_rank is None else backup_rank
+        self.timeout_ns = timeout_ns
+        self.layout = PeerLayout.for_manifest(self.man, with_codec=True)
+        torch.cuda.set_device(self.device)
+        self.peers = PeerGroup(rank, world, self.device, self.layout, tag, use_multicast=use_multicast,
+                               barrier=dist_barrier)
+        # move the trainer's live state into the peer-visible allocation
+        old = trainer.arena
+        new = self.peers.me.client_arena(self.man)
+        new.copy_from(old)
+        new.grad, new.momentum, new.sgd_steps = old.grad, old.momentum, old.sgd_steps
+        new.bind(trainer.model)
+        trainer.arena = new
+        if trainer._engine is not None:
+            trainer._engine.rebind_arena(new)
+        self.live: List[int] = list(range(world))
+        self.round = 0
+        self.side_stream = torch.cuda.Stream(device=self.device, priority=0)
+        self._agg_done = torch.cuda.Event()
+        if codec == "fp8":
+            dev = trainer.device
+            self.residual = torch.zeros(self.man.n_f32, dtype=torch.float32, device=dev)
+            self.base = torch.zeros(self.man.n_f32, dtype=torch.float32, device=dev)   # last global model
+            self.base.copy_(new.f32[:self.man.n_f32])
+        torch.cuda.synchronize(self.device)
+
+    # ------------------------------------------------------------------ views
+    @property
+    def global_arena(self) -> Arena:
+        """The server's global model (lives on the primary's GPU, visible everywhere)."""
+        return self.peers.buffers[self.primary_rank].aux_arena(self.man)
+
+    @property
+    def replica_arena(self) -> Arena:
+        return self.peers.buffers[self.backup_rank].aux_arena(self.man)
+
+    def set_live(self, live: Sequence[int]) -> None:
+        """Membership change: only these ranks take part in (and are averaged by) the next rounds."""
+        self.live = sorted(live)
+
+    # ------------------------------------------------------------------ one aggregation
+    def aggregate(self, weights: Optional[Sequence[float]] = None) -> None:
+        """K-AGG launch of THIS rank (every live rank calls it once per round, any time after its own
+        training pass was enqueued)."""
+        if self.rank not in self.live:
+            return
+        bufs = self.peers.buffers
+        live = self.live
+        me = live.index(self.rank)
+        begin, end = split_ranges(self.man.n_f32, len(live))[me]
+        fused_repl = self.repl_mode == "fused" and self.backup_rank != self.primary_rank
+        dst = [bufs[self.primary_rank].aux_f32_ptr()]
+        dst_i64 = [bufs[self.primary_rank].aux_i64_ptr()]
+        if fused_repl:
+            dst.append(bufs[self.backup_rank].aux_f32_ptr())
+            dst_i64.append(bufs[self.backup_rank].aux_i64_ptr())
+        mc_dst = self.peers.mc_client_f32_ptr() if len(live) == self.world else 0
+        if not mc_dst:
+            dst += [bufs[r].client_f32_ptr() for r in live]
+        dst_i64 += [bufs[r].client_i64_ptr() for r in live]
+        kw = {}
+        if self.codec == "fp8":
+            n = self.man.n_f32
+            K.codec_encode(self.trainer.arena.f32[:n], self.base, self.residual, self.peers.me.q(),
+                           self.peers.me.scale())
+            kw = dict(src_q=[bufs[r].q_ptr() for r in live], src_scale=[bufs[r].scale_ptr() for r in live],
+                      base=self.base.data_ptr())
+        elif self.nvls_reduce and mc_dst:
+            kw = dict(mc_src=mc_dst)
+        K.fedavg_raw([bufs[r].client_f32_ptr() for r in live], dst, begin, end,
+                     ctrl_local=self.peers.me.ctrl_ptr,
+                     src_i64=[bufs[r].client_i64_ptr() for r in live], dst_i64=dst_i64,
+                     n_i64=self.man.n_i64 if me == 0 else 0, weights=weights, mc_dst=mc_dst,
+                     sync_mode=1, rank=me, world=len(live), ctrl_peer=[bufs[r].ctrl_ptr for r in live],
+                     timeout_ns=self.timeout_ns, **kw)
+        if self.codec == "fp8":
+            # the new global model is the base of the next round's deltas
+            self.base.copy_(self.trainer.arena.f32[:self.man.n_f32])
+        self.round += 1
+        if self.repl_mode == "overlap" and self.rank == self.primary_rank and self.backup_rank != self.primary_rank:
+            # K-REPL: primary -> backup peer copy on a side stream, overlapped with what follows
+            self._agg_done.record(torch.cuda.current_stream(self.device))
+            self.side_stream.wait_event(self._agg_done)
+            with torch.cuda.stream(self.side_stream):
+                K.replicate(self.replica_arena, self.global_arena,
+                            self.peers.buffers[self.backup_rank].ctrl(), self.round)
+
+    def check(self) -> None:
+        """Raises if a bounded spin gave up (peer died / never arrived).  Costs one 4-byte D2H read."""
+        st = K.ctrl_field(self.peers.me.ctrl(), "status")
+        if st:
+            raise _lib.FedbError(f"K-AGG flag wait failed on rank {self.rank}: status {st} "
+                                 "(1 = a peer never arrived, 2 = a peer never finished, 3 = aborted)")
+
+    def abort(self) -> None:
+        """Host-side abort: breaks every spin on this rank's control block."""
+        c = self.peers.me.ctrl()
+        c[_lib.CTRL_OFF["abort_flag"] // 4] = 1
+
+    def close(self):
+        torch.cuda.synchronize(self.device)
+        self.peers.close()

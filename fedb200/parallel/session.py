@@ -1,0 +1,77 @@
+"""``GpuFederation`` - the public, in-process API of the GPU data plane (what bench.py times).
+
+One instance per rank (process).  ``run_round()`` is a whole federated round of the reference
+(src/server.py:120-153 + src/client.py:16-31) for this rank:
+
+    H2D of the shard's uint8 images/labels (pinned) -> local pass over shard (rank, world) [N9] ->
+    K-AGG / K-BCAST (/K-REPL) -> evaluation of the new global model on the test set [N8] ->
+    one 32-byte D2H read of the loss/accuracy counters.
+
+The gRPC control plane (``fedb200.control``) drives exactly these calls from ``StartTrain`` /
+``SendModel`` when workers run with ``--plane peer``; here they are driven directly, rank-symmetric,
+which is also how a torchrun job uses the framework.
+"""
+from __future__ import annotations
+
+import os
+from typing import Optional
+
+import torch
+
+from ..control.trainer import LocalTrainer, TrainerConfig
+from ..utils import data as D
+from .group import FedGroup
+
+
+def dist_min_barrier():
+    """all-reduce(MIN) on a flag tensor through torch.distributed (the plumbing backend)."""
+    import torch.distributed as dist
+    if not (dist.is_available() and dist.is_initialized()):
+        return None
+
+    def fn(flag: torch.Tensor):
+        dist.all_reduce(flag, op=dist.ReduceOp.MIN)
+    return fn
+
+
+class GpuFederation:
+    def __init__(self, model: str = "LeNet", rank: int = 0, world: int = 1, device: Optional[int] = None,
+                 dataset: Optional[D.ImageDataset] = None, seed: Optional[int] = None, tag: Optional[str] = None,
+                 lr: float = 0.1, batch_size: int = 128, augment: bool = False, evaluate: bool = True,
+                 **group_kw):
+        device = rank if device is None else device
+        torch.cuda.set_device(device)
+        self.rank, self.world, self.evaluate = rank, world, evaluate
+        ds = dataset if dataset is not None else D.synthetic_cifar(seed=0)
+        cfg = TrainerConfig(model=model, lr=lr, batch_size=batch_size, device=f"cuda:{device}",
+                            seed=(rank if seed is None else seed), augment=augment)
+        self.trainer = LocalTrainer(cfg, ds.pin())
+        self.engine = self.trainer._engine
+        tag = tag or os.environ.get("MASTER_PORT", "solo") + f"-{os.getppid()}"
+        self.group = FedGroup(self.trainer, rank, world, tag, dist_barrier=dist_min_barrier(), **group_kw)
+        self.rounds = 0
+
+    def run_round(self, upload: bool = True, sync: bool = True):
+        """One federated round.  Returns (train_stats, eval_stats) when ``sync``; with ``sync=False``
+        everything is only enqueued (device-timed benchmarking)."""
+        live = self.group.live
+        batches = self.trainer.shard(live.index(self.rank), self.world) if self.rank in live else []
+        self.engine.train_pass(batches, upload=upload, sync=False)
+        self.group.aggregate()
+        if self.evaluate:
+            self.engine.eval_pass(upload=upload, sync=False)
+        self.rounds += 1
+        if not sync:
+            return None
+        out = self.engine.read_round_stats()
+        self.group.check()
+        return out
+
+    def h2d_bytes_per_round(self) -> int:
+        return self.engine.h2d_bytes_last
+
+    def d2h_bytes_per_round(self) -> int:
+        return 32 + 4
+
+    def close(self):
+        self.group.close()

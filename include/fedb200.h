@@ -1,0 +1,180 @@
+/* libfedb200 - C ABI of the fedb200 sm_100a kernels and the peer-memory manager.
+ *
+ * Conventions: every function returns 0 on success, a non-zero code otherwise, and leaves a
+ * human-readable message in fedb_last_error().  `stream` is a cudaStream_t passed as void*.
+ * All pointers are device pointers unless the name says host.  Nothing here allocates device
+ * memory except the fedb_mem_* family and fedb_scratch_*.
+ *
+ * "reference:" lines cite the file:line of amolahinge/739-839-federated-learning-using-grpc whose
+ * behaviour the entry point replaces.
+ */
+#ifndef FEDB200_H
+#define FEDB200_H
+#include <stdint.h>
+#include <stddef.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define FEDB_MAX_PEERS 16
+#define FEDB_MAX_DST 20
+
+const char* fedb_last_error(void);
+int fedb_version(void);
+
+/* ------------------------------------------------------------------ control block (device flags)
+ * One per peer-shared allocation.  arrive[j]/done[j] are written by rank j with st.release.sys and
+ * polled locally with ld.acquire.sys (bounded spin).  Replaces the thread joins of the reference
+ * round loop.  reference: src/server.py:132-135,150-153 */
+typedef struct {
+  uint32_t arrive[FEDB_MAX_PEERS];
+  uint32_t done[FEDB_MAX_PEERS];
+  uint32_t epoch;        /* rounds completed by this rank's K-AGG */
+  uint32_t status;       /* 0 ok | 1 timeout in arrive wait | 2 timeout in done wait | 3 aborted */
+  uint32_t blocks_done;  /* grid completion counter, self-resetting */
+  uint32_t abort_flag;   /* host writes 1 to break every spin */
+  uint32_t version;      /* model version held by the arena this block guards */
+  uint32_t reserved[27];
+} fedb_ctrl_t;
+
+/* ------------------------------------------------------------------ K-AGG / K-BCAST
+ * out[i] = mean_k src[k][i] over [begin, end) of the flat fp32 arena, in the reference's order
+ * ((s0+s1)+s2...)/N with the division last; int64 counters are summed in int64, true-divided in
+ * fp32 and truncated.  The result is stored to every dst[] (peer or local pointers; optional bf16
+ * shadow copies) - that fan-out IS the global-model broadcast.  With sync_mode=1 the kernel first
+ * tells every peer "my arena is final" and waits for theirs, and afterwards tells every peer "my
+ * shard is written" and waits for theirs, so one launch per rank is a complete
+ * reduce-scatter + all-gather over NVLink.
+ * reference: src/server.py:155-179 (allreduce), :144-153 (SendModel fan-out), :141-142 (backup) */
+typedef struct {
+  const float* src[FEDB_MAX_PEERS];       /* client fp32 arenas */
+  const int64_t* src_i64[FEDB_MAX_PEERS]; /* client int64 counter segments (may be NULL) */
+  float* dst[FEDB_MAX_DST];               /* destinations: clients, server global, backup replica */
+  int64_t* dst_i64[FEDB_MAX_DST];
+  uint16_t* dst_bf16[FEDB_MAX_DST];       /* optional bf16 shadow per destination (NULL = none) */
+  float weight[FEDB_MAX_PEERS];           /* sample counts as floats; ignored when uniform */
+  int32_t n_src, n_dst;
+  int32_t uniform;                        /* 1: plain mean (N1) */
+  int32_t do_i64;                         /* 1: this launch also reduces the int64 segment */
+  int64_t begin, end;                     /* fp32 element range, multiples of 4 */
+  int64_t n_i64;
+  /* compressed uploads (K-CODEC decode fused): src_q[k] fp8-e4m3 deltas, src_scale[k] one fp32
+   * scale per 32 elements, base = the model the deltas are relative to.  NULL src_q = raw fp32. */
+  const uint8_t* src_q[FEDB_MAX_PEERS];
+  const float* src_scale[FEDB_MAX_PEERS];
+  const float* base;
+  /* NVLS: when mc_src != NULL the sum comes from one multimem.ld_reduce on the multicast alias
+   * of the client arenas (in-switch reduction, order not defined); when mc_dst != NULL the result
+   * goes out with one multimem.st instead of n unicast stores (dst[] may still list extras). */
+  const float* mc_src;
+  float* mc_dst;
+  /* cross-rank synchronisation */
+  int32_t sync_mode;                      /* 0 none | 1 device flags */
+  int32_t rank, world;
+  fedb_ctrl_t* ctrl_local;
+  fedb_ctrl_t* ctrl_peer[FEDB_MAX_PEERS];
+  uint64_t timeout_ns;
+  uint32_t version;                       /* stamped into ctrl of every destination when nonzero */
+  fedb_ctrl_t* dst_ctrl[FEDB_MAX_DST];    /* optional: where to stamp the version */
+} fedb_agg_desc_t;
+
+int fedb_fedavg(const fedb_agg_desc_t* desc, int max_blocks, void* stream);
+
+/* K-REPL: versioned copy of a flat arena (fp32 + int64) into the backup's replica, meant for a
+ * low-priority side stream so it overlaps the next round.  reference: src/server.py:141-142,236-242 */
+int fedb_replicate(float* dst, const float* src, int64_t n_f32, int64_t* dst_i64, const int64_t* src_i64,
+                   int64_t n_i64, fedb_ctrl_t* dst_ctrl, uint32_t version, void* stream);
+
+/* Barrier on device flags only (bounded spin). */
+int fedb_flag_barrier(fedb_ctrl_t* local, fedb_ctrl_t* const* peers, int rank, int world,
+                      uint64_t timeout_ns, void* stream);
+
+/* ------------------------------------------------------------------ K-CODEC (the -c switch)
+ * Lossy opt-in mode: per 32-element block, delta = cur - base + residual; scale = amax/448;
+ * q = e4m3(delta/scale); residual = delta - q*scale (error feedback).  Lossless mode needs no
+ * kernel on the GPU plane (weights cross NVLink raw).  reference: src/server.py:103-107,
+ * src/client.py:39-43 */
+int fedb_codec_encode(const float* cur, const float* base, float* residual, uint8_t* q, float* scale,
+                      int64_t n, void* stream);
+int fedb_codec_decode(float* out, const float* base, const uint8_t* q, const float* scale, int64_t n,
+                      void* stream);
+
+/* ------------------------------------------------------------------ K10 fused SGD / Adam
+ * torch.optim.SGD semantics over the flat parameter range: g += wd*p; v = mu*v + g; p -= lr*v
+ * (v starts at zero, which makes the first step v = g exactly).  Optionally emits a bf16 shadow.
+ * reference: src/main.py:99-100,151 */
+int fedb_sgd_step(float* param, const float* grad, float* momentum, uint16_t* shadow_bf16, int64_t n,
+                  float lr, float mu, float weight_decay, void* stream);
+int fedb_adam_step(float* param, const float* grad, float* m, float* v, int64_t n, float lr, float beta1,
+                   float beta2, float eps, float weight_decay, const int32_t* step_dev, void* stream);
+
+/* ------------------------------------------------------------------ K9/K13 loss + counters
+ * logits [B, C] -> mean CE loss; dlogits = (softmax - onehot)/B; stats[0] += loss_sum (fp32),
+ * stats[1] += correct (as float), stats[2] += B.  reference: src/main.py:98,149,153-156 */
+int fedb_cross_entropy(const float* logits, const int64_t* target, float* dlogits, float* loss_out,
+                       float* stats, int B, int C, void* stream);
+
+/* ------------------------------------------------------------------ K14 input pipeline
+ * uint8 NHWC [B,32,32,3] -> fp32 NCHW (nhwc_out=0) or NHWC (1), ToTensor+Normalize, optional
+ * RandomCrop(32,4)+flip drawn from (seed, sample index).  reference: src/main.py:36-46 */
+int fedb_prepare_batch(const uint8_t* src_u8, float* dst, int B, int nhwc_out, int augment,
+                       uint64_t seed, void* stream);
+
+/* ------------------------------------------------------------------ LeNet fused training step
+ * Whole step in 4 kernels: features fwd, classifier fwd+loss+bwd, features bwd, reduce+SGD.
+ * `p` points at the flat fp32 arena; off[] are the element offsets of conv1.w, conv1.b, conv2.w,
+ * conv2.b, fc1.w, fc1.b, fc2.w, fc2.b, fc3.w, fc3.b.  Workspace sizes come from
+ * fedb_lenet_workspace_bytes(B).  reference: src/models/lenet.py:5-23, src/main.py:142-151 */
+typedef struct {
+  float* param;            /* arena base */
+  float* momentum;         /* same layout as param */
+  int64_t off[10];
+  float lr, mu, weight_decay;
+  int32_t augment;
+  uint64_t seed;
+  const uint64_t* seed_dev; /* optional device word XOR-ed into every step seed: lets a replayed CUDA
+                               graph draw fresh crops each round (bump it between replays) */
+} fedb_lenet_t;
+
+size_t fedb_lenet_workspace_bytes(int B);
+int fedb_lenet_train_step(const fedb_lenet_t* net, const uint8_t* images_u8, const int64_t* labels,
+                          int B, void* workspace, float* stats, uint64_t step_seed, void* stream);
+int fedb_lenet_eval(const fedb_lenet_t* net, const uint8_t* images_u8, const int64_t* labels, int B,
+                    void* workspace, float* stats, void* stream);
+/* forward only, logits out (tests) */
+int fedb_lenet_forward(const fedb_lenet_t* net, const uint8_t* images_u8, const float* images_f32,
+                       int B, void* workspace, float* logits, void* stream);
+/* gradient only (no update): writes dparam with the arena layout (tests) */
+int fedb_lenet_grad(const fedb_lenet_t* net, const float* images_f32, const int64_t* labels, int B,
+                    void* workspace, float* dparam, float* loss_out, void* stream);
+
+/* ------------------------------------------------------------------ peer memory manager
+ * CUDA VMM allocations exported as POSIX file descriptors, imported and mapped by peers, plus
+ * NVLS multicast objects when the fabric supports them.  Replaces checkpoint files and base64
+ * strings as the IPC medium.  reference: src/client.py:19-23, src/server.py:55-58 */
+typedef struct {
+  uint64_t handle;     /* CUmemGenericAllocationHandle */
+  uint64_t ptr;        /* mapped device VA in this process */
+  uint64_t bytes;      /* padded to the allocation granularity */
+  int32_t device;      /* device the physical memory lives on (-1: imported, unknown) */
+  int32_t fd;          /* exported fd (-1 if not exported) */
+} fedb_mem_t;
+
+int fedb_mem_supported(int device, int* vmm, int* posix_fd, int* multicast);
+int fedb_mem_create(uint64_t bytes, int device, fedb_mem_t* out);
+int fedb_mem_export_fd(fedb_mem_t* mem);
+int fedb_mem_import_fd(int fd, uint64_t bytes, int device, fedb_mem_t* out);
+int fedb_mem_release(fedb_mem_t* mem);
+int fedb_mc_create(uint64_t bytes, int n_devices, fedb_mem_t* out_mc);          /* rank 0 */
+int fedb_mc_import_fd(int fd, uint64_t bytes, fedb_mem_t* out_mc);              /* other ranks */
+int fedb_mc_add_device(fedb_mem_t* mc, int device);
+int fedb_mc_bind_and_map(fedb_mem_t* mc, const fedb_mem_t* local_mem, int device); /* sets mc->ptr */
+/* fd exchange over a unix domain socket (SCM_RIGHTS) */
+int fedb_fd_serve(const char* path, const int* fds, int n_fds, int n_clients, int timeout_ms);
+int fedb_fd_fetch(const char* path, int* out_fds, int n_fds, int timeout_ms);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* FEDB200_H */
