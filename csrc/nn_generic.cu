@@ -1,0 +1,544 @@
+// Generic fp32 NHWC operators for the whole model zoo: every op the 44
+// constructors use has a hand-written forward and backward here, so any zoo model trains on the GPU
+// without a library kernel.  These are the BREADTH kernels - simple, correct for every
+// (kernel, stride, padding, groups) combination in the zoo (1x1/3x3/5x5/7x7, depthwise, grouped,
+// bias) - and the numerical cross-check for the tcgen05 paths (gemm_tc.cu / conv_tc.cu), which take
+// over the GEMM-shaped layers.  Activations are NHWC (channels_last), weights stay OIHW as in the
+// checkpoint; small transposed weight copies are made per call so that every global access is
+// coalesced along the channel dimension.
+#include "common.cuh"
+#include "../include/fedb200.h"
+
+namespace {
+
+struct ConvShape {
+  int N, H, W, C, K, R, S, P, Q, sh, sw, ph, pw, groups;
+};
+
+__device__ __forceinline__ float act_fwd(float z, int act) {
+  if (act == 1) return fmaxf(z, 0.f);
+  if (act == 2) return z / (1.f + expf(-z));          // swish
+  if (act == 3) return 1.f / (1.f + expf(-z));        // sigmoid
+  return z;
+}
+__device__ __forceinline__ float act_bwd(float z, int act) {   // d act / d z
+  if (act == 1) return z > 0.f ? 1.f : 0.f;
+  if (act == 2) { float s = 1.f / (1.f + expf(-z)); return s * (1.f + z * (1.f - s)); }
+  if (act == 3) { float s = 1.f / (1.f + expf(-z)); return s * (1.f - s); }
+  return 1.f;
+}
+
+// w[K][Cg][R][S] -> wt[R][S][Cg][K] (forward) and wt2[R][S][K][Cg] (dgrad)
+__global__ void weight_transpose_kernel(const float* __restrict__ w, float* __restrict__ wt, float* __restrict__ wt2,
+                                        int K, int Cg, int R, int S) {
+  const int total = K * Cg * R * S;
+  for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < total; i += gridDim.x * blockDim.x) {
+    const int s = i % S, r = (i / S) % R, c = (i / (S * R)) % Cg, k = i / (S * R * Cg);
+    const float v = w[i];
+    if (wt) wt[((r * S + s) * Cg + c) * K + k] = v;
+    if (wt2) wt2[((r * S + s) * K + k) * Cg + c] = v;
+  }
+}
+
+__global__ void __launch_bounds__(256) conv_fwd_kernel(const float* __restrict__ x, const float* __restrict__ wt,
+                                                      const float* __restrict__ bias, float* __restrict__ y,
+                                                      ConvShape c) {
+  const int Cg = c.C / c.groups, Kg = c.K / c.groups;
+  const long long total = (long long)c.N * c.P * c.Q * c.K;
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+    const int k = (int)(i % c.K);
+    long long t = i / c.K;
+    const int q = (int)(t % c.Q); t /= c.Q;
+    const int p = (int)(t % c.P);
+    const int n = (int)(t / c.P);
+    const int g = k / Kg;
+    float acc = bias ? bias[k] : 0.f;
+    for (int r = 0; r < c.R; ++r) {
+      const int ih = p * c.sh - c.ph + r;
+      if (ih < 0 || ih >= c.H) continue;
+      for (int s = 0; s < c.S; ++s) {
+        const int iw = q * c.sw - c.pw + s;
+        if (iw < 0 || iw >= c.W) continue;
+        const float* xp = x + (((long long)n * c.H + ih) * c.W + iw) * c.C + g * Cg;
+        const float* wp = wt + ((long long)(r * c.S + s) * Cg) * c.K + k;
+#pragma unroll 4
+        for (int cc = 0; cc < Cg; ++cc) acc = fmaf(xp[cc], wp[(long long)cc * c.K], acc);
+      }
+    }
+    y[i] = acc;
+  }
+}
+
+__global__ void __launch_bounds__(256) conv_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ wt2,
+                                                        float* __restrict__ dx, ConvShape c) {
+  const int Cg = c.C / c.groups, Kg = c.K / c.groups;
+  const long long total = (long long)c.N * c.H * c.W * c.C;
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+    const int ch = (int)(i % c.C);
+    long long t = i / c.C;
+    const int w = (int)(t % c.W); t /= c.W;
+    const int h = (int)(t % c.H);
+    const int n = (int)(t / c.H);
+    const int g = ch / Cg, cl = ch % Cg;
+    float acc = 0.f;
+    for (int r = 0; r < c.R; ++r) {
+      const int pp = h + c.ph - r;
+      if (pp < 0 || pp % c.sh) continue;
+      const int p = pp / c.sh;
+      if (p >= c.P) continue;
+      for (int s = 0; s < c.S; ++s) {
+        const int qq = w + c.pw - s;
+        if (qq < 0 || qq % c.sw) continue;
+        const int q = qq / c.sw;
+        if (q >= c.Q) continue;
+        const float* dyp = dy + (((long long)n * c.P + p) * c.Q + q) * c.K + g * Kg;
+        const float* wp = wt2 + ((long long)(r * c.S + s) * c.K + g * Kg) * Cg + cl;
+#pragma unroll 4
+        for (int kk = 0; kk < Kg; ++kk) acc = fmaf(dyp[kk], wp[(long long)kk * Cg], acc);
+      }
+    }
+    dx[i] = acc;
+  }
+}
+
+// grid.x: chunks of kPix output pixels, grid.y: tiles of 256 weight elements; partial sums are
+// combined with atomicAdd (dw is zeroed by the caller).
+constexpr int kPix = 256;
+__global__ void __launch_bounds__(256) conv_wgrad_kernel(const float* __restrict__ x, const float* __restrict__ dy,
+                                                        float* __restrict__ dw, float* __restrict__ dbias,
+                                                        ConvShape c) {
+  const int Cg = c.C / c.groups, Kg = c.K / c.groups;
+  const int nW = c.K * Cg * c.R * c.S;
+  const int wi = blockIdx.y * 256 + threadIdx.x;
+  const long long npix = (long long)c.N * c.P * c.Q;
+  const long long p0 = (long long)blockIdx.x * kPix;
+  const long long p1 = p0 + kPix < npix ? p0 + kPix : npix;
+  if (wi < nW) {
+    const int s = wi % c.S, r = (wi / c.S) % c.R, cl = (wi / (c.S * c.R)) % Cg, k = wi / (c.S * c.R * Cg);
+    const int g = k / Kg;
+    float acc = 0.f;
+    for (long long pix = p0; pix < p1; ++pix) {
+      const int q = (int)(pix % c.Q);
+      const int p = (int)((pix / c.Q) % c.P);
+      const int n = (int)(pix / ((long long)c.Q * c.P));
+      const int ih = p * c.sh - c.ph + r, iw = q * c.sw - c.pw + s;
+      if (ih < 0 || ih >= c.H || iw < 0 || iw >= c.W) continue;
+      acc = fmaf(dy[pix * c.K + k], x[(((long long)n * c.H + ih) * c.W + iw) * c.C + g * Cg + cl], acc);
+    }
+    atomicAdd(dw + wi, acc);
+  }
+  if (dbias != nullptr && blockIdx.y == 0) {
+    for (int k = threadIdx.x; k < c.K; k += 256) {
+      float acc = 0.f;
+      for (long long pix = p0; pix < p1; ++pix) acc += dy[pix * c.K + k];
+      atomicAdd(dbias + k, acc);
+    }
+  }
+}
+
+// ------------------------------------------------------------------------------------ batch norm
+// NHWC: element (row, c) at row*C + c.  Block = 32 channels x 8 row-lanes.
+__global__ void __launch_bounds__(256) bn_stats_kernel(const float* __restrict__ x, float* __restrict__ mean,
+                                                      float* __restrict__ invstd, float* __restrict__ run_mean,
+                                                      float* __restrict__ run_var, long long rows, int C, float eps,
+                                                      float momentum) {
+  __shared__ float s_sum[8][33], s_sq[8][33];
+  const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  const int ch = blockIdx.x * 32 + cx;
+  float sum = 0.f, sq = 0.f;
+  if (ch < C)
+    for (long long r = ry; r < rows; r += 8) {
+      const float v = x[r * C + ch];
+      sum += v;
+      sq = fmaf(v, v, sq);
+    }
+  s_sum[ry][cx] = sum;
+  s_sq[ry][cx] = sq;
+  __syncthreads();
+  if (ry == 0 && ch < C) {
+#pragma unroll
+    for (int j = 1; j < 8; ++j) { sum += s_sum[j][cx]; sq += s_sq[j][cx]; }
+    const float m = sum / (float)rows;
+    float var = sq / (float)rows - m * m;
+    var = var < 0.f ? 0.f : var;
+    mean[ch] = m;
+    invstd[ch] = rsqrtf(var + eps);
+    if (run_mean != nullptr) {
+      const float unbiased = rows > 1 ? var * (float)rows / (float)(rows - 1) : var;
+      run_mean[ch] = (1.f - momentum) * run_mean[ch] + momentum * m;
+      run_var[ch] = (1.f - momentum) * run_var[ch] + momentum * unbiased;
+    }
+  }
+}
+
+// y = act(gamma * (x - mean) * invstd + beta); in eval mode mean/invstd come from running stats
+__global__ void __launch_bounds__(256) bn_apply_kernel(const float* __restrict__ x, float* __restrict__ y,
+                                                      const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                      const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                      long long total, int C, int act) {
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+    const int ch = (int)(i % C);
+    const float z = fmaf((x[i] - mean[ch]) * invstd[ch], gamma[ch], beta[ch]);
+    y[i] = act_fwd(z, act);
+  }
+}
+
+__global__ void bn_eval_prep_kernel(const float* __restrict__ run_mean, const float* __restrict__ run_var,
+                                    float* __restrict__ mean, float* __restrict__ invstd, int C, float eps) {
+  const int ch = blockIdx.x * blockDim.x + threadIdx.x;
+  if (ch < C) { mean[ch] = run_mean[ch]; invstd[ch] = rsqrtf(run_var[ch] + eps); }
+}
+
+// pass 1 of the backward: per-channel sum(dz) and sum(dz * xhat), dz = dy * act'(z)
+__global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const float* __restrict__ x, const float* __restrict__ dy,
+                                                           const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                           const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                           float* __restrict__ dgamma, float* __restrict__ dbeta,
+                                                           long long rows, int C, int act) {
+  __shared__ float s_a[8][33], s_b[8][33];
+  const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
+  const int ch = blockIdx.x * 32 + cx;
+  float sa = 0.f, sb = 0.f;
+  if (ch < C) {
+    const float m = mean[ch], is = invstd[ch], g = gamma[ch], b = beta[ch];
+    for (long long r = ry; r < rows; r += 8) {
+      const float xh = (x[r * C + ch] - m) * is;
+      float d = dy[r * C + ch];
+      if (act) d *= act_bwd(fmaf(xh, g, b), act);
+      sa += d;
+      sb = fmaf(d, xh, sb);
+    }
+  }
+  s_a[ry][cx] = sa;
+  s_b[ry][cx] = sb;
+  __syncthreads();
+  if (ry == 0 && ch < C) {
+#pragma unroll
+    for (int j = 1; j < 8; ++j) { sa += s_a[j][cx]; sb += s_b[j][cx]; }
+    dbeta[ch] = sa;
+    dgamma[ch] = sb;
+  }
+}
+
+// pass 2: dx = gamma * invstd * (dz - mean(dz) - xhat * mean(dz * xhat))
+__global__ void __launch_bounds__(256) bn_bwd_apply_kernel(const float* __restrict__ x, const float* __restrict__ dy,
+                                                          float* __restrict__ dx, const float* __restrict__ mean,
+                                                          const float* __restrict__ invstd, const float* __restrict__ gamma,
+                                                          const float* __restrict__ beta, const float* __restrict__ dgamma,
+                                                          const float* __restrict__ dbeta, long long total, int C,
+                                                          float inv_rows, int act, int training) {
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+    const int ch = (int)(i % C);
+    const float is = invstd[ch], g = gamma[ch];
+    const float xh = (x[i] - mean[ch]) * is;
+    float d = dy[i];
+    if (act) d *= act_bwd(fmaf(xh, g, beta[ch]), act);
+    // eval mode: the statistics are constants, BN is a per-channel affine map
+    dx[i] = training ? g * is * (d - dbeta[ch] * inv_rows - xh * dgamma[ch] * inv_rows) : g * is * d;
+  }
+}
+
+// ------------------------------------------------------------------------------------ elementwise
+__global__ void __launch_bounds__(256) act_fwd_kernel(const float* __restrict__ x, float* __restrict__ y, long long n, int act) {
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long long)gridDim.x * 256) y[i] = act_fwd(x[i], act);
+}
+__global__ void __launch_bounds__(256) act_bwd_kernel(const float* __restrict__ x, const float* __restrict__ dy,
+                                                     float* __restrict__ dx, long long n, int act) {
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long long)gridDim.x * 256)
+    dx[i] = dy[i] * act_bwd(x[i], act);
+}
+__global__ void __launch_bounds__(256) add_act_kernel(const float* __restrict__ a, const float* __restrict__ b,
+                                                     float* __restrict__ y, long long n, int act) {
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long long)gridDim.x * 256)
+    y[i] = act_fwd(a[i] + b[i], act);
+}
+// y[n,hw,c] = x[n,hw,c] * s[n,c] (mode 0) ; per-sample scalar s[n] (mode 1: drop-connect / dropout masks)
+__global__ void __launch_bounds__(256) scale_kernel(const float* __restrict__ x, const float* __restrict__ s,
+                                                   float* __restrict__ y, long long total, long long per_sample, int C, int mode) {
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+    const long long n = i / per_sample;
+    y[i] = x[i] * (mode == 0 ? s[n * C + (i % C)] : s[n]);
+  }
+}
+// ds[n,c] = sum_hw dy*x   (SE excitation backward wrt the gate)
+__global__ void __launch_bounds__(256) scale_bwd_gate_kernel(const float* __restrict__ x, const float* __restrict__ dy,
+                                                            float* __restrict__ ds, int HW, int C, int N) {
+  const int i = blockIdx.x * 256 + threadIdx.x;
+  if (i >= N * C) return;
+  const int n = i / C, ch = i % C;
+  const float* xp = x + (long long)n * HW * C + ch;
+  const float* dp = dy + (long long)n * HW * C + ch;
+  float acc = 0.f;
+  for (int p = 0; p < HW; ++p) acc = fmaf(xp[(long long)p * C], dp[(long long)p * C], acc);
+  ds[i] = acc;
+}
+// Philox-free counter hash: mask[i] = (u < keep) / keep
+__global__ void __launch_bounds__(256) bernoulli_mask_kernel(float* __restrict__ m, long long n, float keep,
+                                                            unsigned long long seed, const unsigned long long* __restrict__ ctr) {
+  const unsigned long long base = seed ^ (ctr ? *ctr * 0x9E3779B97F4A7C15ull : 0ull);
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long long)gridDim.x * 256) {
+    unsigned long long z = base + (unsigned long long)i * 0xD1B54A32D192ED03ull + 0x9E3779B97F4A7C15ull;
+    z = (z ^ (z >> 30)) * 0xBF58476D1CE4E5B9ull;
+    z = (z ^ (z >> 27)) * 0x94D049BB133111EBull;
+    z ^= z >> 31;
+    const float u = (float)(z >> 40) * (1.f / 16777216.f);
+    m[i] = u < keep ? 1.f / keep : 0.f;
+  }
+}
+
+// ------------------------------------------------------------------------------------ pooling
+struct PoolShape { int N, H, W, C, P, Q, kh, kw, sh, sw, ph, pw; };
+
+__global__ void __launch_bounds__(256) pool_fwd_kernel(const float* __restrict__ x, float* __restrict__ y,
+                                                      int* __restrict__ arg, PoolShape s, int is_max) {
+  const long long total = (long long)s.N * s.P * s.Q * s.C;
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+    const int ch = (int)(i % s.C);
+    long long t = i / s.C;
+    const int q = (int)(t % s.Q); t /= s.Q;
+    const int p = (int)(t % s.P);
+    const int n = (int)(t / s.P);
+    float best = -INFINITY, sum = 0.f;
+    int besti = -1;
+    for (int r = 0; r < s.kh; ++r) {
+      const int ih = p * s.sh - s.ph + r;
+      if (ih < 0 || ih >= s.H) continue;
+      for (int c = 0; c < s.kw; ++c) {
+        const int iw = q * s.sw - s.pw + c;
+        if (iw < 0 || iw >= s.W) continue;
+        const float v = x[(((long long)n * s.H + ih) * s.W + iw) * s.C + ch];
+        sum += v;
+        if (v > best) { best = v; besti = ih * s.W + iw; }
+      }
+    }
+    if (is_max) { y[i] = best; if (arg) arg[i] = besti; }
+    else y[i] = sum / (float)(s.kh * s.kw);          // count_include_pad=True, torch's default
+  }
+}
+
+__global__ void __launch_bounds__(256) pool_bwd_kernel(const float* __restrict__ dy, const int* __restrict__ arg,
+                                                      float* __restrict__ dx, PoolShape s, int is_max) {
+  // gather form: one thread per INPUT element, deterministic
+  const long long total = (long long)s.N * s.H * s.W * s.C;
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+    const int ch = (int)(i % s.C);
+    long long t = i / s.C;
+    const int w = (int)(t % s.W); t /= s.W;
+    const int h = (int)(t % s.H);
+    const int n = (int)(t / s.H);
+    float acc = 0.f;
+    for (int r = 0; r < s.kh; ++r) {
+      const int pp = h + s.ph - r;
+      if (pp < 0 || pp % s.sh) continue;
+      const int p = pp / s.sh;
+      if (p >= s.P) continue;
+      for (int c = 0; c < s.kw; ++c) {
+        const int qq = w + s.pw - c;
+        if (qq < 0 || qq % s.sw) continue;
+        const int q = qq / s.sw;
+        if (q >= s.Q) continue;
+        const long long o = (((long long)n * s.P + p) * s.Q + q) * s.C + ch;
+        if (is_max) { if (arg[o] == h * s.W + w) acc += dy[o]; }
+        else acc += dy[o] / (float)(s.kh * s.kw);
+      }
+    }
+    dx[i] = acc;
+  }
+}
+
+// ------------------------------------------------------------------------------------ channel moves (K11)
+// out[row, dst_off + j] = in[row, src_off + map(j)] for j < width; map = identity or shuffle
+__global__ void __launch_bounds__(256) channel_copy_kernel(const float* __restrict__ in, float* __restrict__ out,
+                                                          long long rows, int Cin, int Cout, int src_off, int dst_off,
+                                                          int width, int shuffle_groups, int accumulate) {
+  const long long total = rows * width;
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+    const int j = (int)(i % width);
+    const long long row = i / width;
+    int sj = j;
+    if (shuffle_groups > 1) {         // out channel j = (cpg_idx * g + grp)  <-  in channel grp * cpg + cpg_idx
+      const int cpg = width / shuffle_groups;
+      sj = (j % shuffle_groups) * cpg + j / shuffle_groups;
+    }
+    const float v = in[row * Cin + src_off + sj];
+    float* o = out + row * Cout + dst_off + j;
+    *o = accumulate ? *o + v : v;
+  }
+}
+
+// ------------------------------------------------------------------------------------ small linear (classifier)
+// y[b][j] = act(bias[j] + sum_k x[b][k] W[j][k]); one warp per output
+__global__ void __launch_bounds__(256) linear_fwd_kernel(const float* __restrict__ x, const float* __restrict__ W,
+                                                        const float* __restrict__ bias, float* __restrict__ y, int B,
+                                                        int K, int J, int act) {
+  const int lane = threadIdx.x & 31;
+  const long long o = ((long long)blockIdx.x * 256 + threadIdx.x) >> 5;
+  if (o >= (long long)B * J) return;
+  const int j = (int)(o % J), b = (int)(o / J);
+  float acc = 0.f;
+  for (int k = lane; k < K; k += 32) acc = fmaf(x[(long long)b * K + k], W[(long long)j * K + k], acc);
+  acc = warp_sum(acc);
+  if (lane == 0) y[o] = act_fwd(acc + (bias ? bias[j] : 0.f), act);
+}
+// dx[b][k] = sum_j dy[b][j] W[j][k]
+__global__ void __launch_bounds__(256) linear_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ W,
+                                                          float* __restrict__ dx, int B, int K, int J) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i >= (long long)B * K) return;
+  const int k = (int)(i % K), b = (int)(i / K);
+  float acc = 0.f;
+  for (int j = 0; j < J; ++j) acc = fmaf(dy[(long long)b * J + j], W[(long long)j * K + k], acc);
+  dx[i] = acc;
+}
+// dW[j][k] = sum_b dy[b][j] x[b][k];  db[j] = sum_b dy[b][j]   (deterministic: fixed order over b)
+__global__ void __launch_bounds__(256) linear_wgrad_kernel(const float* __restrict__ dy, const float* __restrict__ x,
+                                                          float* __restrict__ dW, float* __restrict__ db, int B, int K, int J) {
+  const long long i = (long long)blockIdx.x * 256 + threadIdx.x;
+  if (i < (long long)J * K) {
+    const int k = (int)(i % K), j = (int)(i / K);
+    float acc = 0.f;
+    for (int b = 0; b < B; ++b) acc = fmaf(dy[(long long)b * J + j], x[(long long)b * K + k], acc);
+    dW[i] += acc;
+  } else if (db != nullptr && i < (long long)J * K + J) {
+    const int j = (int)(i - (long long)J * K);
+    float acc = 0.f;
+    for (int b = 0; b < B; ++b) acc += dy[(long long)b * J + j];
+    db[j] += acc;
+  }
+}
+
+inline int grid_for(long long n, int cap_mult = 16) {
+  long long b = (n + 255) / 256;
+  const long long cap = (long long)fedb_num_sms() * cap_mult;
+  if (b > cap) b = cap;
+  if (b < 1) b = 1;
+  return (int)b;
+}
+
+}  // namespace
+
+#define S_ ((cudaStream_t)stream)
+
+extern "C" int fedb_nn_weight_transpose(const float* w, float* wt, float* wt2, int K, int Cg, int R, int S, void* stream) {
+  weight_transpose_kernel<<<grid_for((long long)K * Cg * R * S), 256, 0, S_>>>(w, wt, wt2, K, Cg, R, S);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+
+static ConvShape mk(const int* d) {
+  ConvShape c;
+  c.N = d[0]; c.H = d[1]; c.W = d[2]; c.C = d[3]; c.K = d[4]; c.R = d[5]; c.S = d[6]; c.P = d[7]; c.Q = d[8];
+  c.sh = d[9]; c.sw = d[10]; c.ph = d[11]; c.pw = d[12]; c.groups = d[13];
+  return c;
+}
+
+extern "C" int fedb_nn_conv_fwd(const float* x, const float* wt, const float* bias, float* y, const int* shape14, void* stream) {
+  const ConvShape c = mk(shape14);
+  FEDB_REQUIRE(c.C % c.groups == 0 && c.K % c.groups == 0, "conv: channels not divisible by groups");
+  conv_fwd_kernel<<<grid_for((long long)c.N * c.P * c.Q * c.K), 256, 0, S_>>>(x, wt, bias, y, c);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+extern "C" int fedb_nn_conv_dgrad(const float* dy, const float* wt2, float* dx, const int* shape14, void* stream) {
+  const ConvShape c = mk(shape14);
+  conv_dgrad_kernel<<<grid_for((long long)c.N * c.H * c.W * c.C), 256, 0, S_>>>(dy, wt2, dx, c);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+extern "C" int fedb_nn_conv_wgrad(const float* x, const float* dy, float* dw, float* dbias, const int* shape14, void* stream) {
+  const ConvShape c = mk(shape14);
+  const int nW = c.K * (c.C / c.groups) * c.R * c.S;
+  dim3 grid(fedb_ceil_div((long long)c.N * c.P * c.Q, kPix), fedb_ceil_div(nW, 256));
+  conv_wgrad_kernel<<<grid, 256, 0, S_>>>(x, dy, dw, dbias, c);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+
+extern "C" int fedb_nn_bn_fwd(const float* x, float* y, float* mean, float* invstd, float* run_mean, float* run_var,
+                              const float* gamma, const float* beta, long long rows, int C, float eps, float momentum,
+                              int training, int act, void* stream) {
+  if (training) bn_stats_kernel<<<fedb_ceil_div(C, 32), 256, 0, S_>>>(x, mean, invstd, run_mean, run_var, rows, C, eps, momentum);
+  else bn_eval_prep_kernel<<<fedb_ceil_div(C, 128), 128, 0, S_>>>(run_mean, run_var, mean, invstd, C, eps);
+  bn_apply_kernel<<<grid_for(rows * C), 256, 0, S_>>>(x, y, mean, invstd, gamma, beta, rows * C, C, act);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+extern "C" int fedb_nn_bn_bwd(const float* x, const float* dy, float* dx, const float* mean, const float* invstd,
+                              const float* gamma, const float* beta, float* dgamma, float* dbeta, long long rows, int C,
+                              int act, int training, void* stream) {
+  bn_bwd_reduce_kernel<<<fedb_ceil_div(C, 32), 256, 0, S_>>>(x, dy, mean, invstd, gamma, beta, dgamma, dbeta, rows, C, act);
+  bn_bwd_apply_kernel<<<grid_for(rows * C), 256, 0, S_>>>(x, dy, dx, mean, invstd, gamma, beta, dgamma, dbeta, rows * C, C,
+                                                         1.f / (float)rows, act, training);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+
+extern "C" int fedb_nn_act_fwd(const float* x, float* y, long long n, int act, void* stream) {
+  act_fwd_kernel<<<grid_for(n), 256, 0, S_>>>(x, y, n, act);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+extern "C" int fedb_nn_act_bwd(const float* x, const float* dy, float* dx, long long n, int act, void* stream) {
+  act_bwd_kernel<<<grid_for(n), 256, 0, S_>>>(x, dy, dx, n, act);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+extern "C" int fedb_nn_add_act(const float* a, const float* b, float* y, long long n, int act, void* stream) {
+  add_act_kernel<<<grid_for(n), 256, 0, S_>>>(a, b, y, n, act);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+extern "C" int fedb_nn_scale(const float* x, const float* s, float* y, long long total, long long per_sample, int C, int mode,
+                             void* stream) {
+  scale_kernel<<<grid_for(total), 256, 0, S_>>>(x, s, y, total, per_sample, C, mode);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+extern "C" int fedb_nn_scale_bwd_gate(const float* x, const float* dy, float* ds, int HW, int C, int N, void* stream) {
+  scale_bwd_gate_kernel<<<fedb_ceil_div((long long)N * C, 256), 256, 0, S_>>>(x, dy, ds, HW, C, N);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+extern "C" int fedb_nn_bernoulli_mask(float* m, long long n, float keep, uint64_t seed, const uint64_t* ctr_dev, void* stream) {
+  bernoulli_mask_kernel<<<grid_for(n), 256, 0, S_>>>(m, n, keep, seed, (const unsigned long long*)ctr_dev);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+extern "C" int fedb_nn_pool_fwd(const float* x, float* y, int* arg, const int* shape12, int is_max, void* stream) {
+  PoolShape s;
+  const int* d = shape12;
+  s.N = d[0]; s.H = d[1]; s.W = d[2]; s.C = d[3]; s.P = d[4]; s.Q = d[5]; s.kh = d[6]; s.kw = d[7]; s.sh = d[8]; s.sw = d[9];
+  s.ph = d[10]; s.pw = d[11];
+  pool_fwd_kernel<<<grid_for((long long)s.N * s.P * s.Q * s.C), 256, 0, S_>>>(x, y, arg, s, is_max);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+extern "C" int fedb_nn_pool_bwd(const float* dy, const int* arg, float* dx, const int* shape12, int is_max, void* stream) {
+  PoolShape s;
+  const int* d = shape12;
+  s.N = d[0]; s.H = d[1]; s.W = d[2]; s.C = d[3]; s.P = d[4]; s.Q = d[5]; s.kh = d[6]; s.kw = d[7]; s.sh = d[8]; s.sw = d[9];
+  s.ph = d[10]; s.pw = d[11];
+  pool_bwd_kernel<<<grid_for((long long)s.N * s.H * s.W * s.C), 256, 0, S_>>>(dy, arg, dx, s, is_max);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+extern "C" int fedb_nn_channel_copy(const float* in, float* out, long long rows, int Cin, int Cout, int src_off, int dst_off,
+                                    int width, int shuffle_groups, int accumulate, void* stream) {
+  channel_copy_kernel<<<grid_for(rows * width), 256, 0, S_>>>(in, out, rows, Cin, Cout, src_off, dst_off, width,
+                                                             shuffle_groups, accumulate);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+extern "C" int fedb_nn_linear_fwd(const float* x, const float* W, const float* bias, float* y, int B, int K, int J, int act,
+                                  void* stream) {
+  linear_fwd_kernel<<<fedb_ceil_div((long long)B * J * 32, 256), 256, 0, S_>>>(x, W, bias, y, B, K, J, act);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+extern "C" int fedb_nn_linear_bwd(const float* dy, const float* x, const float* W, float* dx, float* dW, float* db, int B, int K,
+                                  int J, void* stream) {
+  if (dx) linear_dgrad_kernel<<<fedb_ceil_div((long long)B * K, 256), 256, 0, S_>>>(dy, W, dx, B, K, J);
+  if (dW) linear_wgrad_kernel<<<fedb_ceil_div((long long)J * K + J, 256), 256, 0, S_>>>(dy, x, dW, db, B, K, J);
+  FEDB_LAUNCH_OK();
+  return 0;
+}

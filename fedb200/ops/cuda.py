@@ -207,7 +207,9 @@ class LeNetPlan:
         self.desc.lr, self.desc.mu, self.desc.weight_decay = lr, momentum, weight_decay
         self.desc.augment, self.desc.seed = int(augment), 0
         self.max_batch = 0
-        self.workspace = None
+        self.workspace = None          # training workspace: its address is baked into captured graphs
+        self.eval_batch_cap = 0
+        self.eval_workspace = None     # separate, so growing it never invalidates a training graph
         self.stats = torch.zeros(4, dtype=torch.float32, device=arena.f32.device)   # loss, correct, samples, steps
         self.reserve(max_batch)
 
@@ -225,32 +227,36 @@ class LeNetPlan:
                                           current_stream()), "fedb_lenet_train_step")
         _lib.count_launch(4)
 
+    def _eval_ws(self, B: int) -> torch.Tensor:
+        if B > self.eval_batch_cap:
+            self.eval_workspace = torch.empty(lib().fedb_lenet_workspace_bytes(B), dtype=torch.uint8,
+                                              device=self.arena.f32.device)
+            self.eval_batch_cap = B
+        return self.eval_workspace
+
     def eval_batch(self, images_u8: torch.Tensor, labels: torch.Tensor, stats: Optional[torch.Tensor] = None) -> None:
         B = images_u8.shape[0]
-        self.reserve(B)
         check(lib().fedb_lenet_eval(C.byref(self.desc), images_u8.data_ptr(), labels.data_ptr(), B,
-                                    self.workspace.data_ptr(), ptr(self.stats if stats is None else stats),
+                                    self._eval_ws(B).data_ptr(), ptr(self.stats if stats is None else stats),
                                     current_stream()), "fedb_lenet_eval")
         _lib.count_launch(3)
 
     def forward(self, images: torch.Tensor) -> torch.Tensor:
         B = images.shape[0]
-        self.reserve(B)
         logits = torch.empty(B, 10, dtype=torch.float32, device=images.device)
         u8 = images.dtype == torch.uint8
         check(lib().fedb_lenet_forward(C.byref(self.desc), images.data_ptr() if u8 else 0,
-                                       0 if u8 else images.contiguous().data_ptr(), B, self.workspace.data_ptr(),
+                                       0 if u8 else images.contiguous().data_ptr(), B, self._eval_ws(B).data_ptr(),
                                        logits.data_ptr(), current_stream()), "fedb_lenet_forward")
         _lib.count_launch(2)
         return logits
 
     def grad(self, images_f32: torch.Tensor, labels: torch.Tensor):
         B = images_f32.shape[0]
-        self.reserve(B)
         dparam = torch.zeros(self.arena.manifest.n_param, dtype=torch.float32, device=images_f32.device)
         loss = torch.zeros(4, dtype=torch.float32, device=images_f32.device)
         check(lib().fedb_lenet_grad(C.byref(self.desc), images_f32.contiguous().data_ptr(), labels.data_ptr(), B,
-                                    self.workspace.data_ptr(), dparam.data_ptr(), loss.data_ptr(),
+                                    self._eval_ws(B).data_ptr(), dparam.data_ptr(), loss.data_ptr(),
                                     current_stream()), "fedb_lenet_grad")
         _lib.count_launch(4)
         return dparam, loss[0]
