@@ -170,6 +170,18 @@ def main():
                 return
             real_print(*a, **k)
         server.print = stamped_print
+        # harness ordering only: the reference's start-up is racy in two ways - a backup promotes itself
+        # after 10-20 s without pings (src/server.py:254-264) and a primary whose backup push fails
+        # poisons its own worker table - so this process is spawned first (its imports overlap
+        # the backup's) and waits here until the backup listens before it replays the main block.
+        import socket
+        deadline = time.time() + 300
+        while time.time() < deadline:
+            try:
+                socket.create_connection(("127.0.0.1", int(args.backup_port)), timeout=0.5).close()
+                break
+            except OSError:
+                time.sleep(0.1)
         # replay of src/server.py:286-293
         server.ConnectToBackupServer("localhost", args.backup_port)
         server.mountPoint = "Primary"

@@ -95,12 +95,16 @@ def run_reference(n_workers: int, rounds: int, warmup: int, model: str = "LeNet"
         for port in wports:
             if not _wait_port(port, 600):
                 raise RuntimeError(f"reference worker on port {port} did not come up (see {work}/reference.log)")
-        # backup and primary start together: the backup's watchdog promotes it after 10-20 s without a
-        # ping (src/server.py:254-264), so it must not wait for the workers' slow start-up
-        spawn("backup", ["--backup-port", str(bport), "--workers", workers, "--rounds", str(total)], cenv)
+        # Ordering matters twice: the backup's watchdog promotes it after 10-20 s without a ping
+        # (src/server.py:254-264), so the primary is started first and is already pinging when the backup
+        # comes up; and the primary must find the backup listening before round 0, because a failed backup
+        # push poisons its worker table (clients[None] = False, src/server.py:75,142) - the
+        # launcher holds run() until the backup port answers.
         timing = os.path.join(work, "timing.json")
         prim = spawn("primary", ["--backup-port", str(bport), "--workers", workers, "--rounds", str(total),
                                  "--timing-out", timing], cenv)
+        time.sleep(1.0)     # the primary starts pinging first; it waits for the backup before round 0
+        spawn("backup", ["--backup-port", str(bport), "--workers", workers, "--rounds", str(total)], cenv)
         prim.wait(timeout=timeout_s)
         if prim.returncode != 0 or not os.path.exists(timing):
             raise RuntimeError(f"reference primary failed (rc={prim.returncode}); see {work}/reference.log")
