@@ -92,3 +92,66 @@ extern "C" int fedb_cross_entropy(const float* logits, const int64_t* target, fl
   FEDB_LAUNCH_OK();
   return 0;
 }
+
+// ------------------------------------------------------------------------------------------------
+// Allocation-free variant of fedb_cross_entropy.
+//
+// Who needs it: hosts that must not (or cannot) ask the driver for memory at the moment they compute
+// a loss.  Two kinds show up around this library.  (1) A process that has already handed every byte
+// of the GPU to a pool of its own - torch's caching allocator running at its high-water mark next to
+// the model it trains, or a serving runtime that carves one fixed arena at start-up: there a
+// cudaMalloc from a library either fails with out-of-memory although the pool has room, or it
+// fragments the little that is left.  (2) A latency-critical loop (a worker's evaluation inside
+// SendModel, a coordinator's round loop): cudaMalloc and cudaFree synchronise the whole device, so a
+// lazily growing scratch buffer turns into a stall at an unpredictable step.
+// fedb_cross_entropy grows its row scratch with cudaMalloc/cudaFree when the batch grows; this entry
+// point never does.  Its scratch is the fixed array below, which lives in the library image: every
+// GPU that loads libfedb200.so holds these 128 KiB from load until the process exits.
+//
+// Rules that follow from the fixed array:
+//  * B may not exceed FEDB_CE_STATIC_MAX_ROWS; larger batches are refused with an error (split the
+//    batch, or use fedb_cross_entropy).
+//  * All calls on one GPU share the array and it keeps whatever the last call left in it.  Nothing in
+//    it has to start at zero: each call writes rows [0, B) of both halves before its second kernel
+//    reads exactly those rows, so stale rows are never observed and there is nothing to clear.
+//    (`stats` accumulates, but that buffer is the caller's, as in fedb_cross_entropy.)
+//  * Two calls whose kernels can be in flight at the same time on one GPU (different streams, or
+//    different host threads on different streams) race on the array.  Serialise them - same stream,
+//    or an event between them.
+//  * The FIRST call on each device looks up the array's device address (cudaGetSymbolAddress, with
+//    that device current) and caches it per device; make that first call before starting any stream
+//    capture on the device.  The name of the array is only a host-side handle for that lookup - the
+//    kernels are always given the looked-up pointer.
+// FEDB_CE_STATIC_MAX_ROWS (16384) comes from include/fedb200.h: 2 x 16384 floats = 128 KiB
+#define FEDB_CE_STATIC_MAX_DEVICES 64
+
+static __device__ __align__(256) float g_ce_static_rows[2 * FEDB_CE_STATIC_MAX_ROWS];
+static float* g_ce_static_addr[FEDB_CE_STATIC_MAX_DEVICES] = {nullptr};
+
+extern "C" int fedb_cross_entropy_static(const float* logits, const int64_t* target, float* dlogits, float* loss_out,
+                                         float* stats, int B, int C, void* stream) {
+  FEDB_REQUIRE(logits != nullptr && target != nullptr, "fedb_cross_entropy_static: null input");
+  FEDB_REQUIRE(B > 0 && C > 0 && C <= 4096, "fedb_cross_entropy_static: bad shape");
+  if (B > FEDB_CE_STATIC_MAX_ROWS)
+    return fedb_fail(-2, __FILE__, __LINE__,
+                     "fedb_cross_entropy_static: batch exceeds FEDB_CE_STATIC_MAX_ROWS (16384 rows); "
+                     "split the batch or call fedb_cross_entropy");
+  int dev = -1;
+  FEDB_CHECK(cudaGetDevice(&dev));
+  FEDB_REQUIRE(dev >= 0 && dev < FEDB_CE_STATIC_MAX_DEVICES, "fedb_cross_entropy_static: device index out of range");
+  if (g_ce_static_addr[dev] == nullptr) {
+    // once per device, with that device current: the symbol has one instance per GPU
+    float* p = nullptr;
+    FEDB_CHECK(cudaGetSymbolAddress((void**)&p, g_ce_static_rows));
+    FEDB_REQUIRE(p != nullptr, "fedb_cross_entropy_static: symbol lookup returned null");
+    g_ce_static_addr[dev] = p;
+  }
+  float* loss_rows = g_ce_static_addr[dev];
+  float* corr_rows = loss_rows + FEDB_CE_STATIC_MAX_ROWS;
+  cudaStream_t s = (cudaStream_t)stream;
+  ce_kernel<<<fedb_ceil_div(B, 4), 128, 0, s>>>(logits, target, dlogits, loss_rows, corr_rows, B, C);
+  FEDB_LAUNCH_OK();
+  ce_finish_kernel<<<1, 256, 0, s>>>(loss_rows, corr_rows, loss_out, stats, B);
+  FEDB_LAUNCH_OK();
+  return 0;
+}

@@ -156,6 +156,21 @@ def cross_entropy_raw(logits: torch.Tensor, target: torch.Tensor, dlogits: Optio
     _lib.count_launch(2)
 
 
+def cross_entropy_static_raw(logits: torch.Tensor, target: torch.Tensor, dlogits: Optional[torch.Tensor],
+                             loss_out: Optional[torch.Tensor], stats: Optional[torch.Tensor]) -> None:
+    """``cross_entropy_raw`` for hosts that cannot allocate device memory at call time (a GPU already
+    fully owned by the caller's pool, or a latency-critical loop where cudaMalloc would synchronise the
+    device): the library's row scratch is a fixed 128 KiB array, so B is limited to 16384 rows and calls
+    that may overlap on one GPU must be ordered by the caller.  Make the first call on a device outside
+    stream capture (it looks up the array's address once per device)."""
+    B, Cn = logits.shape
+    fn = _lib.bind("fedb_cross_entropy_static", C.c_int,
+                   [C.c_void_p] * 5 + [C.c_int, C.c_int, C.c_void_p])
+    check(fn(logits.data_ptr(), target.data_ptr(), ptr(dlogits), ptr(loss_out), ptr(stats), B, Cn,
+             current_stream()), "fedb_cross_entropy_static")
+    _lib.count_launch(2)
+
+
 class _CrossEntropy(torch.autograd.Function):
     @staticmethod
     def forward(ctx, logits, target):

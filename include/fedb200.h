@@ -115,6 +115,22 @@ int fedb_adam_step(float* param, const float* grad, float* m, float* v, int64_t 
 int fedb_cross_entropy(const float* logits, const int64_t* target, float* dlogits, float* loss_out,
                        float* stats, int B, int C, void* stream);
 
+/* Same computation and same arguments as fedb_cross_entropy, for callers that cannot allocate device
+ * memory when they call: a process whose whole GPU already belongs to its own pool (torch's caching
+ * allocator at its high-water mark, a serving runtime with one fixed arena), where a library's
+ * cudaMalloc fails or fragments, and latency-critical loops, where cudaMalloc/cudaFree would
+ * synchronise the device.  This entry point calls no cudaMalloc/cudaFree and no allocating routine:
+ * its per-row scratch is a fixed 128 KiB array inside the library image (held by every GPU that loads
+ * the library until exit).  Limits and rules: B <= FEDB_CE_STATIC_MAX_ROWS (16384), larger batches are
+ * refused with an error; all calls on a GPU share that array, so calls that may overlap on the GPU
+ * race - keep them on one stream or order them with an event; nothing in the array needs clearing
+ * between calls (each call writes the rows it later reads); the first call on each device looks up
+ * the array's address and should be made before any stream capture on that device.
+ * This entry point has no counterpart in the reference. */
+#define FEDB_CE_STATIC_MAX_ROWS 16384
+int fedb_cross_entropy_static(const float* logits, const int64_t* target, float* dlogits, float* loss_out,
+                              float* stats, int B, int C, void* stream);
+
 /* ------------------------------------------------------------------ K14 input pipeline
  * uint8 NHWC [B,32,32,3] -> fp32 NCHW (nhwc_out=0) or NHWC (1), ToTensor+Normalize, optional
  * RandomCrop(32,4)+flip drawn from (seed, sample index).  reference: src/main.py:36-46 */
