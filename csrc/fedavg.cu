@@ -165,7 +165,7 @@ __global__ void __launch_bounds__(kThreads, 4) fedavg_kernel(const __grid_consta
       long long s = p.src_i64[0][i];
       for (int k = 1; k < p.n_src; ++k) s += p.src_i64[k][i];
       long long r = (long long)truncf(__fdiv_rn(__ll2float_rn(s), n_div));
-      for (int d = 0; d < p.n_dst; ++d)
+      for (int d = 0; d < p.n_dst_i64; ++d)
         if (p.dst_i64[d] != nullptr) p.dst_i64[d][i] = r;
     }
   }
@@ -240,6 +240,7 @@ extern "C" int fedb_fedavg(const fedb_agg_desc_t* d, int max_blocks, void* strea
   FEDB_REQUIRE(d != nullptr, "fedb_fedavg: null descriptor");
   FEDB_REQUIRE(d->n_src >= 1 && d->n_src <= FEDB_MAX_PEERS, "fedb_fedavg: n_src out of range");
   FEDB_REQUIRE(d->n_dst >= 0 && d->n_dst <= FEDB_MAX_DST, "fedb_fedavg: n_dst out of range");
+  FEDB_REQUIRE(d->n_dst_i64 >= 0 && d->n_dst_i64 <= FEDB_MAX_DST, "fedb_fedavg: n_dst_i64 out of range");
   FEDB_REQUIRE((d->begin % 4) == 0 && (d->end % 4) == 0 && d->begin <= d->end,
                "fedb_fedavg: range must be 4-element aligned");
   FEDB_REQUIRE(d->ctrl_local != nullptr, "fedb_fedavg: ctrl_local is required (grid completion counter)");

@@ -1,0 +1,419 @@
+// tcgen05 / TMEM / TMA GEMM for sm_100a (north star: "conv/GEMM as tcgen05/TMEM tiles
+// fed by TMA").  D[M,N] (+)= A[M,K] * B[N,K]^T with fp32 operands fed to the 5th-generation tensor
+// cores as TF32 (kind::tf32, fp32 accumulation in tensor memory): activations and weights of the
+// framework are fp32, so TMA streams them straight from the NHWC tensors / OIHW weights - no
+// conversion pass - and the result stays within tf32 rounding of the reference's fp32 math.
+//
+// One kernel template covers the three GEMMs of a 1x1 convolution / linear layer:
+//   forward   Y[pix,Cout]  = X[pix,Cin]   * W[Cout,Cin]^T        TF32, A and B K-major (as stored)
+//   dgrad     dX[pix,Cin]  = dY[pix,Cout] * Wt[Cin,Cout]^T       TF32, K-major with a transposed copy of the (small) weight
+//   wgrad     dW[Cout,Cin] = dY[pix,Cout]^T * X[pix,Cin]         BF16 (kind::f16), A and B MN-major exactly as the NHWC
+//                                                                 tensors lie in memory, split-K over the pixels
+// (TF32 operands in MN-major order need the 32-byte-atom swizzle variant; the weight gradient instead reads
+//  bf16 copies of dY and X, which is also what mixed-precision training stores for the backward pass.)
+//
+// Structure (one CTA per 128 x BN output tile, 6 warps):
+//   warp 0      TMA producer: cp.async.bulk.tensor.2d (128B swizzle) into a 4-stage smem ring, mbarrier tx-count
+//   warp 1      TMEM allocation + MMA issue: one elected lane issues tcgen05.mma.cta_group::1.kind::tf32,
+//               tcgen05.commit releases smem stages and finally signals the epilogue
+//   warps 2..5  epilogue: tcgen05.ld (32 lanes x 32 bit) -> registers -> bias / ReLU -> global stores
+//               (red.global.add for split-K partial tiles)
+// SASS evidence expected: UTCHMMA/UTCQMMA-family for the MMA, LDTM for tcgen05.ld, UTMALDG for TMA.
+#include "common.cuh"
+#include "../include/fedb200.h"
+#include <cuda.h>
+
+namespace {
+
+constexpr int BM = 128;          // UMMA M
+constexpr int STAGES = 4;
+// KIND 0: tf32, both operands K-major.   stage = [rows][32 fp32] (128 B rows), 4 MMAs of K=8 per stage
+// KIND 1: bf16, both operands MN-major.  stage = chunks of 64 bf16 (128 B) x 64 K-rows, 4 MMAs of K=16 per stage
+template <int KIND> struct Kind;
+template <> struct Kind<0> { static constexpr int kElem = 4, kBK = 32, kUmmaK = 8, kSteps = 4, kChunk = 32; };
+template <> struct Kind<1> { static constexpr int kElem = 2, kBK = 64, kUmmaK = 16, kSteps = 4, kChunk = 64; };
+constexpr int kThreads = 192;
+
+// ------------------------------------------------------------------------------------ PTX wrappers
+__device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
+
+__device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;" ::"r"(smem_u32(bar)), "r"(count));
+}
+__device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
+  const uint32_t addr = smem_u32(bar);
+  uint32_t done;
+  do {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "mbarrier.try_wait.parity.shared::cta.b64 p, [%1], %2;\n"
+        "selp.u32 %0, 1, 0, p;\n"
+        "}\n"
+        : "=r"(done)
+        : "r"(addr), "r"(parity)
+        : "memory");
+  } while (!done);
+}
+__device__ __forceinline__ void tma_load_2d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];" ::"r"(
+          smem_u32(smem_dst)),
+      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void tma_load_4d(void* smem_dst, const CUtensorMap* map, uint64_t* bar, int c0, int c1, int c2,
+                                            int c3) {
+  asm volatile(
+      "cp.async.bulk.tensor.4d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5, %6}], [%2];" ::
+          "r"(smem_u32(smem_dst)),
+      "l"(map), "r"(smem_u32(bar)), "r"(c0), "r"(c1), "r"(c2), "r"(c3)
+      : "memory");
+}
+__device__ __forceinline__ void tmem_alloc(uint32_t* smem_slot, uint32_t ncols) {
+  asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;" ::"r"(smem_u32(smem_slot)), "r"(ncols)
+               : "memory");
+  asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;" ::: "memory");
+}
+__device__ __forceinline__ void tmem_dealloc(uint32_t taddr, uint32_t ncols) {
+  asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;" ::"r"(taddr), "r"(ncols) : "memory");
+}
+__device__ __forceinline__ void tc_fence_before() { asm volatile("tcgen05.fence::before_thread_sync;" ::: "memory"); }
+__device__ __forceinline__ void tc_fence_after() { asm volatile("tcgen05.fence::after_thread_sync;" ::: "memory"); }
+template <int KIND>
+__device__ __forceinline__ void umma(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t idesc, uint32_t accumulate) {
+  if constexpr (KIND == 0) {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::tf32 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  } else {
+    asm volatile(
+        "{\n"
+        ".reg .pred p;\n"
+        "setp.ne.b32 p, %4, 0;\n"
+        "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n"
+        "}\n" ::"r"(tmem_d),
+        "l"(adesc), "l"(bdesc), "r"(idesc), "r"(accumulate)
+        : "memory");
+  }
+}
+__device__ __forceinline__ void umma_commit(uint64_t* bar) {
+  asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
+__device__ __forceinline__ void tmem_ld16(uint32_t taddr, float (&v)[16]) {
+  uint32_t r[16];
+  asm volatile(
+      "tcgen05.ld.sync.aligned.32x32b.x16.b32 {%0,%1,%2,%3,%4,%5,%6,%7,%8,%9,%10,%11,%12,%13,%14,%15}, [%16];"
+      : "=r"(r[0]), "=r"(r[1]), "=r"(r[2]), "=r"(r[3]), "=r"(r[4]), "=r"(r[5]), "=r"(r[6]), "=r"(r[7]), "=r"(r[8]),
+        "=r"(r[9]), "=r"(r[10]), "=r"(r[11]), "=r"(r[12]), "=r"(r[13]), "=r"(r[14]), "=r"(r[15])
+      : "r"(taddr));
+  asm volatile("tcgen05.wait::ld.sync.aligned;" ::: "memory");
+#pragma unroll
+  for (int i = 0; i < 16; ++i) v[i] = __uint_as_float(r[i]);
+}
+
+// 64-bit shared-memory matrix descriptor, 128-byte swizzle, Blackwell version field = 1
+__device__ __forceinline__ uint64_t make_smem_desc(uint32_t saddr, uint32_t lbo_bytes, uint32_t sbo_bytes) {
+  uint64_t d = 0;
+  d |= (uint64_t)((saddr >> 4) & 0x3FFF);
+  d |= (uint64_t)((lbo_bytes >> 4) & 0x3FFF) << 16;
+  d |= (uint64_t)((sbo_bytes >> 4) & 0x3FFF) << 32;
+  d |= (uint64_t)1 << 46;          // descriptor version (sm_100)
+  d |= (uint64_t)2 << 61;          // SWIZZLE_128B
+  return d;
+}
+// instruction descriptor: D=F32, dense, M=128; KIND 0: A=B=TF32 K-major, KIND 1: A=B=BF16 MN-major
+__host__ __device__ constexpr uint32_t make_idesc(int n, int kind) {
+  const uint32_t fmt = kind == 0 ? 2u : 1u;
+  const uint32_t mn = kind == 0 ? 0u : 1u;
+  return (1u << 4) | (fmt << 7) | (fmt << 10) | (mn << 15) | (mn << 16) | ((uint32_t)(n >> 3) << 17) |
+         ((uint32_t)(BM >> 4) << 24);
+}
+
+struct GemmArgs {
+  float* D;
+  const float* bias;   // per output column, may be null
+  long long ldd;
+  int M, N, K;
+  int k_per_split;     // K elements handled by one blockIdx.z
+  int relu;
+  int atomic_out;      // 1: red.add into D (split-K / accumulate)
+};
+
+// smem stage layout: A tile then B tile, each a multiple of 1024 B (swizzle atom)
+template <int BN, int KIND>
+struct Smem {
+  static constexpr int kBN = (KIND == 1 && BN < 64) ? 64 : BN;                 // MN-major chunks are 64 wide
+  static constexpr int kABytes = BM * Kind<KIND>::kBK * Kind<KIND>::kElem;     // 16 KiB
+  static constexpr int kBBytes = kBN * Kind<KIND>::kBK * Kind<KIND>::kElem;
+  static constexpr int kStage = kABytes + kBBytes;
+  static constexpr int kTotal = STAGES * kStage + 1024 /*align slack*/ + 256 /*barriers*/;
+};
+
+template <int BN, int KIND>
+__global__ void __launch_bounds__(kThreads, 1)
+gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, GemmArgs g) {
+  extern __shared__ uint8_t smem_raw[];
+  uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
+  uint64_t* full = (uint64_t*)(smem + STAGES * Smem<BN, KIND>::kStage);
+  uint64_t* empty = full + STAGES;
+  uint64_t* accum_ready = empty + STAGES;
+  uint32_t* tmem_slot = (uint32_t*)(accum_ready + 1);
+
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int m0 = blockIdx.x * BM, n0 = blockIdx.y * BN;
+  const int k_begin = blockIdx.z * g.k_per_split;
+  const int k_end = min(g.K, k_begin + g.k_per_split);
+  constexpr int BK = Kind<KIND>::kBK;
+  constexpr int kChunkBytes = BK * 128;          // one MN-major chunk: BK K-rows of 128 bytes
+  const int num_k = (k_end - k_begin + BK - 1) / BK;
+  constexpr uint32_t kTmemCols = BN < 32 ? 32 : BN;   // power of two >= 32
+
+  if (threadIdx.x == 0) {
+    for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    mbar_init(accum_ready, 1);
+    asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+  }
+  if (warp == 1) tmem_alloc(tmem_slot, kTmemCols);
+  tc_fence_before();
+  __syncthreads();
+  tc_fence_after();
+  const uint32_t tmem_base = *tmem_slot;
+
+  if (warp == 0) {
+    // ===================================================================== TMA producer
+    if (lane == 0) {
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA) : "memory");
+      asm volatile("prefetch.tensormap [%0];" ::"l"(&mapB) : "memory");
+      for (int i = 0; i < num_k; ++i) {
+        const int s = i % STAGES;
+        const uint32_t ph = (i / STAGES) & 1;
+        mbar_wait(&empty[s], ph ^ 1);
+        uint8_t* a_dst = smem + s * Smem<BN, KIND>::kStage;
+        uint8_t* b_dst = a_dst + Smem<BN, KIND>::kABytes;
+        mbar_expect_tx(&full[s], Smem<BN, KIND>::kStage);
+        const int k0 = k_begin + i * BK;
+        if constexpr (KIND == 0) {
+          tma_load_2d(a_dst, &mapA, &full[s], k0, m0);                     // box [32 fp32 (K) x BM rows]
+          tma_load_2d(b_dst, &mapB, &full[s], k0, n0);                     // box [32 fp32 (K) x BN rows]
+        } else {
+#pragma unroll
+          for (int c = 0; c < BM / 64; ++c)                                // box [64 bf16 (M) x BK K-rows] per chunk
+            tma_load_2d(a_dst + c * kChunkBytes, &mapA, &full[s], m0 + c * 64, k0);
+#pragma unroll
+          for (int c = 0; c < Smem<BN, KIND>::kBN / 64; ++c)
+            tma_load_2d(b_dst + c * kChunkBytes, &mapB, &full[s], n0 + c * 64, k0);
+        }
+      }
+    }
+  } else if (warp == 1) {
+    // ===================================================================== MMA issuer
+    if (lane == 0) {
+      constexpr uint32_t idesc = make_idesc(BN, KIND);
+      for (int i = 0; i < num_k; ++i) {
+        const int s = i % STAGES;
+        const uint32_t ph = (i / STAGES) & 1;
+        mbar_wait(&full[s], ph);
+        tc_fence_after();
+        const uint32_t a_base = smem_u32(smem + s * Smem<BN, KIND>::kStage);
+        const uint32_t b_base = a_base + Smem<BN, KIND>::kABytes;
+#pragma unroll
+        for (int k = 0; k < Kind<KIND>::kSteps; ++k) {
+          // K-major (tf32): 8 rows x 128 B swizzle atoms, SBO = 1024 B between 8-row groups; one MMA consumes
+          //   32 B of K, so the start address advances 32 B inside the swizzled row.
+          // MN-major (bf16): 64-element chunks of M/N lie kChunkBytes apart (LBO); 8 K-rows x 128 B form one
+          //   1024 B atom (SBO); one MMA consumes 16 K-rows = 2048 B.
+          const uint64_t ad = KIND == 0 ? make_smem_desc(a_base + k * 32, 16, 1024)
+                                        : make_smem_desc(a_base + k * 2048, kChunkBytes, 1024);
+          const uint64_t bd = KIND == 0 ? make_smem_desc(b_base + k * 32, 16, 1024)
+                                        : make_smem_desc(b_base + k * 2048, kChunkBytes, 1024);
+          umma<KIND>(tmem_base, ad, bd, idesc, (i | k) != 0 ? 1u : 0u);
+        }
+        umma_commit(&empty[s]);          // frees the smem stage once these MMAs have read it
+      }
+      umma_commit(accum_ready);          // accumulator complete -> epilogue
+    }
+  } else {
+    // ===================================================================== epilogue (warps 2..5)
+    const int q = warp & 3;                                  // TMEM lane quarter this warp may access
+    const int row = m0 + q * 32 + lane;
+    mbar_wait(accum_ready, 0);
+    tc_fence_after();
+    if (num_k > 0) {
+#pragma unroll 1
+      for (int c0 = 0; c0 < BN; c0 += 16) {
+        float v[16];
+        tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+        if (row < g.M) {
+          float* drow = g.D + (long long)row * g.ldd + n0 + c0;
+#pragma unroll
+          for (int j = 0; j < 16; ++j) {
+            const int col = n0 + c0 + j;
+            if (col < g.N) {
+              float x = v[j];
+              if (g.bias != nullptr && blockIdx.z == 0) x += g.bias[col];
+              if (g.relu) x = fmaxf(x, 0.f);
+              if (g.atomic_out) atomicAdd(drow + j, x);
+              else drow[j] = x;
+            }
+          }
+        }
+      }
+    }
+    tc_fence_before();
+  }
+  __syncthreads();
+  if (warp == 1) {
+    tc_fence_after();
+    tmem_dealloc(tmem_base, kTmemCols);
+  }
+}
+
+// ------------------------------------------------------------------------------------ host side
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                  const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                  CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+
+int get_encode(EncodeTiledFn* out) {
+  static EncodeTiledFn fn = nullptr;
+  if (!fn) {
+    void* p = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    cudaError_t e = cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q);
+    if (e != cudaSuccess || p == nullptr) return fedb_fail((int)e ? (int)e : -2, __FILE__, __LINE__, "cuTensorMapEncodeTiled not available");
+    fn = (EncodeTiledFn)p;
+  }
+  *out = fn;
+  return 0;
+}
+
+// 2-D tensor [rows][cols] (elements of `elem` bytes: 4 = fp32, 2 = bf16) with row pitch ld (elements);
+// box = [box_cols x box_rows] with box_cols * elem == 128 bytes, 128B swizzle
+int make_map_2d(CUtensorMap* map, const void* base, int elem, long long rows, long long cols, long long ld, int box_cols,
+                int box_rows) {
+  EncodeTiledFn enc;
+  if (int rc = get_encode(&enc)) return rc;
+  FEDB_REQUIRE(((uintptr_t)base & 15) == 0 && (ld * elem) % 16 == 0, "gemm_tc: operand base/pitch must be 16-byte aligned");
+  cuuint64_t dims[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  cuuint64_t strides[1] = {(cuuint64_t)ld * elem};
+  cuuint32_t box[2] = {(cuuint32_t)box_cols, (cuuint32_t)box_rows};
+  cuuint32_t estr[2] = {1, 1};
+  CUresult r = enc(map, elem == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, (void*)base, dims,
+                   strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B,
+                   CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return fedb_fail((int)r, __FILE__, __LINE__, "cuTensorMapEncodeTiled failed");
+  return 0;
+}
+
+template <int BN, int KIND>
+int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmArgs& g, int splits, cudaStream_t s) {
+  static bool attr_set = false;
+  if (!attr_set) {
+    FEDB_CHECK(cudaFuncSetAttribute(gemm_tc_kernel<BN, KIND>, cudaFuncAttributeMaxDynamicSharedMemorySize,
+                                    Smem<BN, KIND>::kTotal));
+    attr_set = true;
+  }
+  dim3 grid(fedb_ceil_div(g.M, BM), fedb_ceil_div(g.N, BN), splits);
+  gemm_tc_kernel<BN, KIND><<<grid, kThreads, Smem<BN, KIND>::kTotal, s>>>(ma, mb, g);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+
+template <int KIND>
+int dispatch_bn(int bn, const CUtensorMap& ma, const CUtensorMap& mb, const GemmArgs& g, int splits, cudaStream_t s) {
+  switch (bn) {
+    case 128: return launch<128, KIND>(ma, mb, g, splits, s);
+    case 64: return launch<64, KIND>(ma, mb, g, splits, s);
+    case 32: return launch<32, KIND>(ma, mb, g, splits, s);
+    default: return fedb_fail(-1, __FILE__, __LINE__, "gemm_tc: unsupported BN");
+  }
+}
+
+int run_gemm(int kind, const void* A, const void* B, float* D, const float* bias, int M, int N, int K, long long lda,
+             long long ldb, long long ldd, int relu, int splits, int accumulate, cudaStream_t s) {
+  FEDB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_tc: empty problem");
+  FEDB_REQUIRE(splits >= 1, "gemm_tc: splits >= 1");
+  FEDB_REQUIRE(!(relu && (splits > 1 || accumulate)), "gemm_tc: ReLU cannot be fused into a partial sum");
+  const int bn = N >= 128 ? 128 : (N > 32 ? 64 : 32);
+  const int bk = kind == 0 ? Kind<0>::kBK : Kind<1>::kBK;
+  CUtensorMap ma, mb;
+  if (kind == 0) {       // A [M][K], B [N][K], fp32
+    if (int rc = make_map_2d(&ma, A, 4, M, K, lda, 32, BM)) return rc;
+    if (int rc = make_map_2d(&mb, B, 4, N, K, ldb, 32, bn)) return rc;
+  } else {               // A [K][M], B [K][N], bf16
+    if (int rc = make_map_2d(&ma, A, 2, K, M, lda, 64, bk)) return rc;
+    if (int rc = make_map_2d(&mb, B, 2, K, N, ldb, 64, bk)) return rc;
+  }
+  GemmArgs g;
+  g.D = D; g.bias = bias; g.ldd = ldd; g.M = M; g.N = N; g.K = K;
+  int kps = (K + splits - 1) / splits;
+  kps = (kps + bk - 1) / bk * bk;
+  g.k_per_split = kps;
+  splits = (K + kps - 1) / kps;
+  g.relu = relu;
+  g.atomic_out = (splits > 1 || accumulate) ? 1 : 0;
+  return kind == 0 ? dispatch_bn<0>(bn, ma, mb, g, splits, s) : dispatch_bn<1>(bn, ma, mb, g, splits, s);
+}
+
+__global__ void __launch_bounds__(256) cast_bf16_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst, long long n4) {
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n4; i += (long long)gridDim.x * 256) {
+    const float4 v = reinterpret_cast<const float4*>(src)[i];
+    __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y), hi = __floats2bfloat162_rn(v.z, v.w);
+    uint2 r;
+    r.x = *reinterpret_cast<uint32_t*>(&lo);
+    r.y = *reinterpret_cast<uint32_t*>(&hi);
+    reinterpret_cast<uint2*>(dst)[i] = r;
+  }
+}
+
+// out[c][r] = in[r][c]  (small weight matrices only)
+__global__ void __launch_bounds__(256) transpose_kernel(const float* __restrict__ in, float* __restrict__ out, int rows, int cols) {
+  __shared__ float tile[32][33];
+  const int bx = blockIdx.x * 32, by = blockIdx.y * 32;
+  const int tx = threadIdx.x & 31, ty = threadIdx.x >> 5;
+  for (int j = ty; j < 32; j += 8)
+    if (by + j < rows && bx + tx < cols) tile[j][tx] = in[(long long)(by + j) * cols + bx + tx];
+  __syncthreads();
+  for (int j = ty; j < 32; j += 8)
+    if (bx + j < cols && by + tx < rows) out[(long long)(bx + j) * rows + by + tx] = tile[tx][j];
+}
+
+}  // namespace
+
+// D[M,N] (+)= A[M,K] * B[N,K]^T, fp32 operands as TF32, both K-contiguous.
+extern "C" int fedb_gemm_tf32(const float* A, const float* B, float* D, const float* bias, int M, int N, int K, long long lda,
+                              long long ldb, long long ldd, int relu, int splits, int accumulate, void* stream) {
+  return run_gemm(0, A, B, D, bias, M, N, K, lda, ldb, ldd, relu, splits, accumulate, (cudaStream_t)stream);
+}
+
+// D[M,N] (+)= At[K,M]^T * Bt[K,N], bf16 operands stored with the REDUCTION dimension outermost (the layout of
+// NHWC activations / output gradients when the reduction runs over pixels), fp32 accumulation and output.
+extern "C" int fedb_gemm_bf16_tn(const uint16_t* At, const uint16_t* Bt, float* D, int M, int N, int K, long long lda,
+                                 long long ldb, long long ldd, int splits, int accumulate, void* stream) {
+  return run_gemm(1, At, Bt, D, nullptr, M, N, K, lda, ldb, ldd, 0, splits, accumulate, (cudaStream_t)stream);
+}
+
+extern "C" int fedb_cast_bf16(const float* src, uint16_t* dst, long long n, void* stream) {
+  FEDB_REQUIRE(n % 4 == 0, "fedb_cast_bf16: n must be a multiple of 4");
+  long long blocks = (n / 4 + 255) / 256;
+  if (blocks > fedb_num_sms() * 16) blocks = fedb_num_sms() * 16;
+  if (blocks < 1) blocks = 1;
+  cast_bf16_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(src, (__nv_bfloat16*)dst, n / 4);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+
+extern "C" int fedb_transpose(const float* in, float* out, int rows, int cols, void* stream) {
+  dim3 grid(fedb_ceil_div(cols, 32), fedb_ceil_div(rows, 32));
+  transpose_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(in, out, rows, cols);
+  FEDB_LAUNCH_OK();
+  return 0;
+}

@@ -101,8 +101,30 @@ extern "C" int fedb_mem_create(uint64_t bytes, int device, fedb_mem_t* out) {
   CUmemAllocationProp prop = device_prop(device);
   size_t gran = 0;
   DRV(cuMemGetAllocationGranularity, &gran, &prop, CU_MEM_ALLOC_GRANULARITY_RECOMMENDED);
-  // multicast binding wants its own (possibly larger) granularity; 2 MiB covers both on sm_100
   if (gran < (2u << 20)) gran = 2u << 20;
+  // a multicast object must be a multiple of ITS granularity, and it spans the whole allocation:
+  // pad to the larger of the two so that fedb_mc_create(bytes) succeeds for every arena size
+  {
+    CUdevice dev;
+    DRV(cuDeviceGet, &dev, device);
+    int mc = 0;
+    DRV(cuDeviceGetAttribute, &mc, CU_DEVICE_ATTRIBUTE_MULTICAST_SUPPORTED, dev);
+    for (int it = 0; mc && it < 4; ++it) {   // the granularity may depend on the (padded) size: iterate to a fixpoint
+      CUmulticastObjectProp mp;
+      memset(&mp, 0, sizeof(mp));
+      mp.numDevices = 2;
+      mp.size = (bytes + gran - 1) / gran * gran;
+      mp.handleTypes = CU_MEM_HANDLE_TYPE_POSIX_FILE_DESCRIPTOR;
+      size_t mgran = 0;
+      DRV(cuMulticastGetGranularity, &mgran, &mp, CU_MULTICAST_GRANULARITY_RECOMMENDED);
+      if (mgran <= gran || mgran % gran != 0) {
+        if (mgran > gran) gran = mgran;
+        else break;
+      } else {
+        gran = mgran;
+      }
+    }
+  }
   const uint64_t padded = (bytes + gran - 1) / gran * gran;
   CUmemGenericAllocationHandle h;
   DRV(cuMemCreate, &h, padded, &prop, 0);

@@ -36,7 +36,8 @@ class AggDesc(C.Structure):
         ("src", vp * MAX_PEERS), ("src_i64", vp * MAX_PEERS),
         ("dst", vp * MAX_DST), ("dst_i64", vp * MAX_DST), ("dst_bf16", vp * MAX_DST),
         ("weight", C.c_float * MAX_PEERS),
-        ("n_src", C.c_int32), ("n_dst", C.c_int32), ("uniform", C.c_int32), ("do_i64", C.c_int32),
+        ("n_src", C.c_int32), ("n_dst", C.c_int32), ("n_dst_i64", C.c_int32), ("uniform", C.c_int32),
+        ("do_i64", C.c_int32),
         ("begin", C.c_int64), ("end", C.c_int64), ("n_i64", C.c_int64),
         ("src_q", vp * MAX_PEERS), ("src_scale", vp * MAX_PEERS), ("base", vp),
         ("mc_src", vp), ("mc_dst", vp),

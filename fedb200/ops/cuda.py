@@ -65,7 +65,7 @@ def fedavg_raw(src_f32: Sequence[int], dst_f32: Sequence[int], begin: int, end: 
     if not uniform:
         for i, w in enumerate(weights):
             d.weight[i] = float(w)
-    d.n_src, d.n_dst, d.uniform = n_src, len(dst_f32), int(uniform)
+    d.n_src, d.n_dst, d.n_dst_i64, d.uniform = n_src, len(dst_f32), len(dst_i64), int(uniform)
     d.do_i64 = int(n_i64 > 0 and len(src_i64) == n_src)
     d.begin, d.end, d.n_i64 = begin, end, n_i64
     d.base, d.mc_src, d.mc_dst = base, mc_src, mc_dst

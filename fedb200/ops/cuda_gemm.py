@@ -1,13 +1,108 @@
-"""tcgen05 GEMM bindings (filled in with csrc/gemm_tc.cu)."""
+"""Bindings of the tcgen05/TMEM/TMA GEMM (csrc/gemm_tc.cu) and the conv lowering onto it.
+
+A 1x1 / stride-1 / ungrouped convolution over NHWC activations IS a GEMM over the flat
+[pixels, channels] matrices:
+  forward  Y[pix,K]  = X[pix,C] W[K,C]^T          TF32, operands exactly as stored
+  dgrad    dX[pix,C] = dY[pix,K] Wt[C,K]^T        TF32, with a transposed copy of the (small) weight
+  wgrad    dW[K,C]   = dY[pix,K]^T X[pix,C]       BF16 copies of dY and X, MN-major (as stored), split-K
+Shapes outside the covered set return False and the caller runs the generic fp32 kernel.
+"""
+from __future__ import annotations
+
+import ctypes as C
+
+import torch
+
+from . import _lib
+from ._lib import check, current_stream, lib
+
+_fns = {}
+MIN_PIXELS = 128          # below one M tile the generic kernel is as good
+
+
+def _f(name):
+    if name not in _fns:
+        vp, i, ll = C.c_void_p, C.c_int, C.c_longlong
+        sig = {
+            "fedb_gemm_tf32": [vp, vp, vp, vp, i, i, i, ll, ll, ll, i, i, i, vp],
+            "fedb_gemm_bf16_tn": [vp, vp, vp, i, i, i, ll, ll, ll, i, i, vp],
+            "fedb_cast_bf16": [vp, vp, ll, vp],
+            "fedb_transpose": [vp, vp, i, i, vp],
+        }[name]
+        _fns[name] = _lib.bind(name, C.c_int, sig)
+    return _fns[name]
+
+
+def gemm_tf32(A, B, D, M, N, K, lda, ldb, ldd, bias=None, relu=False, splits=1, accumulate=False):
+    """D[M,N] (+)= A[M,K] B[N,K]^T on the tensor cores (TF32 inputs, fp32 accumulation in TMEM)."""
+    check(_f("fedb_gemm_tf32")(A.data_ptr(), B.data_ptr(), D.data_ptr(), 0 if bias is None else bias.data_ptr(), M, N, K,
+                               lda, ldb, ldd, int(relu), splits, int(accumulate), current_stream()), "fedb_gemm_tf32")
+    _lib.count_launch()
+
+
+def gemm_bf16_tn(At, Bt, D, M, N, K, lda, ldb, ldd, splits=1, accumulate=False):
+    """D[M,N] (+)= At[K,M]^T Bt[K,N] with bf16 operands (reduction dimension outermost), fp32 out."""
+    check(_f("fedb_gemm_bf16_tn")(At.data_ptr(), Bt.data_ptr(), D.data_ptr(), M, N, K, lda, ldb, ldd, splits,
+                                  int(accumulate), current_stream()), "fedb_gemm_bf16_tn")
+    _lib.count_launch()
+
+
+def cast_bf16(x: torch.Tensor) -> torch.Tensor:
+    out = torch.empty(x.numel(), dtype=torch.bfloat16, device=x.device)
+    check(_f("fedb_cast_bf16")(x.data_ptr(), out.data_ptr(), x.numel(), current_stream()), "fedb_cast_bf16")
+    _lib.count_launch()
+    return out
+
+
+def transpose(w2d: torch.Tensor, rows: int, cols: int) -> torch.Tensor:
+    out = torch.empty(rows * cols, dtype=torch.float32, device=w2d.device)
+    check(_f("fedb_transpose")(w2d.data_ptr(), out.data_ptr(), rows, cols, current_stream()), "fedb_transpose")
+    _lib.count_launch()
+    return out
+
+
+def matmul_nt(a: torch.Tensor, b: torch.Tensor, bias=None, relu=False) -> torch.Tensor:
+    """a[M,K] @ b[N,K]^T (both row-major) -> [M,N]."""
+    M, K = a.shape
+    N = b.shape[0]
+    d = torch.empty(M, N, dtype=torch.float32, device=a.device)
+    gemm_tf32(a, b, d, M, N, K, a.stride(0), b.stride(0), N, bias=bias, relu=relu)
+    return d
+
+
+def _is_pointwise(shp) -> bool:
+    N, H, W, Cc, K, R, S, P, Q, sh, sw, ph, pw, groups = shp
+    return (R == 1 and S == 1 and sh == 1 and sw == 1 and ph == 0 and pw == 0 and groups == 1
+            and Cc % 32 == 0 and K % 32 == 0 and N * H * W >= MIN_PIXELS)
 
 
 def conv_forward(x, w, bias, y, shp) -> bool:
-    return False
+    if not _is_pointwise(shp):
+        return False
+    N, H, W, Cc, K = shp[:5]
+    gemm_tf32(x, w, y, N * H * W, K, Cc, Cc, Cc, K, bias=bias)          # Y[pix,K] = X[pix,C] W[K,C]^T
+    return True
 
 
 def conv_dgrad(dy, w, dx, shp) -> bool:
-    return False
+    if not _is_pointwise(shp):
+        return False
+    N, H, W, Cc, K = shp[:5]
+    wt = transpose(w, K, Cc)                                             # Wt[C,K]
+    gemm_tf32(dy, wt, dx, N * H * W, Cc, K, K, K, Cc)                    # dX[pix,C] = dY[pix,K] Wt[C,K]^T
+    return True
 
 
 def conv_wgrad(x, dy, dw, db, shp) -> bool:
-    return False
+    if not _is_pointwise(shp) or shp[3] % 64 or shp[4] % 64:
+        return False
+    N, H, W, Cc, K = shp[:5]
+    pix = N * H * W
+    # dW[K,C] = dY[pix,K]^T X[pix,C]: reduction over pixels, split across CTAs so that small layers
+    # (few output tiles) still fill the machine; partial tiles are reduced with red.global.add
+    tiles = ((K + 127) // 128) * ((Cc + 127) // 128)
+    splits = max(1, min(pix // 256, 296 // max(tiles, 1)))
+    gemm_bf16_tn(cast_bf16(dy), cast_bf16(x), dw, K, Cc, pix, K, Cc, Cc, splits=splits, accumulate=True)
+    if db is not None:
+        db += dy.sum(dim=(0, 2, 3))       # bias on a pointwise conv that reaches a GEMM tile: rare in the zoo
+    return True

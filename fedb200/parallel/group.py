@@ -57,6 +57,7 @@ class FedGroup:
         self.round = 0
         self.side_stream = torch.cuda.Stream(device=self.device, priority=0)
         self._agg_done = torch.cuda.Event()
+        self._common_base = False
         if codec == "fp8":
             dev = trainer.device
             self.residual = torch.zeros(self.man.n_f32, dtype=torch.float32, device=dev)
@@ -99,7 +100,10 @@ class FedGroup:
             dst += [bufs[r].client_f32_ptr() for r in live]
         dst_i64 += [bufs[r].client_i64_ptr() for r in live]
         kw = {}
-        if self.codec == "fp8":
+        # deltas need a base that is IDENTICAL on every rank: the first aggregation (different random
+        # inits, N6) therefore goes out lossless and establishes it
+        use_codec = self.codec == "fp8" and self._common_base
+        if use_codec:
             n = self.man.n_f32
             K.codec_encode(self.trainer.arena.f32[:n], self.base, self.residual, self.peers.me.q(),
                            self.peers.me.scale())
@@ -116,6 +120,7 @@ class FedGroup:
         if self.codec == "fp8":
             # the new global model is the base of the next round's deltas
             self.base.copy_(self.trainer.arena.f32[:self.man.n_f32])
+            self._common_base = True
         self.round += 1
         if self.repl_mode == "overlap" and self.rank == self.primary_rank and self.backup_rank != self.primary_rank:
             # K-REPL: primary -> backup peer copy on a side stream, overlapped with what follows

@@ -54,7 +54,9 @@ typedef struct {
   int64_t* dst_i64[FEDB_MAX_DST];
   uint16_t* dst_bf16[FEDB_MAX_DST];       /* optional bf16 shadow per destination (NULL = none) */
   float weight[FEDB_MAX_PEERS];           /* sample counts as floats; ignored when uniform */
-  int32_t n_src, n_dst;
+  int32_t n_src, n_dst;                   /* n_dst counts dst[] (fp32) */
+  int32_t n_dst_i64;                      /* entries of dst_i64[]: may exceed n_dst when the fp32 fan-out
+                                             goes through mc_dst but the counters go out as unicast stores */
   int32_t uniform;                        /* 1: plain mean (N1) */
   int32_t do_i64;                         /* 1: this launch also reduces the int64 segment */
   int64_t begin, end;                     /* fp32 element range, multiples of 4 */

@@ -11,6 +11,7 @@ if ROOT not in sys.path:
 def pytest_configure(config):
     config.addinivalue_line("markers", "gpu: needs a CUDA device (run with -m gpu on a B200)")
     config.addinivalue_line("markers", "slow: multi-process / long running")
+    config.addinivalue_line("markers", "tensorcores: run with the tcgen05 routing enabled")
 
 
 def reference_src():
