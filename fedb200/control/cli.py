@@ -38,6 +38,9 @@ def server_parser() -> argparse.ArgumentParser:
     p.add_argument("--no-backup", action="store_true", help="primary without a backup")
     p.add_argument("--state-dir", default=None, help="default Primary/ or Backup/")
     p.add_argument("--train-timeout", type=float, default=3600.0)
+    p.add_argument("--plane", choices=("legacy", "peer"), default="legacy",
+                   help="peer: workers exchange weights over NVLink peer memory, RPCs carry descriptors")
+    p.add_argument("--checkpoint-every", type=int, default=0, help="peer plane: dump optimizedModel.pth every k rounds")
     return p
 
 
@@ -53,7 +56,8 @@ def server_main(argv=None) -> int:
         workers=tuple(w for w in args.workers.split(",") if w), rounds=args.rounds, model=args.model,
         compress=compress, state_dir=args.state_dir or ("Primary" if primary else "Backup"),
         backup_target=None if (args.no_backup or not primary) else f"{args.backupAddress}:{args.backupPort}",
-        replicate=args.replicate, weighted=args.weighted, metrics_path=args.metrics,
+        replicate=args.replicate, weighted=args.weighted, metrics_path=args.metrics, plane=args.plane,
+        checkpoint_every=args.checkpoint_every,
         train_timeout_s=args.train_timeout, send_timeout_s=args.train_timeout)
     sink = JsonlSink(args.metrics)
     if primary:
@@ -86,6 +90,13 @@ def client_parser() -> argparse.ArgumentParser:
     p.add_argument("--pad-from", type=int, default=None, help="draw SxS images, zero-pad to 32x32")
     p.add_argument("--augment", action="store_true", help="RandomCrop(32,4)+flip like the reference")
     p.add_argument("--no-eval", action="store_true", help="skip the eval inside SendModel")
+    p.add_argument("--peer-rank", type=int, default=0, help="peer plane: this worker's index in the coordinator's --workers list")
+    p.add_argument("--peer-world", type=int, default=1, help="peer plane: number of configured workers")
+    p.add_argument("--peer-tag", default="fed", help="peer plane: job tag shared by all workers (names the unix sockets)")
+    p.add_argument("--codec", choices=("none", "fp8"), default="none",
+                   help="peer plane meaning of -c: none = lossless fp32 words, fp8 = block-scaled e4m3 deltas")
+    p.add_argument("--agg-timeout", type=float, default=20.0, help="peer plane: bound of the device-flag waits (s)")
+    p.add_argument("--rejoin", action="store_true", help="peer plane: this worker restarts into a running job")
     return p
 
 
@@ -104,8 +115,19 @@ def client_main(argv=None) -> int:
     tcfg = TrainerConfig(model=args.model, lr=args.lr, batch_size=args.batch_size, device=device,
                          seed=args.seed, augment=args.augment, resume=args.resume,
                          checkpoint_path=ckpt.worker_checkpoint_path(args.address))
-    trainer = LocalTrainer(tcfg, ds)
     wcfg = WorkerConfig(address=args.address, compress=args.compressFlag == "Y", plane=args.plane,
                         eval_on_send=not args.no_eval)
+    if args.plane == "peer":
+        from ..parallel.session import GpuFederation, PeerWorker
+        dev = torch.device(device)
+        fed = GpuFederation(model=args.model, rank=args.peer_rank, world=args.peer_world,
+                            device=dev.index if dev.index is not None else args.peer_rank, dataset=ds, seed=args.seed,
+                            tag=args.peer_tag, lr=args.lr, batch_size=args.batch_size, augment=args.augment,
+                            codec=args.codec, use_multicast=False, timeout_ns=int(args.agg_timeout * 1e9),
+                            persistent_server=True, rejoin=args.rejoin)
+        fed.trainer.cfg.checkpoint_path = tcfg.checkpoint_path
+        serve_worker(fed.trainer, wcfg, sink=JsonlSink(args.metrics), peer_endpoint=PeerWorker(fed), block=True)
+        return 0
+    trainer = LocalTrainer(tcfg, ds)
     serve_worker(trainer, wcfg, sink=JsonlSink(args.metrics), block=True)
     return 0

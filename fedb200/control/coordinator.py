@@ -58,6 +58,10 @@ class CoordinatorConfig:
     heartbeat_timeout_s: float = 2.0
     membership_period_s: float = 1.0
     metrics_path: Optional[str] = None
+    plane: str = "legacy"               # legacy: weights in the RPC payloads | peer: weights over NVLink, RPCs
+                                        # carry descriptors (workers must run with --plane peer on one box)
+    checkpoint_every: int = 0           # peer plane: every k rounds ask the primary's rank to dump
+                                        # optimizedModel.pth (0 = never; the global model lives in GPU memory)
 
 
 class Membership:
@@ -128,6 +132,9 @@ class Coordinator:
         self._repl_thread: Optional[threading.Thread] = None
         self._member_thread: Optional[threading.Thread] = None
         self.round_times: List[float] = []
+        # peer plane: a round died inside the device-flag protocol -> put the survivors on a fresh epoch first.
+        # A coordinator that takes over mid-run (promotion, restart) cannot know what is in flight: it resets too.
+        self._need_reset = cfg.plane == "peer" and start_round > 0
         os.makedirs(cfg.state_dir, exist_ok=True)
 
     # ------------------------------------------------------------------ persistence (C10, B6)
@@ -140,7 +147,7 @@ class Coordinator:
 
     def persist_meta(self) -> None:
         """``next_round`` = first round that has NOT been committed yet."""
-        tmp = self._path(STATE_FILE) + ".tmp"
+        tmp = self._path(STATE_FILE) + f".tmp.{os.getpid()}.{threading.get_ident()}"
         with open(tmp, "w") as f:
             json.dump({"term": self.term, "next_round": self.round, "model": self.cfg.model}, f)
         os.replace(tmp, self._path(STATE_FILE))
@@ -178,6 +185,18 @@ class Coordinator:
                     ch.close()
                     continue
                 if rep.status == 1:
+                    if self.cfg.plane == "peer":
+                        # the newcomer is a new process with new GPU memory: survivors map it again, then it
+                        # pulls the global model out of the primary's peer memory
+                        r = list(self.cfg.workers).index(w)
+                        remap = desc.encode("remap", rank=r)
+                        for other in self.members.live_workers():
+                            self._send_model_to(other, remap)
+                        self.members.readmit(w, ch)
+                        if self.round > 0:
+                            self._send_model_to(w, desc.encode("pull"))
+                        self._need_reset = True
+                        continue
                     self.members.readmit(w, ch)
                     if self.global_state is not None:       # hand the newcomer the current model
                         self._send_model_to(w)
@@ -201,15 +220,21 @@ class Coordinator:
             log.warning("deposed by worker %s during %s: %s", w, phase, e.details())
             return
         if code == grpc.StatusCode.ABORTED:
-            log.warning("worker %s busy during %s; skipped this round", w, phase)
+            log.warning("worker %s: %s aborted (%s); skipped this round", w, phase, e.details())
+            if "aggregation failed" in (e.details() or ""):
+                self._need_reset = True
             return
         self.members.mark_dead(w, f"{phase}: {code}")
+        self._need_reset = True
 
-    def _train_one(self, rank: int, w: str, world: int):
+    def _train_one(self, rank: int, w: str, world: int, live_ranks=None):
+        md = self._metadata()
+        if live_ranks is not None:
+            md = md + desc.live_metadata(live_ranks)
         try:
             call = self.members.stub(w).StartTrain.with_call(
                 proto.TrainRequest(rank=rank, world=world), timeout=self.cfg.train_timeout_s,
-                metadata=self._metadata())
+                metadata=md)
         except grpc.RpcError as e:
             self._rpc_failed(w, e, "StartTrain")
             return None
@@ -277,8 +302,20 @@ class Coordinator:
             log.warning("round %d: no live workers", self.round)
             time.sleep(self.cfg.membership_period_s)
             return None
+        peer = self.cfg.plane == "peer"
+        live_ranks = [list(self.cfg.workers).index(w) for w in live] if peer else None
+        if peer and self._need_reset:
+            # a previous round lost a worker inside the flag protocol: put every survivor on a fresh epoch
+            reset = desc.encode("reset", epoch=(self.round + 1) * 1024 + self.term)
+            with ThreadPoolExecutor(max_workers=len(live)) as pool:
+                list(pool.map(lambda w: self._send_model_to(w, reset), live))
+            self._need_reset = False
+            live = self.members.live_workers()
+            live_ranks = [list(self.cfg.workers).index(w) for w in live]
+            if not live:
+                return None
         with ThreadPoolExecutor(max_workers=len(live)) as pool:
-            uploads = list(pool.map(lambda rw: self._train_one(rw[0], rw[1], world), enumerate(live)))
+            uploads = list(pool.map(lambda rw: self._train_one(rw[0], rw[1], world, live_ranks), enumerate(live)))
         uploads = [u for u in uploads if u is not None]
         if self.stop_event.is_set():
             return None
@@ -286,9 +323,16 @@ class Coordinator:
         faults.fire("after_train", self.round)
         if not uploads:
             return None
-        self.global_state = self.aggregate(uploads)
-        payload = self._global_payload()
-        self.persist_model()
+        if peer:
+            if len(uploads) != len(live):
+                # somebody never trained, so the K-AGG launches already in flight on the survivors will time
+                # out in their flag wait: let SendModel collect that, then reset
+                self._need_reset = True
+            payload = desc.encode("global", round=self.round, term=self.term, version=self.round + 1)
+        else:
+            self.global_state = self.aggregate(uploads)
+            payload = self._global_payload()
+            self.persist_model()
         t2 = time.perf_counter()
         faults.fire("after_agg", self.round)
         if self._repl_thread is not None:
@@ -302,11 +346,18 @@ class Coordinator:
         faults.fire("after_repl", self.round)
         targets = [u["worker"] for u in uploads if self.members.snapshot().get(u["worker"])]
         with ThreadPoolExecutor(max_workers=max(len(targets), 1)) as pool:
-            list(pool.map(lambda w: self._send_model_to(w, payload), targets))
+            sent = list(pool.map(lambda w: self._send_model_to(w, payload), targets))
+        if peer and not all(sent):
+            # the aggregation did not complete on every participant (a peer died inside the flag protocol):
+            # the round is NOT committed; survivors are reset and the same round number runs again
+            self._need_reset = True
+            return None
         t4 = time.perf_counter()
         faults.fire("round_end", self.round)
+        if peer and self.cfg.checkpoint_every and (self.round + 1) % self.cfg.checkpoint_every == 0 and targets:
+            self._send_model_to(targets[0], desc.encode("dump", path=os.path.abspath(self._path(GLOBAL_MODEL_FILE))))
         rec = self.sink.write(
-            "round", round=self.round, term=self.term, live=len(live), uploads=len(uploads),
+            "round", round=self.round, term=self.term, live=len(live), uploads=len(uploads), plane=self.cfg.plane,
             world=world, train_s=t1 - t0, agg_s=t2 - t1, repl_s=t3 - t2, bcast_s=t4 - t3,
             total_s=t4 - t0, bytes_up=sum(u.get("bytes", 0) for u in uploads),
             bytes_down=len(payload) * (len(targets) + (1 if self._backup_channel else 0)))
@@ -318,7 +369,7 @@ class Coordinator:
         rounds = self.cfg.rounds if rounds is None else rounds
         self.start_membership()
         done = 0
-        if self.global_state is not None and self.round > 0:
+        if self.global_state is not None and self.round > 0 and self.cfg.plane != "peer":
             # promotion / restart: put every worker back on the last committed model (B6)
             for w in self.members.live_workers():
                 self._send_model_to(w)

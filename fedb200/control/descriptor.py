@@ -18,6 +18,7 @@ MAGIC = "fedb200/1 "
 MD_TERM = "fedb200-term"
 MD_ROUND = "fedb200-round"
 MD_ROLE = "fedb200-role"
+MD_LIVE = "fedb200-live"      # comma separated peer ranks that take part in this round (GPU plane)
 
 
 def encode(kind: str, **fields) -> str:
@@ -65,3 +66,14 @@ def read_fence(metadata: Optional[Iterable]) -> Tuple[Optional[int], Optional[in
         elif k == MD_ROUND:
             rnd = int(v)
     return term, rnd
+
+
+def live_metadata(live) -> Tuple[Tuple[str, str], ...]:
+    return ((MD_LIVE, ",".join(str(int(r)) for r in live)),)
+
+
+def read_live(metadata: Optional[Iterable]):
+    for item in metadata or ():
+        if item[0] == MD_LIVE:
+            return [int(x) for x in item[1].split(",") if x != ""]
+    return None

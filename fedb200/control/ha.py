@@ -148,6 +148,16 @@ class BackupNode(proto.TrainerServicer):
     def SendModel(self, request, context):
         """Replica store (reference src/server.py:236-242) + which round/term it belongs to."""
         term, rnd = desc.read_fence(context.invocation_metadata())
+        if desc.is_descriptor(request.model):
+            # GPU plane: the replica itself was written into the backup rank's aux arena by K-REPL / K-AGG over
+            # NVLink; the RPC only tells us which round it belongs to
+            if term is not None:
+                self.term = max(self.term, term)
+            if rnd is not None:
+                self.next_round = rnd + 1
+            self._write_meta()
+            self.sink.write("replica", round=rnd, term=term, bytes=0, plane="peer")
+            return proto.SendModelReply(reply="success")
         raw = ckpt.decode_wire(request.model)
         path = os.path.join(self.cfg.state_dir, GLOBAL_MODEL_FILE)
         tmp = path + ".tmp"
@@ -178,7 +188,7 @@ class BackupNode(proto.TrainerServicer):
     # ------------------------------------------------------------------ role machine
     def _write_meta(self):
         import json
-        tmp = os.path.join(self.cfg.state_dir, "coordinator.json.tmp")
+        tmp = os.path.join(self.cfg.state_dir, f"coordinator.json.tmp.{os.getpid()}.{threading.get_ident()}")
         with open(tmp, "w") as f:
             json.dump({"term": self.term, "next_round": self.next_round,
                        "model": self.cfg.coordinator.model if self.cfg.coordinator else None}, f)

@@ -89,7 +89,10 @@ class WorkerServicer(proto.TrainerServicer):
             self.rejected += 1
             context.abort(grpc.StatusCode.ABORTED, "a local pass is already running")
         try:
-            st = self.trainer.train(1, request.rank, request.world)
+            if self.cfg.plane == "peer" and self.peer is not None:
+                st = self.peer.start_round(request.rank, request.world, desc.read_live(context.invocation_metadata()))
+            else:
+                st = self.trainer.train(1, request.rank, request.world)
             self.passes += 1
             self.sink.write("train_pass", address=self.cfg.address, rank=request.rank,
                             world=request.world, steps=st.steps, samples=st.samples,
@@ -113,10 +116,33 @@ class WorkerServicer(proto.TrainerServicer):
         with self._busy:                     # never swap weights under a running pass
             if desc.is_descriptor(request.model):
                 d = desc.decode(request.model)
-                if d.get("kind") != "global":
+                kind = d.get("kind")
+                if self.peer is None:
+                    context.abort(grpc.StatusCode.FAILED_PRECONDITION, "descriptor received but this worker has no GPU plane")
+                if kind == "reset":
+                    self.peer.reset(int(d["epoch"]))
+                    return proto.SendModelReply(reply="success")
+                if kind == "remap":
+                    self.peer.remap(int(d["rank"]))
+                    return proto.SendModelReply(reply="success")
+                if kind == "pull":
+                    self.peer.pull_global()
+                    return proto.SendModelReply(reply="success")
+                if kind == "dump":
+                    self.peer.dump_global(d["path"])
+                    return proto.SendModelReply(reply="success")
+                if kind != "global":
                     context.abort(grpc.StatusCode.INVALID_ARGUMENT, f"unexpected descriptor {d}")
-                if self.peer is not None:
-                    self.peer.wait_version(int(d.get("version", 0)))
+                try:
+                    ev = self.peer.finish_round(evaluate=self.cfg.eval_on_send)
+                except Exception as e:   # noqa: BLE001  (FedbError: the flag protocol gave up on a dead peer)
+                    self.sink.write("aggregation_failed", address=self.cfg.address, error=str(e), round=self.round)
+                    context.abort(grpc.StatusCode.ABORTED, f"aggregation failed: {e}")
+                if ev is not None:
+                    self.last_eval = ev
+                    self.sink.write("eval", address=self.cfg.address, loss=ev.mean_loss, acc=ev.accuracy,
+                                    samples=ev.samples, seconds=ev.seconds, term=self.term, round=self.round)
+                return proto.SendModelReply(reply="success")
             else:
                 state = ckpt.load_checkpoint(ckpt.decode_wire(request.model))
                 self.trainer.load_state_dict(state["net"])

@@ -31,7 +31,7 @@ class FedGroup:
     def __init__(self, trainer, rank: int, world: int, tag: str, *, use_multicast: bool = True,
                  nvls_reduce: bool = False, codec: str = "none", primary_rank: int = 0,
                  backup_rank: Optional[int] = None, repl_mode: str = "overlap", dist_barrier=None,
-                 timeout_ns: int = K.DEFAULT_TIMEOUT_NS):
+                 timeout_ns: int = K.DEFAULT_TIMEOUT_NS, persistent_server: bool = False, rejoin: bool = False):
         assert trainer.device.type == "cuda"
         self.trainer, self.rank, self.world = trainer, rank, world
         self.device = trainer.device.index or 0
@@ -43,7 +43,7 @@ class FedGroup:
         self.layout = PeerLayout.for_manifest(self.man, with_codec=True)
         torch.cuda.set_device(self.device)
         self.peers = PeerGroup(rank, world, self.device, self.layout, tag, use_multicast=use_multicast,
-                               barrier=dist_barrier)
+                               barrier=dist_barrier, persistent_server=persistent_server, rejoin=rejoin)
         # move the trainer's live state into the peer-visible allocation
         old = trainer.arena
         new = self.peers.me.client_arena(self.man)
@@ -136,6 +136,29 @@ class FedGroup:
         if st:
             raise _lib.FedbError(f"K-AGG flag wait failed on rank {self.rank}: status {st} "
                                  "(1 = a peer never arrived, 2 = a peer never finished, 3 = aborted)")
+
+    def reset_sync(self, epoch: int) -> None:
+        """After a failed round (a peer died inside the flag protocol): clear this rank's flags and jump to a
+        coordinator-chosen epoch that is larger than any epoch used so far, so that stale flag values written
+        by slow peers can never satisfy a future wait."""
+        torch.cuda.synchronize(self.device)
+        c = self.peers.me.ctrl()
+        c.zero_()
+        c[_lib.CTRL_OFF["epoch"] // 4] = int(epoch)
+        torch.cuda.synchronize(self.device)
+
+    def remap_peer(self, r: int) -> None:
+        """A restarted worker re-joined with a fresh allocation: map it (worker re-admission)."""
+        torch.cuda.synchronize(self.device)
+        self.peers.remap(r)
+
+    def pull_global(self) -> None:
+        """Newcomer side of re-admission: copy the server's global model out of the primary's peer memory into
+        this worker's arena (what the reference does by re-sending the checkpoint, src/server.py:92-97)."""
+        if self.peers.buffers[self.primary_rank].base == 0:
+            raise _lib.FedbError("the primary's memory is not mapped here")
+        K.broadcast(self.global_arena, [self.trainer.arena])
+        torch.cuda.synchronize(self.device)
 
     def abort(self) -> None:
         """Host-side abort: breaks every spin on this rank's control block."""

@@ -120,7 +120,8 @@ class PeerGroup:
     multicast alias of the whole layout (0 when NVLS is unavailable or disabled)."""
 
     def __init__(self, rank: int, world: int, device: int, layout: PeerLayout, tag: str,
-                 sock_dir: str = "/tmp", use_multicast: bool = True, timeout_ms: int = 120_000, barrier=None):
+                 sock_dir: str = "/tmp", use_multicast: bool = True, timeout_ms: int = 120_000, barrier=None,
+                 persistent_server: bool = False, rejoin: bool = False):
         L = _lib.lib()
         self.rank, self.world, self.device, self.layout = rank, world, device, layout
         self.local = _lib.Mem()
@@ -149,8 +150,14 @@ class PeerGroup:
         arr = (C.c_int * len(serve_fds))(*serve_fds)
         err: List[Optional[str]] = [None]
 
+        self._path = path
+        self._serve_arr = arr            # keep the ctypes array alive for a persistent server
+
         def serve():
-            rc = L.fedb_fd_serve(path(rank).encode(), arr, len(serve_fds), world - 1, timeout_ms)
+            # persistent mode (gRPC-driven workers): keep answering so that a restarted peer, or survivors
+            # re-mapping a restarted peer, can fetch this allocation at any time
+            n_clients, tmo = (1 << 30, 0x7FFFFFFF) if persistent_server else (world - 1, timeout_ms)
+            rc = L.fedb_fd_serve(path(rank).encode(), arr, len(serve_fds), n_clients, tmo)
             if rc != 0:
                 err[0] = L.fedb_last_error().decode()
 
@@ -159,24 +166,30 @@ class PeerGroup:
             th = threading.Thread(target=serve, daemon=True)
             th.start()
         mc_fd = -1
+        self.missing: List[int] = []
         for r in range(world):
             if r == rank:
                 continue
             n = 2 if r == 0 else 1
             got = (C.c_int * n)()
-            _lib.check(L.fedb_fd_fetch(path(r).encode(), got, n, timeout_ms), f"fd fetch from rank {r}")
+            rc = L.fedb_fd_fetch(path(r).encode(), got, n, 5000 if rejoin else timeout_ms)
+            if rc != 0:
+                if rejoin:               # a peer that is down right now: mapped later through remap()
+                    self.missing.append(r)
+                    continue
+                _lib.check(rc, f"fd fetch from rank {r}")
             m = _lib.Mem()
             _lib.check(L.fedb_mem_import_fd(got[0], self.alloc_bytes, device, C.byref(m)), f"import rank {r}")
             os.close(got[0])
             self.imported[r] = m
             if r == 0:
                 mc_fd = got[1]
-        if th is not None:
+        if th is not None and not persistent_server:
             th.join()
             if err[0]:
                 raise _lib.FedbError(err[0])
-        self.buffers = [PeerBuffer(int(self.local.ptr if r == rank else self.imported[r].ptr), layout, device, r)
-                        for r in range(world)]
+        self.buffers = [PeerBuffer(int(self.local.ptr if r == rank else (self.imported[r].ptr if self.imported[r] else 0)),
+                                   layout, device, r) for r in range(world)]
 
         # ---- multicast: every rank adds its device, barrier, every rank binds + maps
         self.multicast_error = mc_err
@@ -213,6 +226,27 @@ class PeerGroup:
     @property
     def me(self) -> PeerBuffer:
         return self.buffers[self.rank]
+
+    def remap(self, r: int, timeout_ms: int = 30_000) -> None:
+        """Peer ``r`` was restarted (new process, new allocation): fetch and map its memory again."""
+        L = _lib.lib()
+        n = 2 if r == 0 else 1
+        got = (C.c_int * n)()
+        _lib.check(L.fedb_fd_fetch(self._path(r).encode(), got, n, timeout_ms), f"fd fetch from restarted rank {r}")
+        m = _lib.Mem()
+        _lib.check(L.fedb_mem_import_fd(got[0], self.alloc_bytes, self.device, C.byref(m)), f"import rank {r}")
+        for fd in got:
+            try:
+                os.close(fd)
+            except OSError:
+                pass
+        old = self.imported[r]
+        self.imported[r] = m
+        self.buffers[r] = PeerBuffer(int(m.ptr), self.layout, self.device, r)
+        if old is not None:
+            L.fedb_mem_release(C.byref(old))
+        if r in self.missing:
+            self.missing.remove(r)
 
     def mc_client_f32_ptr(self) -> int:
         return self.mc_base + self.layout.off_client_f32 if self.mc_base else 0

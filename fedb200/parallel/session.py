@@ -75,3 +75,50 @@ class GpuFederation:
 
     def close(self):
         self.group.close()
+
+
+class PeerWorker:
+    """What ``WorkerServicer`` drives on the GPU plane: ``StartTrain`` -> ``start_round`` (local pass, then the
+    K-AGG launch is enqueued and overlaps the RPC round trip), ``SendModel`` -> ``finish_round`` (wait for the
+    aggregation, verify the flag protocol, evaluate).  gRPC handler threads differ per call, so every entry
+    point re-selects the device."""
+
+    def __init__(self, fed: GpuFederation):
+        self.fed = fed
+        self.name = f"rank{fed.rank}"
+        self.device = fed.trainer.device
+
+    def start_round(self, rank: int, world: int, live=None):
+        torch.cuda.set_device(self.device)
+        fed = self.fed
+        if live is not None:
+            fed.group.set_live(live)
+        batches = fed.trainer.shard(rank, world)
+        st = fed.engine.train_pass(batches, upload=True, sync=True)
+        fed.group.aggregate()
+        return st
+
+    def finish_round(self, evaluate: bool = True):
+        torch.cuda.set_device(self.device)
+        torch.cuda.current_stream(self.device).synchronize()
+        self.fed.group.check()                       # raises FedbError when a peer never showed up
+        return self.fed.engine.eval_pass(upload=True, sync=True) if evaluate else None
+
+    def reset(self, epoch: int) -> None:
+        torch.cuda.set_device(self.device)
+        self.fed.group.reset_sync(epoch)
+
+    def remap(self, r: int) -> None:
+        torch.cuda.set_device(self.device)
+        self.fed.group.remap_peer(r)
+
+    def pull_global(self) -> None:
+        torch.cuda.set_device(self.device)
+        self.fed.group.pull_global()
+
+    def dump_global(self, path: str) -> None:
+        """Writes the server's global model (primary's aux arena) as a reference-format checkpoint."""
+        from ..utils import checkpoint as ckpt
+        torch.cuda.set_device(self.device)
+        torch.cuda.synchronize(self.device)
+        ckpt.save_checkpoint(path, self.fed.group.global_arena.state_dict(to_cpu=True), acc=1, epoch=1)

@@ -1,0 +1,166 @@
+"""gRPC control plane + GPU data plane, end to end on one box with >= 2 GPUs:
+
+  coordinator (this process, no GPU context) --StartTrain/SendModel descriptors--> 2 worker processes
+  (``python -m fedb200.client --plane peer``), one per GPU, whose arenas are peer-mapped; FedAvg, broadcast and
+  the backup replica run as K-AGG/K-REPL kernels over NVLink.  Then: kill a worker mid-run (bounded flag wait ->
+  ABORTED -> reset -> live-only rounds), restart it with --rejoin (survivor re-maps its memory, newcomer pulls the
+  global model), and check the rounds continue with both.
+"""
+import os
+import signal
+import socket
+import subprocess
+import sys
+import tempfile
+import time
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+from fedb200.control.coordinator import Coordinator, CoordinatorConfig  # noqa: E402
+from fedb200.control.ha import BackupConfig, BackupNode  # noqa: E402
+from fedb200.utils import checkpoint as ckpt  # noqa: E402
+
+
+def free_port():
+    with socket.socket() as s:
+        s.bind(("127.0.0.1", 0))
+        return s.getsockname()[1]
+
+
+def wait_port(port, timeout=240):
+    end = time.time() + timeout
+    while time.time() < end:
+        try:
+            socket.create_connection(("127.0.0.1", port), timeout=0.5).close()
+            return True
+        except OSError:
+            time.sleep(0.3)
+    return False
+
+
+def spawn_worker(rank, port, tag, work, rejoin=False):
+    cmd = [sys.executable, "-m", "fedb200.client", "-a", f"127.0.0.1:{port}", "--plane", "peer", "--model", "LeNet",
+           "--device", f"cuda:{rank}", "--peer-rank", str(rank), "--peer-world", "2", "--peer-tag", tag,
+           "--dataset-size", "2048", "--test-size", "500", "--seed", str(10 + rank), "--agg-timeout", "4"]
+    if rejoin:
+        cmd.append("--rejoin")
+    log = open(os.path.join(work, f"worker{rank}{'-re' if rejoin else ''}.log"), "w")
+    env = dict(os.environ, PYTHONPATH=ROOT)
+    return subprocess.Popen(cmd, cwd=work, stdout=log, stderr=subprocess.STDOUT, env=env, start_new_session=True)
+
+
+def main():
+    work = tempfile.mkdtemp(prefix="fedb200-grpcgpu-")
+    tag = f"g{os.getpid()}"
+    ports = [free_port(), free_port()]
+    procs = [spawn_worker(r, ports[r], tag, work) for r in range(2)]
+    try:
+        assert all(wait_port(p) for p in ports), "workers did not come up"
+        bport = free_port()
+        ccfg = CoordinatorConfig(workers=tuple(f"127.0.0.1:{p}" for p in ports), model="LeNet", rounds=3,
+                                 state_dir=os.path.join(work, "Primary"), backup_target=f"127.0.0.1:{bport}",
+                                 plane="peer", checkpoint_every=1, membership_period_s=0.5, train_timeout_s=120,
+                                 send_timeout_s=120)
+        backup = BackupNode(BackupConfig(port=str(bport), watchdog_s=3600, state_dir=os.path.join(work, "Backup"),
+                                         coordinator=ccfg))
+        backup.start()
+        c = Coordinator(ccfg, term=1)
+        assert c.run() == 3
+        rounds = [r for r in c.sink.records if r["event"] == "round"]
+        assert all(r["uploads"] == 2 and r["plane"] == "peer" for r in rounds), rounds
+        assert all(r["bytes_up"] == 0 for r in rounds)                       # no weights in the RPC payloads
+        glob = ckpt.load_checkpoint(os.path.join(work, "Primary", "optimizedModel.pth"))
+        assert list(glob["net"].keys())[0] == "conv1.weight" and glob["acc"] == 1
+        assert backup.next_round == 3                                          # replica metadata followed
+        print("phase 1 ok: 3 descriptor rounds,", [round(r["total_s"], 3) for r in rounds])
+
+        # ---- kill worker 1: the survivor's flag wait is bounded, the round is dropped, the next ones are live-only
+        os.killpg(procs[1].pid, signal.SIGKILL)
+        procs[1].wait()
+        c.cfg.rounds = 6
+        done = c.run()
+        rounds = [r for r in c.sink.records if r["event"] == "round"]
+        assert done == 3 and rounds[-1]["uploads"] == 1, (done, rounds[-3:])
+        assert c.members.snapshot()[ccfg.workers[1]] is False
+        print("phase 2 ok: worker 1 killed, rounds continue with the survivor:", [r["uploads"] for r in rounds])
+
+        # ---- restart it with --rejoin: membership re-admits it (remap + pull), rounds use both again
+        procs[1] = spawn_worker(1, ports[1], tag, work, rejoin=True)
+        assert wait_port(ports[1])
+        end = time.time() + 60
+        while time.time() < end and not c.members.snapshot()[ccfg.workers[1]]:
+            time.sleep(0.2)
+        assert c.members.snapshot()[ccfg.workers[1]], "worker 1 was not re-admitted"
+        c.cfg.rounds = c.round + 2
+        done = c.run()
+        rounds = [r for r in c.sink.records if r["event"] == "round"]
+        assert done == 2 and rounds[-1]["uploads"] == 2, (done, rounds[-2:])
+        print("phase 3 ok: worker 1 re-admitted, uploads per round:", [r["uploads"] for r in rounds])
+        last_round = c.round
+        c.close()
+        backup.stop()
+
+        # ---- phase 4: primary failover on the GPU plane.  A primary PROCESS is killed by fault injection right
+        # after the workers trained (K-AGG launches in flight); the backup's watchdog promotes it, it resets the
+        # flag protocol, bumps the term and the rounds go on from the replicated round number.
+        bport2 = free_port()
+        pdir = os.path.join(work, "Primary2")
+        ccfg2 = CoordinatorConfig(workers=ccfg.workers, model="LeNet", rounds=10_000, state_dir=os.path.join(work, "Backup2"),
+                                  plane="peer", membership_period_s=0.5, train_timeout_s=120, send_timeout_s=120)
+        env = dict(os.environ, PYTHONPATH=ROOT, FEDB200_FAULTS="kill:after_train:800")
+        prim = subprocess.Popen([sys.executable, "-m", "fedb200.server", "--p", "y", "--plane", "peer", "--model", "LeNet",
+                                 "--workers", ",".join(ccfg.workers), "--rounds", "100000", "--backupPort", str(bport2),
+                                 "--backupAddress", "127.0.0.1", "--state-dir", pdir, "--ping-period", "0.2"],
+                                cwd=work, env=env, stdout=open(os.path.join(work, "primary2.log"), "w"),
+                                stderr=subprocess.STDOUT, start_new_session=True)
+        procs.append(prim)
+        # the backup (watchdog 1.5 s) starts once the primary is up and running rounds, like an operator would
+        import json
+        end = time.time() + 120
+        while time.time() < end:
+            try:
+                if json.load(open(os.path.join(pdir, "coordinator.json")))["next_round"] >= 1:
+                    break
+            except (OSError, ValueError, KeyError):
+                pass
+            time.sleep(0.05)
+        backup2 = BackupNode(BackupConfig(port=str(bport2), watchdog_s=1.5, state_dir=os.path.join(work, "Backup2"),
+                                          coordinator=ccfg2))
+        backup2.start()
+        prim.wait(timeout=120)
+        if prim.returncode != 137:
+            print(open(os.path.join(work, "primary2.log")).read()[-3000:])
+        assert prim.returncode == 137, f"primary should have been killed by the injected fault, rc={prim.returncode}"
+        t_kill = time.time()
+        end = time.time() + 30
+        while time.time() < end and backup2.role != "ACTING":
+            time.sleep(0.05)
+        assert backup2.role == "ACTING", "backup did not take over"
+        t_take = time.time() - t_kill
+        acting = backup2.acting
+        start = acting.round
+        end = time.time() + 60
+        while time.time() < end and acting.round < start + 3:
+            time.sleep(0.1)
+        assert acting.round >= start + 3, f"acting coordinator stuck at round {acting.round}"
+        assert acting.term >= 2 and start >= 100, (acting.term, start)
+        print(f"phase 4 ok: primary killed mid-round, backup took over {t_take:.2f}s later at round {start}, "
+              f"term {acting.term}, now at round {acting.round}")
+        backup2.stop()
+        print("GRPC_GPU_CHECK_OK")
+    finally:
+        for p in procs:
+            if p.poll() is None:
+                try:
+                    os.killpg(p.pid, signal.SIGKILL)
+                except ProcessLookupError:
+                    pass
+        for name in sorted(os.listdir(work)):
+            if name.endswith(".log"):
+                tail = open(os.path.join(work, name)).read()[-1500:]
+                if "Traceback" in tail or "Error" in tail:
+                    print(f"---- {name}\n{tail}")
+
+
+if __name__ == "__main__":
+    main()
