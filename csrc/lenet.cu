@@ -1,17 +1,18 @@
-// LeNet training step as four fused kernels (the minimum training slice).
+// LeNet training step in TWO kernels (the minimum training slice; K1,K7,K8,K9,K10,K13,K14).
 //
-//   A  features_fwd   one CTA per sample: u8 image -> normalise(+crop/flip) -> conv1+ReLU+pool ->
-//                     conv2+ReLU+pool, everything in shared memory; saves pooled maps + argmax
-//   B  classifier     one CTA per kS samples: fc1/fc2/fc3 forward, softmax-CE, backward through the
-//                     three linears down to d(flat); keeps dh1/dh2/dlogits for the weight gradients
-//   C  features_bwd   one CTA per sample: un-pool, conv2 wgrad + sparse dgrad, conv1 wgrad;
-//                     per-sample partial gradients go to scratch (deterministic, no atomics)
-//   D  update         one thread per parameter: fc weight gradients as batch reductions, conv
-//                     partial reduction, then the SGD update (K10) in the same kernel
+//   S  sample kernel   one CTA per sample, the WHOLE forward and backward of that sample in shared memory:
+//                      u8 image -> normalise (+crop/flip) -> conv1+ReLU+pool -> conv2+ReLU+pool -> fc1/fc2/fc3 ->
+//                      softmax-CE -> backward through the three linears (data path) -> un-pool -> conv2 wgrad +
+//                      sparse dgrad -> conv1 wgrad.  Leaves per-sample rows in scratch: conv partial gradients,
+//                      (flat, h1, h2) and (dh1, dh2, dlogits).  No cross-sample dependency, no atomics.
+//   U  update kernel   one thread per parameter: fc weight gradients as fixed-order batch reductions
+//                      dW = sum_s dout[s] (x) in[s], conv partial reduction, then the SGD update (K10) in place.
 //
-// All fp32 on CUDA cores: N_out is 6/16/10 and K is 75/150, far below a tcgen05 tile, and fp32
-// keeps the step bit-comparable with the reference's CPU run (src/models/lenet.py:5-23,
-// src/main.py:142-151).  Summation order over the batch is fixed, so a step is reproducible.
+// fp32 on CUDA cores on purpose: N_out is 6/16/10 and K is 75/150/400, far below a tcgen05 tile, and fp32 keeps
+// the step comparable bit-for-tolerance with the reference's CPU run (src/models/lenet.py:5-23,
+// src/main.py:142-151).  Every summation order is fixed, so a step is reproducible run to run.
+// Weight reads of the classifier come from L2 (192 KB fc1 matrix, read twice per sample); all loads of a phase
+// are issued before their first use so one phase costs about one memory latency, not one per element.
 #include "common.cuh"
 #include "../include/fedb200.h"
 #include "augment.cuh"
@@ -26,23 +27,18 @@ constexpr int H1 = 120, H2 = 84, NCLS = 10;
 constexpr int NW1 = C1 * 3 * 25, NW2 = C2 * C1 * 25;   // 450, 2400
 constexpr int CONV_PART = 2880;                // [w1 450 | b1 6 | w2 2400 | b2 16] padded
 constexpr int OFF_B1 = 450, OFF_W2 = 456, OFF_B2 = 2856;
-constexpr int kS = 4;                          // samples per classifier CTA
+constexpr int kThreads = 256;
 
 struct Workspace {
-  float* p1;        // [B][1176]
   float* flat;      // [B][400]
   float* h1;        // [B][120]
   float* h2;        // [B][84]
-  float* logits;    // [B][10]
   float* dlogits;   // [B][10]
   float* dh2;       // [B][84]
   float* dh1;       // [B][120]
-  float* dflat;     // [B][400]
   float* loss_rows; // [B]
   float* corr_rows; // [B]
   float* conv_part; // [B][2880]
-  uint8_t* idx1;    // [B][1176]
-  uint8_t* idx2;    // [B][400]
 };
 
 __host__ __device__ inline size_t align_up(size_t x, size_t a) { return (x + a - 1) / a * a; }
@@ -52,21 +48,16 @@ __host__ size_t carve(Workspace* w, void* base, int B) {
   auto take = [&](size_t bytes) { size_t o = off; off = align_up(off + bytes, 256); return o; };
   char* b = (char*)base;
 #define FEDB_TAKE_F(field, n) { size_t o = take(sizeof(float) * (size_t)(n)); if (w) w->field = (float*)(b + o); }
-  FEDB_TAKE_F(p1, (size_t)B * NP1)
   FEDB_TAKE_F(flat, (size_t)B * NFLAT)
   FEDB_TAKE_F(h1, (size_t)B * H1)
   FEDB_TAKE_F(h2, (size_t)B * H2)
-  FEDB_TAKE_F(logits, (size_t)B * NCLS)
   FEDB_TAKE_F(dlogits, (size_t)B * NCLS)
   FEDB_TAKE_F(dh2, (size_t)B * H2)
   FEDB_TAKE_F(dh1, (size_t)B * H1)
-  FEDB_TAKE_F(dflat, (size_t)B * NFLAT)
   FEDB_TAKE_F(loss_rows, (size_t)B)
   FEDB_TAKE_F(corr_rows, (size_t)B)
   FEDB_TAKE_F(conv_part, (size_t)B * CONV_PART)
 #undef FEDB_TAKE_F
-  { size_t o = take((size_t)B * NP1); if (w) w->idx1 = (uint8_t*)(b + o); }
-  { size_t o = take((size_t)B * NFLAT); if (w) w->idx2 = (uint8_t*)(b + o); }
   return off;
 }
 
@@ -74,7 +65,36 @@ struct Params {
   const float *w1, *b1, *w2, *b2, *fw1, *fb1, *fw2, *fb2, *fw3, *fb3;
 };
 
-// ------------------------------------------------------------------------------------ kernel A
+// shared-memory plan of the sample kernel (floats)
+struct Sm {
+  static constexpr int img = 0;                       // 3072
+  static constexpr int w1 = img + 3072;               // 452 (450 used)
+  static constexpr int b1 = w1 + 452;                 // 8
+  static constexpr int w2 = b1 + 8;                   // 2400
+  static constexpr int b2 = w2 + 2400;                // 16
+  static constexpr int p1 = b2 + 16;                  // 1176
+  static constexpr int flat = p1 + NP1;               // 400
+  static constexpr int h1 = flat + NFLAT;             // 120
+  static constexpr int h2 = h1 + H1;                  // 84
+  static constexpr int lg = h2 + H2;                  // 16
+  static constexpr int dlg = lg + 16;                 // 16
+  static constexpr int dh2 = dlg + 16;                // 84
+  static constexpr int dh1 = dh2 + H2;                // 120
+  static constexpr int dflat = dh1 + H1;              // 400
+  static constexpr int fwd_end = dflat + NFLAT;
+  // backward only
+  static constexpr int g2 = fwd_end;                  // 400
+  static constexpr int g1 = g2 + NFLAT;               // 1176
+  static constexpr int dp1 = g1 + NP1;                // 8 x 1176 (also the 8 x 400 partials of d(flat), and 2 x 120 of dh1)
+  static constexpr int half = dp1 + 8 * NP1;          // 900
+  static constexpr int pos2 = half + 2 * NW1;         // 400 ints
+  static constexpr int pos1 = pos2 + NFLAT;           // 1176 ints
+  static constexpr int idx1 = pos1 + NP1;             // 1176 bytes = 294 words
+  static constexpr int idx2 = idx1 + 296;             // 400 bytes = 100 words
+  static constexpr int total = idx2 + 100;
+};
+constexpr size_t kSmemBytes = sizeof(float) * (size_t)Sm::total;
+
 // conv (valid, 5x5) + ReLU + 2x2 max-pool for one output position and CO output channels,
 // input planes in shared memory.  Returns pooled values and the argmax slot (0..3).
 template <int CI, int CO_PER_THREAD, int IN_W>
@@ -124,34 +144,129 @@ __device__ __forceinline__ void conv5_relu_pool(const float* __restrict__ in, co
   }
 }
 
-template <bool kU8>
-__global__ void __launch_bounds__(256) features_fwd_kernel(const void* __restrict__ images, Params P, Workspace W,
-                                                          int B, int augment, unsigned long long seed,
-                                                          const unsigned long long* __restrict__ seed_dev) {
-  __shared__ float s_img[3 * 32 * 32];
-  __shared__ float s_w1[NW1], s_b1[C1], s_w2[NW2], s_b2[C2];
-  __shared__ float s_p1[NP1];
-  const int n = blockIdx.x, tid = threadIdx.x;
+__device__ __forceinline__ float4 ldg4(const float* p) { return __ldg(reinterpret_cast<const float4*>(p)); }
+__device__ __forceinline__ float dot4(float4 a, float4 b, float acc) {
+  acc = fmaf(a.x, b.x, acc);
+  acc = fmaf(a.y, b.y, acc);
+  acc = fmaf(a.z, b.z, acc);
+  return fmaf(a.w, b.w, acc);
+}
+
+// y[j] = act(b[j] + sum_k W[j][k] x[k]) for one sample: warp w owns rows w, w+8, ...; lanes own float4 slices of k.
+// ROWS rows are in flight at once (all their loads are issued before the first FMA).
+template <int K, int J, int ROWS, bool kRelu>
+__device__ __forceinline__ void matvec(const float* __restrict__ W, const float* __restrict__ bias,
+                                       const float* __restrict__ x_s, float* __restrict__ y_s, int warp, int lane) {
+  constexpr int K4 = K / 4;                       // K is a multiple of 4 for 400 / 120 / 84
+  constexpr int T = (K4 + 31) / 32;               // float4 slices per lane
+  float4 xv[T];
+#pragma unroll
+  for (int t = 0; t < T; ++t) {
+    const int k4 = lane + 32 * t;
+    xv[t] = k4 < K4 ? reinterpret_cast<const float4*>(x_s)[k4] : make_float4(0.f, 0.f, 0.f, 0.f);
+  }
+  for (int j0 = warp; j0 < J; j0 += 8 * ROWS) {
+    float4 wv[ROWS][T];
+#pragma unroll
+    for (int r = 0; r < ROWS; ++r) {
+      const int j = j0 + 8 * r;
+#pragma unroll
+      for (int t = 0; t < T; ++t) {
+        const int k4 = lane + 32 * t;
+        wv[r][t] = (j < J && k4 < K4) ? ldg4(W + (size_t)j * K + 4 * k4) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+    }
+#pragma unroll
+    for (int r = 0; r < ROWS; ++r) {
+      const int j = j0 + 8 * r;
+      float acc = 0.f;
+#pragma unroll
+      for (int t = 0; t < T; ++t) acc = dot4(wv[r][t], xv[t], acc);
+      acc = warp_sum(acc);
+      if (lane == 0 && j < J) {
+        const float v = acc + __ldg(bias + j);
+        y_s[j] = kRelu ? fmaxf(v, 0.f) : v;
+      }
+    }
+  }
+}
+
+template <bool kU8, bool kTrain>
+__global__ void __launch_bounds__(kThreads) lenet_sample_kernel(const void* __restrict__ images, Params P, Workspace W,
+                                                               const int64_t* __restrict__ labels, int B, int augment,
+                                                               unsigned long long seed,
+                                                               const unsigned long long* __restrict__ seed_dev,
+                                                               float* __restrict__ logits_out) {
+  extern __shared__ __align__(16) float sm[];
+  float* s_img = sm + Sm::img;
+  float* s_w1 = sm + Sm::w1;
+  float* s_b1 = sm + Sm::b1;
+  float* s_w2 = sm + Sm::w2;
+  float* s_b2 = sm + Sm::b2;
+  float* s_p1 = sm + Sm::p1;
+  float* s_flat = sm + Sm::flat;
+  float* s_h1 = sm + Sm::h1;
+  float* s_h2 = sm + Sm::h2;
+  float* s_lg = sm + Sm::lg;
+  float* s_dlg = sm + Sm::dlg;
+  uint8_t* s_idx1 = reinterpret_cast<uint8_t*>(sm + Sm::idx1);
+  uint8_t* s_idx2 = reinterpret_cast<uint8_t*>(sm + Sm::idx2);
+  const int n = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (n >= B) return;
 
-  if constexpr (kU8) {
-    const uint8_t* img = (const uint8_t*)images + (size_t)n * 3072;
-    const fedb::Crop cr = fedb::draw_crop(seed ^ (seed_dev ? *seed_dev : 0ull), (unsigned long long)n, augment);
-    for (int e = tid; e < 3072; e += 256) {
-      const int x = e & 31, y = (e >> 5) & 31, c = e >> 10;
-      s_img[e] = fedb::fetch_pixel(img, cr, c, y, x);
+  // ------------------------------------------------------------------ phase 0: stage image + conv weights
+  {
+    float4 w2v[3];
+#pragma unroll
+    for (int j = 0; j < 3; ++j) {
+      const int i4 = tid + 256 * j;
+      w2v[j] = i4 < NW2 / 4 ? ldg4(P.w2 + 4 * i4) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
-  } else {
-    const float4* img = (const float4*)((const float*)images + (size_t)n * 3072);
-    for (int e = tid; e < 768; e += 256) reinterpret_cast<float4*>(s_img)[e] = img[e];
+    float w1v[2];
+#pragma unroll
+    for (int j = 0; j < 2; ++j) {
+      const int i = tid + 256 * j;
+      w1v[j] = i < NW1 ? __ldg(P.w1 + i) : 0.f;
+    }
+    if constexpr (kU8) {
+      const uint8_t* img = (const uint8_t*)images + (size_t)n * 3072;
+      const fedb::Crop cr = fedb::draw_crop(seed ^ (seed_dev ? *seed_dev : 0ull), (unsigned long long)n, augment);
+      float px[12];
+#pragma unroll
+      for (int j = 0; j < 12; ++j) {                       // destination-centric: all 12 byte loads in flight
+        const int e = tid + 256 * j;
+        const int x = e & 31, y = (e >> 5) & 31, c = e >> 10;
+        const int sx = (cr.flip ? 31 - x : x) + cr.dx, sy = y + cr.dy;
+        const bool in = sx >= 0 && sx < 32 && sy >= 0 && sy < 32;
+        px[j] = in ? (float)__ldg(img + (sy * 32 + sx) * 3 + c) : 0.f;
+      }
+#pragma unroll
+      for (int j = 0; j < 12; ++j) {
+        const int c = (tid + 256 * j) >> 10;
+        const float mean = c == 0 ? 0.4914f : (c == 1 ? 0.4822f : 0.4465f);
+        const float stdv = c == 0 ? 0.2023f : (c == 1 ? 0.1994f : 0.2010f);
+        s_img[tid + 256 * j] = (px[j] / 255.f - mean) / stdv;
+      }
+    } else {
+      const float* img = (const float*)images + (size_t)n * 3072;
+      float4 v[3];
+#pragma unroll
+      for (int j = 0; j < 3; ++j) v[j] = ldg4(img + 4 * (tid + 256 * j));
+#pragma unroll
+      for (int j = 0; j < 3; ++j) reinterpret_cast<float4*>(s_img)[tid + 256 * j] = v[j];
+    }
+#pragma unroll
+    for (int j = 0; j < 3; ++j)
+      if (tid + 256 * j < NW2 / 4) reinterpret_cast<float4*>(s_w2)[tid + 256 * j] = w2v[j];
+#pragma unroll
+    for (int j = 0; j < 2; ++j)
+      if (tid + 256 * j < NW1) s_w1[tid + 256 * j] = w1v[j];
+    if (tid < C1) s_b1[tid] = __ldg(P.b1 + tid);
+    if (tid < C2) s_b2[tid] = __ldg(P.b2 + tid);
   }
-  for (int e = tid; e < NW1; e += 256) s_w1[e] = P.w1[e];
-  for (int e = tid; e < NW2; e += 256) s_w2[e] = P.w2[e];
-  if (tid < C1) s_b1[tid] = P.b1[tid];
-  if (tid < C2) s_b2[tid] = P.b2[tid];
   __syncthreads();
 
-  // conv1: 196 pooled positions x 6 channels; one position per thread, all channels
+  // ------------------------------------------------------------------ phase 1: conv1 + ReLU + pool
   if (tid < P1 * P1) {
     const int py = tid / P1, px = tid % P1;
     float o[C1];
@@ -160,13 +275,12 @@ __global__ void __launch_bounds__(256) features_fwd_kernel(const void* __restric
 #pragma unroll
     for (int c = 0; c < C1; ++c) {
       s_p1[c * 196 + tid] = o[c];
-      W.p1[(size_t)n * NP1 + c * 196 + tid] = o[c];
-      W.idx1[(size_t)n * NP1 + c * 196 + tid] = a[c];
+      s_idx1[c * 196 + tid] = a[c];
     }
   }
   __syncthreads();
 
-  // conv2: 25 pooled positions x 16 channels; (position, channel pair) per thread -> 200 threads
+  // ------------------------------------------------------------------ phase 2: conv2 + ReLU + pool
   if (tid < 200) {
     const int pos = tid % 25, cg = tid / 25;   // cg in 0..7 -> channels 2cg, 2cg+1
     const int py = pos / P2, px = pos % P2;
@@ -176,86 +290,23 @@ __global__ void __launch_bounds__(256) features_fwd_kernel(const void* __restric
 #pragma unroll
     for (int c = 0; c < 2; ++c) {
       const int f = (2 * cg + c) * 25 + pos;     // NCHW flatten order == fc1's input order
-      W.flat[(size_t)n * NFLAT + f] = o[c];
-      W.idx2[(size_t)n * NFLAT + f] = a[c];
+      s_flat[f] = o[c];
+      s_idx2[f] = a[c];
     }
   }
-}
-
-// ------------------------------------------------------------------------------------ kernel B
-// y[s][j] = act(b[j] + sum_k x[s][k] W[j][k]); one warp per output j, lanes over k.
-template <int K, int J, bool kRelu>
-__device__ __forceinline__ void fc_forward(const float* __restrict__ Wt, const float* __restrict__ bias,
-                                           const float* __restrict__ x_s /*[kS][K] smem*/,
-                                           float* __restrict__ y_s /*[kS][J] smem*/, int warp, int lane) {
-  for (int j = warp; j < J; j += 8) {
-    float acc[kS];
-#pragma unroll
-    for (int s = 0; s < kS; ++s) acc[s] = 0.f;
-    const float* wr = Wt + (size_t)j * K;
-    for (int k = lane; k < K; k += 32) {
-      const float wv = wr[k];
-#pragma unroll
-      for (int s = 0; s < kS; ++s) acc[s] = fmaf(wv, x_s[s * K + k], acc[s]);
-    }
-#pragma unroll
-    for (int s = 0; s < kS; ++s) acc[s] = warp_sum(acc[s]);
-    if (lane == 0) {
-      const float b = bias[j];
-#pragma unroll
-      for (int s = 0; s < kS; ++s) {
-        float v = acc[s] + b;
-        y_s[s * J + j] = kRelu ? fmaxf(v, 0.f) : v;
-      }
-    }
-  }
-}
-
-// dx[s][k] = (sum_j dy[s][j] W[j][k]) * (x[s][k] > 0 if masked); one thread per k
-template <int K, int J, bool kMask>
-__device__ __forceinline__ void fc_backward_data(const float* __restrict__ Wt, const float* __restrict__ dy_s,
-                                                 const float* __restrict__ x_s, float* __restrict__ dx_s, int tid) {
-  for (int k = tid; k < K; k += 256) {
-    float acc[kS];
-#pragma unroll
-    for (int s = 0; s < kS; ++s) acc[s] = 0.f;
-#pragma unroll 4
-    for (int j = 0; j < J; ++j) {
-      const float wv = Wt[(size_t)j * K + k];
-#pragma unroll
-      for (int s = 0; s < kS; ++s) acc[s] = fmaf(wv, dy_s[s * J + j], acc[s]);
-    }
-#pragma unroll
-    for (int s = 0; s < kS; ++s) dx_s[s * K + k] = (kMask && !(x_s[s * K + k] > 0.f)) ? 0.f : acc[s];
-  }
-}
-
-template <bool kTrain>
-__global__ void __launch_bounds__(256) classifier_kernel(Params P, Workspace W, const int64_t* __restrict__ labels,
-                                                        int B, float* __restrict__ logits_out) {
-  __shared__ float s_flat[kS * NFLAT];
-  __shared__ float s_h1[kS * H1], s_h2[kS * H2], s_lg[kS * NCLS];
-  __shared__ float s_dlg[kS * NCLS], s_dh2[kS * H2], s_dh1[kS * H1];
-  __shared__ float s_dflat[kS * NFLAT];
-  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int n0 = blockIdx.x * kS;
-  const int ns = min(kS, B - n0);
-  for (int e = tid; e < kS * NFLAT; e += 256) {
-    const int s = e / NFLAT;
-    s_flat[e] = s < ns ? W.flat[(size_t)n0 * NFLAT + e] : 0.f;
-  }
-  __syncthreads();
-  fc_forward<NFLAT, H1, true>(P.fw1, P.fb1, s_flat, s_h1, warp, lane);
-  __syncthreads();
-  fc_forward<H1, H2, true>(P.fw2, P.fb2, s_h1, s_h2, warp, lane);
-  __syncthreads();
-  fc_forward<H2, NCLS, false>(P.fw3, P.fb3, s_h2, s_lg, warp, lane);
   __syncthreads();
 
-  // softmax-CE per sample: warp s handles sample s
-  if (warp < ns) {
-    const int n = n0 + warp;
-    const float z = lane < NCLS ? s_lg[warp * NCLS + lane] : -INFINITY;
+  // ------------------------------------------------------------------ phase 3: classifier forward
+  matvec<NFLAT, H1, 5, true>(P.fw1, P.fb1, s_flat, s_h1, warp, lane);
+  __syncthreads();
+  matvec<H1, H2, 11, true>(P.fw2, P.fb2, s_h1, s_h2, warp, lane);
+  __syncthreads();
+  matvec<H2, NCLS, 2, false>(P.fw3, P.fb3, s_h2, s_lg, warp, lane);
+  __syncthreads();
+
+  // ------------------------------------------------------------------ phase 4: softmax cross-entropy
+  if (warp == 0) {
+    const float z = lane < NCLS ? s_lg[lane] : -INFINITY;
     float mx = z;
     int arg = lane < NCLS ? lane : 1 << 20;
 #pragma unroll
@@ -266,86 +317,119 @@ __global__ void __launch_bounds__(256) classifier_kernel(Params P, Workspace W, 
     }
     const float se = warp_sum(lane < NCLS ? expf(z - mx) : 0.f);
     const float lse = logf(se) + mx;
-    const int t = (int)labels[n];
+    const int t = labels != nullptr ? (int)labels[n] : 0;
     if (lane < NCLS) {
-      const float sm = expf(z - lse);
-      s_dlg[warp * NCLS + lane] = (sm - (lane == t ? 1.f : 0.f)) / (float)B;
+      const float smx = expf(z - lse);
+      s_dlg[lane] = (smx - (lane == t ? 1.f : 0.f)) / (float)B;
       if (logits_out) logits_out[(size_t)n * NCLS + lane] = z;
     }
     if (lane == 0) {
-      W.loss_rows[n] = lse - s_lg[warp * NCLS + t];
+      W.loss_rows[n] = lse - s_lg[t];
       W.corr_rows[n] = (arg == t) ? 1.f : 0.f;
     }
-  } else if (warp < kS && lane < NCLS) {
-    s_dlg[warp * NCLS + lane] = 0.f;
   }
   if constexpr (!kTrain) return;
   __syncthreads();
 
-  fc_backward_data<H2, NCLS, true>(P.fw3, s_dlg, s_h2, s_dh2, tid);
-  __syncthreads();
-  fc_backward_data<H1, H2, true>(P.fw2, s_dh2, s_h1, s_dh1, tid);
-  __syncthreads();
-  fc_backward_data<NFLAT, H1, false>(P.fw1, s_dh1, s_flat, s_dflat, tid);
-  __syncthreads();
+  float* s_dh2 = sm + Sm::dh2;
+  float* s_dh1 = sm + Sm::dh1;
+  float* s_dflat = sm + Sm::dflat;
+  float* s_g2 = sm + Sm::g2;
+  float* s_g1 = sm + Sm::g1;
+  float* s_dp1 = sm + Sm::dp1;
+  float* s_half = sm + Sm::half;
+  int* s_pos2 = reinterpret_cast<int*>(sm + Sm::pos2);
+  int* s_pos1 = reinterpret_cast<int*>(sm + Sm::pos1);
 
-  // publish what kernels C and D need
-  for (int e = tid; e < ns * NFLAT; e += 256) W.dflat[(size_t)n0 * NFLAT + e] = s_dflat[e];
-  for (int e = tid; e < ns * H1; e += 256) {
-    W.h1[(size_t)n0 * H1 + e] = s_h1[e];
-    W.dh1[(size_t)n0 * H1 + e] = s_dh1[e];
+  // ------------------------------------------------------------------ phase 5: classifier backward (data path)
+  // dh2[j] = relu'(h2[j]) * sum_c dlg[c] W3[c][j]
+  if (tid < H2) {
+    float wv[NCLS];
+#pragma unroll
+    for (int c = 0; c < NCLS; ++c) wv[c] = __ldg(P.fw3 + c * H2 + tid);
+    float acc = 0.f;
+#pragma unroll
+    for (int c = 0; c < NCLS; ++c) acc = fmaf(s_dlg[c], wv[c], acc);
+    s_dh2[tid] = s_h2[tid] > 0.f ? acc : 0.f;
   }
-  for (int e = tid; e < ns * H2; e += 256) {
-    W.h2[(size_t)n0 * H2 + e] = s_h2[e];
-    W.dh2[(size_t)n0 * H2 + e] = s_dh2[e];
+  __syncthreads();
+  // dh1[i] = relu'(h1[i]) * sum_j dh2[j] W2[j][i]; two threads per output (j halves), all 42 loads in flight
+  if (tid < 2 * H1) {
+    const int i = tid % H1, hf = tid / H1;
+    float wv[42];
+#pragma unroll
+    for (int j = 0; j < 42; ++j) wv[j] = __ldg(P.fw2 + (hf * 42 + j) * H1 + i);
+    float acc = 0.f;
+#pragma unroll
+    for (int j = 0; j < 42; ++j) acc = fmaf(s_dh2[hf * 42 + j], wv[j], acc);
+    s_dp1[tid] = acc;
   }
-  for (int e = tid; e < ns * NCLS; e += 256) W.dlogits[(size_t)n0 * NCLS + e] = s_dlg[e];
-}
-
-// ------------------------------------------------------------------------------------ kernel C
-template <bool kU8>
-__global__ void __launch_bounds__(256) features_bwd_kernel(const void* __restrict__ images, Params P, Workspace W,
-                                                          int B, int augment, unsigned long long seed,
-                                                          const unsigned long long* __restrict__ seed_dev) {
-  extern __shared__ __align__(16) float smem[];
-  float* s_img = smem;                    // 3072
-  float* s_p1 = s_img + 3072;             // 1176
-  float* s_w2 = s_p1 + NP1;               // 2400
-  float* s_g2 = s_w2 + NW2;               // 400  masked d(pool2)
-  float* s_g1 = s_g2 + NFLAT;             // 1176 masked d(pool1)
-  float* s_dp1 = s_g1 + NP1;              // 8 x 1176 private accumulators
-  int* s_pos2 = reinterpret_cast<int*>(s_dp1 + 8 * NP1);   // 400: argmax position y*10+x inside conv2 output
-  int* s_pos1 = s_pos2 + NFLAT;                            // 1176: y*28+x inside conv1 output
-  const int n = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  if (n >= B) return;
-
-  if constexpr (kU8) {
-    const uint8_t* img = (const uint8_t*)images + (size_t)n * 3072;
-    const fedb::Crop cr = fedb::draw_crop(seed ^ (seed_dev ? *seed_dev : 0ull), (unsigned long long)n, augment);
-    for (int e = tid; e < 3072; e += 256) {
-      const int x = e & 31, y = (e >> 5) & 31, c = e >> 10;
-      s_img[e] = fedb::fetch_pixel(img, cr, c, y, x);
+  __syncthreads();
+  if (tid < H1) s_dh1[tid] = s_h1[tid] > 0.f ? (s_dp1[tid] + s_dp1[H1 + tid]) : 0.f;
+  __syncthreads();
+  // dflat[k] = sum_j dh1[j] W1[j][k]: warp w owns rows [15w, 15w+15), lanes own float4 slices of k
+  {
+    float4 acc[4];
+#pragma unroll
+    for (int t = 0; t < 4; ++t) acc[t] = make_float4(0.f, 0.f, 0.f, 0.f);
+#pragma unroll 1
+    for (int jj = 0; jj < 15; jj += 5) {
+      float4 wv[5][4];
+#pragma unroll
+      for (int r = 0; r < 5; ++r) {
+        const int j = warp * 15 + jj + r;
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          const int k4 = lane + 32 * t;
+          wv[r][t] = k4 < NFLAT / 4 ? ldg4(P.fw1 + (size_t)j * NFLAT + 4 * k4) : make_float4(0.f, 0.f, 0.f, 0.f);
+        }
+      }
+#pragma unroll
+      for (int r = 0; r < 5; ++r) {
+        const float d = s_dh1[warp * 15 + jj + r];
+#pragma unroll
+        for (int t = 0; t < 4; ++t) {
+          acc[t].x = fmaf(d, wv[r][t].x, acc[t].x);
+          acc[t].y = fmaf(d, wv[r][t].y, acc[t].y);
+          acc[t].z = fmaf(d, wv[r][t].z, acc[t].z);
+          acc[t].w = fmaf(d, wv[r][t].w, acc[t].w);
+        }
+      }
     }
-  } else {
-    const float4* img = (const float4*)((const float*)images + (size_t)n * 3072);
-    for (int e = tid; e < 768; e += 256) reinterpret_cast<float4*>(s_img)[e] = img[e];
+#pragma unroll
+    for (int t = 0; t < 4; ++t) {
+      const int k4 = lane + 32 * t;
+      if (k4 < NFLAT / 4) reinterpret_cast<float4*>(s_dp1 + warp * NFLAT)[k4] = acc[t];
+    }
   }
-  for (int e = tid; e < NP1; e += 256) s_p1[e] = W.p1[(size_t)n * NP1 + e];
-  for (int e = tid; e < NW2; e += 256) s_w2[e] = P.w2[e];
-  for (int e = tid; e < 8 * NP1; e += 256) s_dp1[e] = 0.f;
-  for (int e = tid; e < NFLAT; e += 256) {
-    const float a = W.flat[(size_t)n * NFLAT + e];
-    const int k = W.idx2[(size_t)n * NFLAT + e];
+  __syncthreads();
+  for (int k = tid; k < NFLAT; k += kThreads) {
+    float d = 0.f;
+#pragma unroll
+    for (int w = 0; w < 8; ++w) d += s_dp1[w * NFLAT + k];
+    s_dflat[k] = d;
+  }
+  __syncthreads();
+
+  // publish the rows kernel U needs (coalesced)
+  for (int e = tid; e < NFLAT; e += kThreads) W.flat[(size_t)n * NFLAT + e] = s_flat[e];
+  if (tid < H1) { W.h1[(size_t)n * H1 + tid] = s_h1[tid]; W.dh1[(size_t)n * H1 + tid] = s_dh1[tid]; }
+  if (tid < H2) { W.h2[(size_t)n * H2 + tid] = s_h2[tid]; W.dh2[(size_t)n * H2 + tid] = s_dh2[tid]; }
+  if (tid < NCLS) W.dlogits[(size_t)n * NCLS + tid] = s_dlg[tid];
+
+  // ------------------------------------------------------------------ phase 6: feature extractor backward
+  for (int e = tid; e < 8 * NP1; e += kThreads) s_dp1[e] = 0.f;
+  for (int e = tid; e < NFLAT; e += kThreads) {
+    const int k = s_idx2[e];
     const int pos = e % 25, py = pos / 5, px = pos % 5;
-    s_g2[e] = a > 0.f ? W.dflat[(size_t)n * NFLAT + e] : 0.f;
+    s_g2[e] = s_flat[e] > 0.f ? s_dflat[e] : 0.f;
     s_pos2[e] = (2 * py + (k >> 1)) * 10 + (2 * px + (k & 1));
   }
   __syncthreads();
 
   float* part = W.conv_part + (size_t)n * CONV_PART;
-
   // conv2 weight gradient: dW2[co][ci][r][s] = sum_pos g2[co][pos] * p1[ci][y+r][x+s]
-  for (int e = tid; e < NW2; e += 256) {
+  for (int e = tid; e < NW2; e += kThreads) {
     const int s = e % 5, r = (e / 5) % 5, ci = (e / 25) % C1, co = e / 150;
     const float* src = s_p1 + ci * 196 + r * 14 + s;
     float acc = 0.f;
@@ -361,15 +445,14 @@ __global__ void __launch_bounds__(256) features_bwd_kernel(const void* __restric
     for (int pos = 0; pos < 25; ++pos) acc += s_g2[tid * 25 + pos];
     part[OFF_B2 + tid] = acc;
   }
-
-  // conv2 data gradient, sparse scatter: each non-zero of d(conv2 out) touches a 5x5 patch of every
-  // input channel.  Warp w owns non-zeros w, w+8, ... and its own accumulator copy; lanes are taps.
+  // conv2 data gradient, sparse scatter: each non-zero of d(conv2 out) touches a 5x5 patch of every input channel.
+  // Warp w owns non-zeros w, w+8, ... and its own accumulator copy; lanes are the 25 taps.
   {
     float* acc = s_dp1 + warp * NP1;
     const int r = lane / 5, s = lane % 5;
     for (int e = warp; e < NFLAT; e += 8) {
       const float g = s_g2[e];
-      if (g != 0.f && lane < 25) {           // warp-uniform test on g, lane test for the 25 taps
+      if (g != 0.f && lane < 25) {
         const int co = e / 25, q = s_pos2[e];
         const int base = ((q / 10) + r) * 14 + (q % 10) + s;
 #pragma unroll
@@ -380,26 +463,23 @@ __global__ void __launch_bounds__(256) features_bwd_kernel(const void* __restric
     }
   }
   __syncthreads();
-  for (int e = tid; e < NP1; e += 256) {
+  for (int e = tid; e < NP1; e += kThreads) {
     float d = 0.f;
 #pragma unroll
     for (int w = 0; w < 8; ++w) d += s_dp1[w * NP1 + e];
-    const int k = W.idx1[(size_t)n * NP1 + e];
+    const int k = s_idx1[e];
     const int pos = e % 196, py = pos / 14, px = pos % 14;
     s_g1[e] = s_p1[e] > 0.f ? d : 0.f;
     s_pos1[e] = (2 * py + (k >> 1)) * 28 + (2 * px + (k & 1));
   }
   __syncthreads();
-
-  // conv1 weight gradient: dW1[co][ci][r][s] = sum_pos g1[co][pos] * img[ci][y+r][x+s]; 450 outputs,
-  // each split in two halves of the 196 positions so that all 256 threads have work
-  __shared__ float s_half[2 * NW1];
-  for (int e = tid; e < 2 * NW1; e += 256) {
-    const int half = e / NW1, o = e % NW1;
+  // conv1 weight gradient: 450 outputs, each split in two halves of the 196 positions so all threads have work
+  for (int e = tid; e < 2 * NW1; e += kThreads) {
+    const int hf = e / NW1, o = e % NW1;
     const int s = o % 5, r = (o / 5) % 5, ci = (o / 25) % 3, co = o / 75;
     const float* src = s_img + ci * 1024 + r * 32 + s;
     float acc = 0.f;
-    const int lo = half * 98;
+    const int lo = hf * 98;
 #pragma unroll 7
     for (int pos = lo; pos < lo + 98; ++pos) {
       const int q = s_pos1[co * 196 + pos];
@@ -408,7 +488,7 @@ __global__ void __launch_bounds__(256) features_bwd_kernel(const void* __restric
     s_half[e] = acc;
   }
   __syncthreads();
-  for (int o = tid; o < NW1; o += 256) part[o] = s_half[o] + s_half[NW1 + o];
+  for (int o = tid; o < NW1; o += kThreads) part[o] = s_half[o] + s_half[NW1 + o];
   if (tid < C1) {
     float acc = 0.f;
     for (int pos = 0; pos < 196; ++pos) acc += s_g1[tid * 196 + pos];
@@ -416,9 +496,7 @@ __global__ void __launch_bounds__(256) features_bwd_kernel(const void* __restric
   }
 }
 
-constexpr size_t kBwdSmemBytes = sizeof(float) * (3072 + NP1 + NW2 + NFLAT + NP1 + 8 * NP1) + sizeof(int) * (NFLAT + NP1);
-
-// ------------------------------------------------------------------------------------ kernel D
+// ------------------------------------------------------------------------------------ kernel U
 struct UpdateArgs {
   float* param;
   float* momentum;
@@ -465,11 +543,11 @@ __global__ void __launch_bounds__(256) update_kernel(UpdateArgs U, Workspace W) 
     else if (i < E4) { const int e = i - E3; J = NCLS; K = H2; j = e / H2; k = e % H2; dout = W.dlogits; in = W.h2; dst = U.off[8] + e; }
     else             { J = NCLS; K = 0; j = i - E4; k = 0; dout = W.dlogits; in = nullptr; is_bias = true; dst = U.off[9] + j; }
     if (is_bias) {
-#pragma unroll 8
-      for (int s = 0; s < B; ++s) g += dout[(size_t)s * J + j];
+#pragma unroll 16
+      for (int s = 0; s < B; ++s) g += __ldg(dout + (size_t)s * J + j);
     } else {
-#pragma unroll 8
-      for (int s = 0; s < B; ++s) g = fmaf(dout[(size_t)s * J + j], in[(size_t)s * K + k], g);
+#pragma unroll 16
+      for (int s = 0; s < B; ++s) g = fmaf(__ldg(dout + (size_t)s * J + j), __ldg(in + (size_t)s * K + k), g);
     }
   } else {
     int c;
@@ -477,8 +555,8 @@ __global__ void __launch_bounds__(256) update_kernel(UpdateArgs U, Workspace W) 
     else if (i < E7) { c = OFF_B1 + (i - E6); dst = U.off[1] + (i - E6); }
     else if (i < E8) { c = OFF_W2 + (i - E7); dst = U.off[2] + (i - E7); }
     else             { c = OFF_B2 + (i - E8); dst = U.off[3] + (i - E8); }
-#pragma unroll 8
-    for (int s = 0; s < B; ++s) g += W.conv_part[(size_t)s * CONV_PART + c];
+#pragma unroll 16
+    for (int s = 0; s < B; ++s) g += __ldg(W.conv_part + (size_t)s * CONV_PART + c);
   }
 
   if constexpr (kApply) {
@@ -520,19 +598,28 @@ Params make_params(const fedb_lenet_t* net) {
   return P;
 }
 
-int ensure_bwd_smem() {
-  static bool done[2] = {false, false};
-  if (!done[0]) {
-    FEDB_CHECK(cudaFuncSetAttribute(features_bwd_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)kBwdSmemBytes));
-    FEDB_CHECK(cudaFuncSetAttribute(features_bwd_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize,
-                                    (int)kBwdSmemBytes));
-    done[0] = true;
+int ensure_smem() {
+  static bool done = false;
+  if (!done) {
+    FEDB_CHECK(cudaFuncSetAttribute(lenet_sample_kernel<true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    FEDB_CHECK(cudaFuncSetAttribute(lenet_sample_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    FEDB_CHECK(cudaFuncSetAttribute(lenet_sample_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    FEDB_CHECK(cudaFuncSetAttribute(lenet_sample_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    done = true;
   }
   return 0;
 }
 
+int check_offsets(const fedb_lenet_t* net) {
+  for (int i = 0; i < 10; ++i)
+    FEDB_REQUIRE(net->off[i] % 4 == 0, "fedb_lenet: parameter offsets must be multiples of 4 elements (16-byte loads)");
+  FEDB_REQUIRE(((uintptr_t)net->param & 15) == 0, "fedb_lenet: arena must be 16-byte aligned");
+  return 0;
+}
+
 constexpr int kNumParams = 62006;
+constexpr size_t kFwdSmemBytes = sizeof(float) * (size_t)Sm::fwd_end + 0;   // eval uses the forward part only...
+// ...but idx1/idx2 live at the end of the plan, so the full plan is always requested (89 KB, 2 CTAs per SM).
 
 }  // namespace
 
@@ -541,14 +628,14 @@ extern "C" size_t fedb_lenet_workspace_bytes(int B) { return carve(nullptr, null
 extern "C" int fedb_lenet_train_step(const fedb_lenet_t* net, const uint8_t* images_u8, const int64_t* labels, int B,
                                      void* workspace, float* stats, uint64_t step_seed, void* stream) {
   FEDB_REQUIRE(net && images_u8 && labels && workspace && B > 0, "fedb_lenet_train_step: bad arguments");
-  if (int rc = ensure_bwd_smem()) return rc;
+  if (int rc = ensure_smem()) return rc;
+  if (int rc = check_offsets(net)) return rc;
   Workspace W;
   carve(&W, workspace, B);
   const Params P = make_params(net);
   cudaStream_t s = (cudaStream_t)stream;
-  features_fwd_kernel<true><<<B, 256, 0, s>>>(images_u8, P, W, B, net->augment, step_seed, (const unsigned long long*)net->seed_dev);
-  classifier_kernel<true><<<fedb_ceil_div(B, kS), 256, 0, s>>>(P, W, labels, B, nullptr);
-  features_bwd_kernel<true><<<B, 256, kBwdSmemBytes, s>>>(images_u8, P, W, B, net->augment, step_seed, (const unsigned long long*)net->seed_dev);
+  lenet_sample_kernel<true, true><<<B, kThreads, kSmemBytes, s>>>(images_u8, P, W, labels, B, net->augment, step_seed,
+                                                                  (const unsigned long long*)net->seed_dev, nullptr);
   UpdateArgs U;
   U.param = net->param; U.momentum = net->momentum; U.dparam = nullptr;
   for (int i = 0; i < 10; ++i) U.off[i] = net->off[i];
@@ -561,12 +648,13 @@ extern "C" int fedb_lenet_train_step(const fedb_lenet_t* net, const uint8_t* ima
 extern "C" int fedb_lenet_eval(const fedb_lenet_t* net, const uint8_t* images_u8, const int64_t* labels, int B,
                                void* workspace, float* stats, void* stream) {
   FEDB_REQUIRE(net && images_u8 && labels && workspace && B > 0, "fedb_lenet_eval: bad arguments");
+  if (int rc = ensure_smem()) return rc;
+  if (int rc = check_offsets(net)) return rc;
   Workspace W;
   carve(&W, workspace, B);
   const Params P = make_params(net);
   cudaStream_t s = (cudaStream_t)stream;
-  features_fwd_kernel<true><<<B, 256, 0, s>>>(images_u8, P, W, B, 0, 0ull, nullptr);
-  classifier_kernel<false><<<fedb_ceil_div(B, kS), 256, 0, s>>>(P, W, labels, B, nullptr);
+  lenet_sample_kernel<true, false><<<B, kThreads, kSmemBytes, s>>>(images_u8, P, W, labels, B, 0, 0ull, nullptr, nullptr);
   if (stats) stats_kernel<<<1, 256, 0, s>>>(W, B, stats);
   FEDB_LAUNCH_OK();
   return 0;
@@ -575,15 +663,17 @@ extern "C" int fedb_lenet_eval(const fedb_lenet_t* net, const uint8_t* images_u8
 extern "C" int fedb_lenet_forward(const fedb_lenet_t* net, const uint8_t* images_u8, const float* images_f32, int B,
                                   void* workspace, float* logits, void* stream) {
   FEDB_REQUIRE(net && (images_u8 || images_f32) && workspace && logits && B > 0, "fedb_lenet_forward: bad arguments");
+  if (int rc = ensure_smem()) return rc;
+  if (int rc = check_offsets(net)) return rc;
   Workspace W;
   carve(&W, workspace, B);
   const Params P = make_params(net);
   cudaStream_t s = (cudaStream_t)stream;
-  // labels are only needed for the loss rows; point them at a zeroed scratch (dlogits area reused as int64 zeros)
-  FEDB_CHECK(cudaMemsetAsync(W.dflat, 0, sizeof(int64_t) * (size_t)B, s));
-  if (images_u8) features_fwd_kernel<true><<<B, 256, 0, s>>>(images_u8, P, W, B, net->augment, net->seed, nullptr);
-  else features_fwd_kernel<false><<<B, 256, 0, s>>>(images_f32, P, W, B, 0, 0ull, nullptr);
-  classifier_kernel<false><<<fedb_ceil_div(B, kS), 256, 0, s>>>(P, W, (const int64_t*)W.dflat, B, logits);
+  if (images_u8)
+    lenet_sample_kernel<true, false><<<B, kThreads, kSmemBytes, s>>>(images_u8, P, W, nullptr, B, net->augment, net->seed,
+                                                                     nullptr, logits);
+  else
+    lenet_sample_kernel<false, false><<<B, kThreads, kSmemBytes, s>>>(images_f32, P, W, nullptr, B, 0, 0ull, nullptr, logits);
   FEDB_LAUNCH_OK();
   return 0;
 }
@@ -591,14 +681,13 @@ extern "C" int fedb_lenet_forward(const fedb_lenet_t* net, const uint8_t* images
 extern "C" int fedb_lenet_grad(const fedb_lenet_t* net, const float* images_f32, const int64_t* labels, int B,
                                void* workspace, float* dparam, float* loss_out, void* stream) {
   FEDB_REQUIRE(net && images_f32 && labels && workspace && dparam && B > 0, "fedb_lenet_grad: bad arguments");
-  if (int rc = ensure_bwd_smem()) return rc;
+  if (int rc = ensure_smem()) return rc;
+  if (int rc = check_offsets(net)) return rc;
   Workspace W;
   carve(&W, workspace, B);
   const Params P = make_params(net);
   cudaStream_t s = (cudaStream_t)stream;
-  features_fwd_kernel<false><<<B, 256, 0, s>>>(images_f32, P, W, B, 0, 0ull, nullptr);
-  classifier_kernel<true><<<fedb_ceil_div(B, kS), 256, 0, s>>>(P, W, labels, B, nullptr);
-  features_bwd_kernel<false><<<B, 256, kBwdSmemBytes, s>>>(images_f32, P, W, B, 0, 0ull, nullptr);
+  lenet_sample_kernel<false, true><<<B, kThreads, kSmemBytes, s>>>(images_f32, P, W, labels, B, 0, 0ull, nullptr, nullptr);
   UpdateArgs U;
   U.param = net->param; U.momentum = net->momentum; U.dparam = dparam;
   for (int i = 0; i < 10; ++i) U.off[i] = net->off[i];

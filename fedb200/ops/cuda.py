@@ -240,7 +240,7 @@ class LeNetPlan:
         check(lib().fedb_lenet_train_step(C.byref(self.desc), images_u8.data_ptr(), labels.data_ptr(), B,
                                           self.workspace.data_ptr(), self.stats.data_ptr(), step_seed,
                                           current_stream()), "fedb_lenet_train_step")
-        _lib.count_launch(4)
+        _lib.count_launch(2)
 
     def _eval_ws(self, B: int) -> torch.Tensor:
         if B > self.eval_batch_cap:
@@ -254,7 +254,7 @@ class LeNetPlan:
         check(lib().fedb_lenet_eval(C.byref(self.desc), images_u8.data_ptr(), labels.data_ptr(), B,
                                     self._eval_ws(B).data_ptr(), ptr(self.stats if stats is None else stats),
                                     current_stream()), "fedb_lenet_eval")
-        _lib.count_launch(3)
+        _lib.count_launch(2)
 
     def forward(self, images: torch.Tensor) -> torch.Tensor:
         B = images.shape[0]
@@ -263,7 +263,7 @@ class LeNetPlan:
         check(lib().fedb_lenet_forward(C.byref(self.desc), images.data_ptr() if u8 else 0,
                                        0 if u8 else images.contiguous().data_ptr(), B, self._eval_ws(B).data_ptr(),
                                        logits.data_ptr(), current_stream()), "fedb_lenet_forward")
-        _lib.count_launch(2)
+        _lib.count_launch(1)
         return logits
 
     def grad(self, images_f32: torch.Tensor, labels: torch.Tensor):
@@ -273,7 +273,7 @@ class LeNetPlan:
         check(lib().fedb_lenet_grad(C.byref(self.desc), images_f32.contiguous().data_ptr(), labels.data_ptr(), B,
                                     self._eval_ws(B).data_ptr(), dparam.data_ptr(), loss.data_ptr(),
                                     current_stream()), "fedb_lenet_grad")
-        _lib.count_launch(4)
+        _lib.count_launch(2)
         return dparam, loss[0]
 
 

@@ -141,7 +141,7 @@ class CudaEngine:
             return self.read_stats() if sync else None
 
     def _launches_per_pass(self, sh) -> int:
-        return (4 if self.is_lenet else 0) * len(sh["sizes"])
+        return (2 if self.is_lenet else 0) * len(sh["sizes"])
 
     def read_stats(self, which: str = "train"):
         """One D2H read per pass: loss, correct, samples, steps."""
@@ -186,7 +186,7 @@ class CudaEngine:
             if self.is_lenet:
                 if self.cfg.use_cuda_graph and self._eval_graph is not None:
                     self._eval_graph.replay()
-                    _lib.count_launch(3 * ((n + chunk - 1) // chunk))
+                    _lib.count_launch(2 * ((n + chunk - 1) // chunk))
                 else:
                     def issue():
                         for lo in range(0, n, chunk):
