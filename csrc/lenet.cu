@@ -27,7 +27,8 @@ constexpr int H1 = 120, H2 = 84, NCLS = 10;
 constexpr int NW1 = C1 * 3 * 25, NW2 = C2 * C1 * 25;   // 450, 2400
 constexpr int CONV_PART = 2880;                // [w1 450 | b1 6 | w2 2400 | b2 16] padded
 constexpr int OFF_B1 = 450, OFF_W2 = 456, OFF_B2 = 2856;
-constexpr int kThreads = 256;
+constexpr int kThreads = 512;          // sample kernel: 16 warps per sample keep the issue slots fed
+constexpr int kWarps = kThreads / 32;
 
 struct Workspace {
   float* flat;      // [B][400]
@@ -86,8 +87,8 @@ struct Sm {
   static constexpr int g2 = fwd_end;                  // 400
   static constexpr int g1 = g2 + NFLAT;               // 1176
   static constexpr int dp1 = g1 + NP1;                // 8 x 1176 (also the 8 x 400 partials of d(flat), and 2 x 120 of dh1)
-  static constexpr int half = dp1 + 8 * NP1;          // 900
-  static constexpr int pos2 = half + 2 * NW1;         // 400 ints
+  static constexpr int half = dp1 + 8 * NP1;          // 4 x 450
+  static constexpr int pos2 = half + 4 * NW1;         // 400 ints
   static constexpr int pos1 = pos2 + NFLAT;           // 1176 ints
   static constexpr int idx1 = pos1 + NP1;             // 1176 bytes = 294 words
   static constexpr int idx2 = idx1 + 296;             // 400 bytes = 100 words
@@ -152,7 +153,7 @@ __device__ __forceinline__ float dot4(float4 a, float4 b, float acc) {
   return fmaf(a.w, b.w, acc);
 }
 
-// y[j] = act(b[j] + sum_k W[j][k] x[k]) for one sample: warp w owns rows w, w+8, ...; lanes own float4 slices of k.
+// y[j] = act(b[j] + sum_k W[j][k] x[k]) for one sample: warp w owns rows w, w+kWarps, ...; lanes own float4 slices of k.
 // ROWS rows are in flight at once (all their loads are issued before the first FMA).
 template <int K, int J, int ROWS, bool kRelu>
 __device__ __forceinline__ void matvec(const float* __restrict__ W, const float* __restrict__ bias,
@@ -165,11 +166,11 @@ __device__ __forceinline__ void matvec(const float* __restrict__ W, const float*
     const int k4 = lane + 32 * t;
     xv[t] = k4 < K4 ? reinterpret_cast<const float4*>(x_s)[k4] : make_float4(0.f, 0.f, 0.f, 0.f);
   }
-  for (int j0 = warp; j0 < J; j0 += 8 * ROWS) {
+  for (int j0 = warp; j0 < J; j0 += kWarps * ROWS) {
     float4 wv[ROWS][T];
 #pragma unroll
     for (int r = 0; r < ROWS; ++r) {
-      const int j = j0 + 8 * r;
+      const int j = j0 + kWarps * r;
 #pragma unroll
       for (int t = 0; t < T; ++t) {
         const int k4 = lane + 32 * t;
@@ -178,7 +179,7 @@ __device__ __forceinline__ void matvec(const float* __restrict__ W, const float*
     }
 #pragma unroll
     for (int r = 0; r < ROWS; ++r) {
-      const int j = j0 + 8 * r;
+      const int j = j0 + kWarps * r;
       float acc = 0.f;
 #pragma unroll
       for (int t = 0; t < T; ++t) acc = dot4(wv[r][t], xv[t], acc);
@@ -192,7 +193,7 @@ __device__ __forceinline__ void matvec(const float* __restrict__ W, const float*
 }
 
 template <bool kU8, bool kTrain>
-__global__ void __launch_bounds__(kThreads) lenet_sample_kernel(const void* __restrict__ images, Params P, Workspace W,
+__global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* __restrict__ images, Params P, Workspace W,
                                                                const int64_t* __restrict__ labels, int B, int augment,
                                                                unsigned long long seed,
                                                                const unsigned long long* __restrict__ seed_dev,
@@ -216,92 +217,85 @@ __global__ void __launch_bounds__(kThreads) lenet_sample_kernel(const void* __re
 
   // ------------------------------------------------------------------ phase 0: stage image + conv weights
   {
-    float4 w2v[3];
+    constexpr int NW2V = (NW2 / 4 + kThreads - 1) / kThreads;     // float4 loads of conv2.weight per thread
+    constexpr int NPX = 3072 / kThreads;                           // pixels per thread
+    float4 w2v[NW2V];
 #pragma unroll
-    for (int j = 0; j < 3; ++j) {
-      const int i4 = tid + 256 * j;
+    for (int j = 0; j < NW2V; ++j) {
+      const int i4 = tid + kThreads * j;
       w2v[j] = i4 < NW2 / 4 ? ldg4(P.w2 + 4 * i4) : make_float4(0.f, 0.f, 0.f, 0.f);
     }
-    float w1v[2];
-#pragma unroll
-    for (int j = 0; j < 2; ++j) {
-      const int i = tid + 256 * j;
-      w1v[j] = i < NW1 ? __ldg(P.w1 + i) : 0.f;
-    }
+    const float w1v = tid < NW1 ? __ldg(P.w1 + tid) : 0.f;
     if constexpr (kU8) {
       const uint8_t* img = (const uint8_t*)images + (size_t)n * 3072;
       const fedb::Crop cr = fedb::draw_crop(seed ^ (seed_dev ? *seed_dev : 0ull), (unsigned long long)n, augment);
-      float px[12];
+      float px[NPX];
 #pragma unroll
-      for (int j = 0; j < 12; ++j) {                       // destination-centric: all 12 byte loads in flight
-        const int e = tid + 256 * j;
+      for (int j = 0; j < NPX; ++j) {                      // destination-centric: all byte loads in flight
+        const int e = tid + kThreads * j;
         const int x = e & 31, y = (e >> 5) & 31, c = e >> 10;
         const int sx = (cr.flip ? 31 - x : x) + cr.dx, sy = y + cr.dy;
         const bool in = sx >= 0 && sx < 32 && sy >= 0 && sy < 32;
         px[j] = in ? (float)__ldg(img + (sy * 32 + sx) * 3 + c) : 0.f;
       }
 #pragma unroll
-      for (int j = 0; j < 12; ++j) {
-        const int c = (tid + 256 * j) >> 10;
+      for (int j = 0; j < NPX; ++j) {
+        const int c = (tid + kThreads * j) >> 10;
         const float mean = c == 0 ? 0.4914f : (c == 1 ? 0.4822f : 0.4465f);
         const float stdv = c == 0 ? 0.2023f : (c == 1 ? 0.1994f : 0.2010f);
-        s_img[tid + 256 * j] = (px[j] / 255.f - mean) / stdv;
+        s_img[tid + kThreads * j] = (px[j] / 255.f - mean) / stdv;
       }
     } else {
       const float* img = (const float*)images + (size_t)n * 3072;
-      float4 v[3];
+      float4 v[2];
 #pragma unroll
-      for (int j = 0; j < 3; ++j) v[j] = ldg4(img + 4 * (tid + 256 * j));
+      for (int j = 0; j < 2; ++j) v[j] = tid + kThreads * j < 768 ? ldg4(img + 4 * (tid + kThreads * j)) : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-      for (int j = 0; j < 3; ++j) reinterpret_cast<float4*>(s_img)[tid + 256 * j] = v[j];
+      for (int j = 0; j < 2; ++j)
+        if (tid + kThreads * j < 768) reinterpret_cast<float4*>(s_img)[tid + kThreads * j] = v[j];
     }
 #pragma unroll
-    for (int j = 0; j < 3; ++j)
-      if (tid + 256 * j < NW2 / 4) reinterpret_cast<float4*>(s_w2)[tid + 256 * j] = w2v[j];
-#pragma unroll
-    for (int j = 0; j < 2; ++j)
-      if (tid + 256 * j < NW1) s_w1[tid + 256 * j] = w1v[j];
+    for (int j = 0; j < NW2V; ++j)
+      if (tid + kThreads * j < NW2 / 4) reinterpret_cast<float4*>(s_w2)[tid + kThreads * j] = w2v[j];
+    if (tid < NW1) s_w1[tid] = w1v;
     if (tid < C1) s_b1[tid] = __ldg(P.b1 + tid);
     if (tid < C2) s_b2[tid] = __ldg(P.b2 + tid);
   }
   __syncthreads();
 
   // ------------------------------------------------------------------ phase 1: conv1 + ReLU + pool
-  if (tid < P1 * P1) {
-    const int py = tid / P1, px = tid % P1;
-    float o[C1];
-    uint8_t a[C1];
-    conv5_relu_pool<3, C1, 32>(s_img, s_w1, s_b1, 0, py, px, o, a);
+  if (tid < 2 * P1 * P1) {                     // (position, half of the output channels) per thread
+    const int pos = tid % 196, hf = tid / 196;
+    const int py = pos / P1, px = pos % P1;
+    float o[3];
+    uint8_t a[3];
+    conv5_relu_pool<3, 3, 32>(s_img, s_w1, s_b1, 3 * hf, py, px, o, a);
 #pragma unroll
-    for (int c = 0; c < C1; ++c) {
-      s_p1[c * 196 + tid] = o[c];
-      s_idx1[c * 196 + tid] = a[c];
+    for (int c = 0; c < 3; ++c) {
+      s_p1[(3 * hf + c) * 196 + pos] = o[c];
+      s_idx1[(3 * hf + c) * 196 + pos] = a[c];
     }
   }
   __syncthreads();
 
   // ------------------------------------------------------------------ phase 2: conv2 + ReLU + pool
-  if (tid < 200) {
-    const int pos = tid % 25, cg = tid / 25;   // cg in 0..7 -> channels 2cg, 2cg+1
+  if (tid < NFLAT) {                           // (position, output channel) per thread
+    const int pos = tid % 25, co = tid / 25;
     const int py = pos / P2, px = pos % P2;
-    float o[2];
-    uint8_t a[2];
-    conv5_relu_pool<C1, 2, P1>(s_p1, s_w2, s_b2, 2 * cg, py, px, o, a);
-#pragma unroll
-    for (int c = 0; c < 2; ++c) {
-      const int f = (2 * cg + c) * 25 + pos;     // NCHW flatten order == fc1's input order
-      s_flat[f] = o[c];
-      s_idx2[f] = a[c];
-    }
+    float o[1];
+    uint8_t a[1];
+    conv5_relu_pool<C1, 1, P1>(s_p1, s_w2, s_b2, co, py, px, o, a);
+    s_flat[tid] = o[0];                        // co * 25 + pos: NCHW flatten order == fc1's input order
+    s_idx2[tid] = a[0];
   }
   __syncthreads();
 
   // ------------------------------------------------------------------ phase 3: classifier forward
   matvec<NFLAT, H1, 5, true>(P.fw1, P.fb1, s_flat, s_h1, warp, lane);
   __syncthreads();
-  matvec<H1, H2, 11, true>(P.fw2, P.fb2, s_h1, s_h2, warp, lane);
+  matvec<H1, H2, 6, true>(P.fw2, P.fb2, s_h1, s_h2, warp, lane);
   __syncthreads();
-  matvec<H2, NCLS, 2, false>(P.fw3, P.fb3, s_h2, s_lg, warp, lane);
+  matvec<H2, NCLS, 1, false>(P.fw3, P.fb3, s_h2, s_lg, warp, lane);
   __syncthreads();
 
   // ------------------------------------------------------------------ phase 4: softmax cross-entropy
@@ -353,31 +347,32 @@ __global__ void __launch_bounds__(kThreads) lenet_sample_kernel(const void* __re
     s_dh2[tid] = s_h2[tid] > 0.f ? acc : 0.f;
   }
   __syncthreads();
-  // dh1[i] = relu'(h1[i]) * sum_j dh2[j] W2[j][i]; two threads per output (j halves), all 42 loads in flight
-  if (tid < 2 * H1) {
-    const int i = tid % H1, hf = tid / H1;
-    float wv[42];
+  // dh1[i] = relu'(h1[i]) * sum_j dh2[j] W2[j][i]; four threads per output (j quarters), all 21 loads in flight
+  if (tid < 4 * H1) {
+    const int i = tid % H1, qt = tid / H1;
+    float wv[21];
 #pragma unroll
-    for (int j = 0; j < 42; ++j) wv[j] = __ldg(P.fw2 + (hf * 42 + j) * H1 + i);
+    for (int j = 0; j < 21; ++j) wv[j] = __ldg(P.fw2 + (qt * 21 + j) * H1 + i);
     float acc = 0.f;
 #pragma unroll
-    for (int j = 0; j < 42; ++j) acc = fmaf(s_dh2[hf * 42 + j], wv[j], acc);
+    for (int j = 0; j < 21; ++j) acc = fmaf(s_dh2[qt * 21 + j], wv[j], acc);
     s_dp1[tid] = acc;
   }
   __syncthreads();
-  if (tid < H1) s_dh1[tid] = s_h1[tid] > 0.f ? (s_dp1[tid] + s_dp1[H1 + tid]) : 0.f;
+  if (tid < H1)
+    s_dh1[tid] = s_h1[tid] > 0.f ? ((s_dp1[tid] + s_dp1[H1 + tid]) + (s_dp1[2 * H1 + tid] + s_dp1[3 * H1 + tid])) : 0.f;
   __syncthreads();
-  // dflat[k] = sum_j dh1[j] W1[j][k]: warp w owns rows [15w, 15w+15), lanes own float4 slices of k
-  {
+  // dflat[k] = sum_j dh1[j] W1[j][k]: warps 0..14 own rows [8w, 8w+8), lanes own float4 slices of k
+  if (warp < 15) {
     float4 acc[4];
 #pragma unroll
     for (int t = 0; t < 4; ++t) acc[t] = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll 1
-    for (int jj = 0; jj < 15; jj += 5) {
-      float4 wv[5][4];
+    for (int jj = 0; jj < 8; jj += 4) {
+      float4 wv[4][4];
 #pragma unroll
-      for (int r = 0; r < 5; ++r) {
-        const int j = warp * 15 + jj + r;
+      for (int r = 0; r < 4; ++r) {
+        const int j = warp * 8 + jj + r;
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
           const int k4 = lane + 32 * t;
@@ -385,8 +380,8 @@ __global__ void __launch_bounds__(kThreads) lenet_sample_kernel(const void* __re
         }
       }
 #pragma unroll
-      for (int r = 0; r < 5; ++r) {
-        const float d = s_dh1[warp * 15 + jj + r];
+      for (int r = 0; r < 4; ++r) {
+        const float d = s_dh1[warp * 8 + jj + r];
 #pragma unroll
         for (int t = 0; t < 4; ++t) {
           acc[t].x = fmaf(d, wv[r][t].x, acc[t].x);
@@ -406,7 +401,7 @@ __global__ void __launch_bounds__(kThreads) lenet_sample_kernel(const void* __re
   for (int k = tid; k < NFLAT; k += kThreads) {
     float d = 0.f;
 #pragma unroll
-    for (int w = 0; w < 8; ++w) d += s_dp1[w * NFLAT + k];
+    for (int w = 0; w < 15; ++w) d += s_dp1[w * NFLAT + k];
     s_dflat[k] = d;
   }
   __syncthreads();
@@ -446,18 +441,22 @@ __global__ void __launch_bounds__(kThreads) lenet_sample_kernel(const void* __re
     part[OFF_B2 + tid] = acc;
   }
   // conv2 data gradient, sparse scatter: each non-zero of d(conv2 out) touches a 5x5 patch of every input channel.
-  // Warp w owns non-zeros w, w+8, ... and its own accumulator copy; lanes are the 25 taps.
+  // Warps w and w+8 share accumulator copy w%8 but own disjoint input channels (0-2 / 3-5); each copy's owners
+  // walk non-zeros w%8, w%8+8, ...; lanes are the 25 taps.
   {
-    float* acc = s_dp1 + warp * NP1;
+    float* acc = s_dp1 + (warp & 7) * NP1;
+    const int ci0 = (warp >> 3) * 3;
     const int r = lane / 5, s = lane % 5;
-    for (int e = warp; e < NFLAT; e += 8) {
+    for (int e = warp & 7; e < NFLAT; e += 8) {
       const float g = s_g2[e];
       if (g != 0.f && lane < 25) {
         const int co = e / 25, q = s_pos2[e];
         const int base = ((q / 10) + r) * 14 + (q % 10) + s;
 #pragma unroll
-        for (int ci = 0; ci < C1; ++ci)
+        for (int c = 0; c < 3; ++c) {
+          const int ci = ci0 + c;
           acc[ci * 196 + base] = fmaf(g, s_w2[(co * C1 + ci) * 25 + lane], acc[ci * 196 + base]);
+        }
       }
       __syncwarp();
     }
@@ -473,22 +472,23 @@ __global__ void __launch_bounds__(kThreads) lenet_sample_kernel(const void* __re
     s_pos1[e] = (2 * py + (k >> 1)) * 28 + (2 * px + (k & 1));
   }
   __syncthreads();
-  // conv1 weight gradient: 450 outputs, each split in two halves of the 196 positions so all threads have work
-  for (int e = tid; e < 2 * NW1; e += kThreads) {
+  // conv1 weight gradient: 450 outputs, each split in four quarters of the 196 positions so all threads have work
+  for (int e = tid; e < 4 * NW1; e += kThreads) {
     const int hf = e / NW1, o = e % NW1;
     const int s = o % 5, r = (o / 5) % 5, ci = (o / 25) % 3, co = o / 75;
     const float* src = s_img + ci * 1024 + r * 32 + s;
     float acc = 0.f;
-    const int lo = hf * 98;
+    const int lo = hf * 49;
 #pragma unroll 7
-    for (int pos = lo; pos < lo + 98; ++pos) {
+    for (int pos = lo; pos < lo + 49; ++pos) {
       const int q = s_pos1[co * 196 + pos];
       acc = fmaf(s_g1[co * 196 + pos], src[(q / 28) * 32 + (q % 28)], acc);
     }
     s_half[e] = acc;
   }
   __syncthreads();
-  for (int o = tid; o < NW1; o += kThreads) part[o] = s_half[o] + s_half[NW1 + o];
+  for (int o = tid; o < NW1; o += kThreads)
+    part[o] = (s_half[o] + s_half[NW1 + o]) + (s_half[2 * NW1 + o] + s_half[3 * NW1 + o]);
   if (tid < C1) {
     float acc = 0.f;
     for (int pos = 0; pos < 196; ++pos) acc += s_g1[tid * 196 + pos];
@@ -507,58 +507,19 @@ struct UpdateArgs {
   float* stats;            // [loss_sum_of_means, correct, samples, steps]
 };
 
+// Block roles (grid = kUpdateBlocks):
+//   [0, 60)   fc1.weight tiles: 8 rows (j) x 128 cols (k) of dW1 = dh1^T flat      (15 x 4 tiles)
+//   [60, 71)  fc2.weight tiles: 8 x 128 of dW2 = dh2^T h1                           (11 x 1)
+//   [71, 73)  fc3.weight tiles: 8 x 128 of dW3 = dlogits^T h2                       (2 x 1)
+//   [73, 86)  one thread per remaining parameter: fc biases (column sums of dout) and the conv partial sums
+// Weight tiles stream the batch through shared memory in chunks of 32 samples (next chunk prefetched into
+// registers while the current one is consumed), every thread owns 1 row x 4 consecutive columns, and the batch
+// is summed in sample order - fixed, so the step is reproducible.  The SGD update (K10) is the epilogue.
+constexpr int kUpdateBlocks = 86;
+constexpr int kRestParams = H1 + H2 + NCLS + NW1 + C1 + NW2 + C2;   // 3086
+
 template <bool kApply>
-__global__ void __launch_bounds__(256) update_kernel(UpdateArgs U, Workspace W) {
-  // parameter index space, in this order: fc1.w fc1.b fc2.w fc2.b fc3.w fc3.b | conv1.w conv1.b conv2.w conv2.b
-  constexpr int N_FC1W = H1 * NFLAT, N_FC2W = H2 * H1, N_FC3W = NCLS * H2;
-  constexpr int E0 = N_FC1W, E1 = E0 + H1, E2 = E1 + N_FC2W, E3 = E2 + H2, E4 = E3 + N_FC3W, E5 = E4 + NCLS;
-  constexpr int E6 = E5 + NW1, E7 = E6 + C1, E8 = E7 + NW2, E9 = E8 + C2;
-  const int B = U.B;
-  const int i = blockIdx.x * 256 + threadIdx.x;
-
-  if (blockIdx.x == 0 && threadIdx.x < 32 && U.stats != nullptr) {   // K13: counters stay on the device
-    float l = 0.f, c = 0.f;
-    for (int s = threadIdx.x; s < B; s += 32) { l += W.loss_rows[s]; c += W.corr_rows[s]; }
-    l = warp_sum(l);
-    c = warp_sum(c);
-    if (threadIdx.x == 0) {
-      U.stats[0] += l / (float)B;
-      U.stats[1] += c;
-      U.stats[2] += (float)B;
-      U.stats[3] += 1.f;
-    }
-  }
-  if (i >= E9) return;
-
-  float g = 0.f;
-  long long dst;
-  if (i < E5) {
-    const float *dout, *in;
-    int J, K, j, k;
-    bool is_bias = false;
-    if (i < E0)      { J = H1; K = NFLAT; j = i / NFLAT; k = i % NFLAT; dout = W.dh1; in = W.flat; dst = U.off[4] + i; }
-    else if (i < E1) { J = H1; K = 0; j = i - E0; k = 0; dout = W.dh1; in = nullptr; is_bias = true; dst = U.off[5] + j; }
-    else if (i < E2) { const int e = i - E1; J = H2; K = H1; j = e / H1; k = e % H1; dout = W.dh2; in = W.h1; dst = U.off[6] + e; }
-    else if (i < E3) { J = H2; K = 0; j = i - E2; k = 0; dout = W.dh2; in = nullptr; is_bias = true; dst = U.off[7] + j; }
-    else if (i < E4) { const int e = i - E3; J = NCLS; K = H2; j = e / H2; k = e % H2; dout = W.dlogits; in = W.h2; dst = U.off[8] + e; }
-    else             { J = NCLS; K = 0; j = i - E4; k = 0; dout = W.dlogits; in = nullptr; is_bias = true; dst = U.off[9] + j; }
-    if (is_bias) {
-#pragma unroll 16
-      for (int s = 0; s < B; ++s) g += __ldg(dout + (size_t)s * J + j);
-    } else {
-#pragma unroll 16
-      for (int s = 0; s < B; ++s) g = fmaf(__ldg(dout + (size_t)s * J + j), __ldg(in + (size_t)s * K + k), g);
-    }
-  } else {
-    int c;
-    if (i < E6)      { c = i - E5; dst = U.off[0] + c; }
-    else if (i < E7) { c = OFF_B1 + (i - E6); dst = U.off[1] + (i - E6); }
-    else if (i < E8) { c = OFF_W2 + (i - E7); dst = U.off[2] + (i - E7); }
-    else             { c = OFF_B2 + (i - E8); dst = U.off[3] + (i - E8); }
-#pragma unroll 16
-    for (int s = 0; s < B; ++s) g += __ldg(W.conv_part + (size_t)s * CONV_PART + c);
-  }
-
+__device__ __forceinline__ void apply_update(const UpdateArgs& U, long long dst, float g) {
   if constexpr (kApply) {
     const float p = U.param[dst];
     const float g1 = __fadd_rn(g, __fmul_rn(U.wd, p));
@@ -568,6 +529,102 @@ __global__ void __launch_bounds__(256) update_kernel(UpdateArgs U, Workspace W) 
   } else {
     U.dparam[dst] = g;
   }
+}
+
+template <bool kApply>
+__global__ void __launch_bounds__(256) update_kernel(UpdateArgs U, Workspace W) {
+  __shared__ __align__(16) float s_in[32 * 128];
+  __shared__ float s_dout[32 * 8];
+  const int B = U.B, b = blockIdx.x, tid = threadIdx.x;
+
+  if (b < 73) {
+    int J, K, jt, kt;
+    const float *dout, *in;
+    long long off;
+    if (b < 60)      { J = H1; K = NFLAT; jt = b / 4; kt = b % 4; dout = W.dh1; in = W.flat; off = U.off[4]; }
+    else if (b < 71) { J = H2; K = H1; jt = b - 60; kt = 0; dout = W.dh2; in = W.h1; off = U.off[6]; }
+    else             { J = NCLS; K = H2; jt = b - 71; kt = 0; dout = W.dlogits; in = W.h2; off = U.off[8]; }
+    const int tj = tid >> 5, tk4 = tid & 31;
+    const int j = jt * 8 + tj, k = kt * 128 + tk4 * 4;          // this thread's outputs: (j, k..k+3)
+    // loader roles: tile of `in` is 32 samples x 128 cols = 1024 float4 (4 per thread); tile of dout is 32 x 8
+    const int lk4 = tid & 31, ls = tid >> 5;                    // float4 column, sample row (+8 per step)
+    const int dj = tid & 7, ds = tid >> 3;                      // dout: column, sample row
+    const bool lk_ok = kt * 128 + lk4 * 4 < K;                  // K is a multiple of 4
+    const bool dj_ok = jt * 8 + dj < J;
+    float4 pre_in[4];
+    float pre_d;
+    auto fetch = [&](int s0) {
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        const int s = s0 + ls + 8 * r;
+        pre_in[r] = (lk_ok && s < B) ? __ldg(reinterpret_cast<const float4*>(in + (size_t)s * K + kt * 128) + lk4)
+                                     : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+      const int s = s0 + ds;
+      pre_d = (dj_ok && s < B) ? __ldg(dout + (size_t)s * J + jt * 8 + dj) : 0.f;
+    };
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    fetch(0);
+    for (int s0 = 0; s0 < B; s0 += 32) {
+      __syncthreads();                                          // previous chunk fully consumed
+#pragma unroll
+      for (int r = 0; r < 4; ++r) reinterpret_cast<float4*>(s_in)[(ls + 8 * r) * 32 + lk4] = pre_in[r];
+      s_dout[ds * 8 + dj] = pre_d;
+      __syncthreads();
+      if (s0 + 32 < B) fetch(s0 + 32);                          // next chunk in flight during the FMAs
+#pragma unroll 8
+      for (int s = 0; s < 32; ++s) {
+        const float d = s_dout[s * 8 + tj];
+        const float4 x = reinterpret_cast<const float4*>(s_in)[s * 32 + tk4];
+        acc.x = fmaf(d, x.x, acc.x);
+        acc.y = fmaf(d, x.y, acc.y);
+        acc.z = fmaf(d, x.z, acc.z);
+        acc.w = fmaf(d, x.w, acc.w);
+      }
+    }
+    if (j < J && k < K) {
+      const long long dst = off + (long long)j * K + k;
+      apply_update<kApply>(U, dst + 0, acc.x);
+      apply_update<kApply>(U, dst + 1, acc.y);
+      apply_update<kApply>(U, dst + 2, acc.z);
+      apply_update<kApply>(U, dst + 3, acc.w);
+    }
+    return;
+  }
+
+  if (b == 73 && tid < 32 && U.stats != nullptr) {   // K13: counters stay on the device
+    float l = 0.f, c = 0.f;
+    for (int s = tid; s < B; s += 32) { l += W.loss_rows[s]; c += W.corr_rows[s]; }
+    l = warp_sum(l);
+    c = warp_sum(c);
+    if (tid == 0) {
+      U.stats[0] += l / (float)B;
+      U.stats[1] += c;
+      U.stats[2] += (float)B;
+      U.stats[3] += 1.f;
+    }
+  }
+  const int i = (b - 73) * 256 + tid;
+  if (i >= kRestParams) return;
+  const float* src;
+  size_t stride;
+  long long dst;
+  if (i < H1)                  { src = W.dh1 + i; stride = H1; dst = U.off[5] + i; }
+  else if (i < H1 + H2)        { src = W.dh2 + (i - H1); stride = H2; dst = U.off[7] + (i - H1); }
+  else if (i < H1 + H2 + NCLS) { src = W.dlogits + (i - H1 - H2); stride = NCLS; dst = U.off[9] + (i - H1 - H2); }
+  else {
+    const int c = i - (H1 + H2 + NCLS);                          // position inside the conv partial row
+    src = W.conv_part + c;
+    stride = CONV_PART;
+    if (c < OFF_B1)      dst = U.off[0] + c;
+    else if (c < OFF_W2) dst = U.off[1] + (c - OFF_B1);
+    else if (c < OFF_B2) dst = U.off[2] + (c - OFF_W2);
+    else                 dst = U.off[3] + (c - OFF_B2);
+  }
+  float g = 0.f;
+#pragma unroll 16
+  for (int s = 0; s < B; ++s) g += __ldg(src + (size_t)s * stride);
+  apply_update<kApply>(U, dst, g);
 }
 
 __global__ void __launch_bounds__(256) stats_kernel(Workspace W, int B, float* __restrict__ stats) {
@@ -640,7 +697,7 @@ extern "C" int fedb_lenet_train_step(const fedb_lenet_t* net, const uint8_t* ima
   U.param = net->param; U.momentum = net->momentum; U.dparam = nullptr;
   for (int i = 0; i < 10; ++i) U.off[i] = net->off[i];
   U.lr = net->lr; U.mu = net->mu; U.wd = net->weight_decay; U.B = B; U.stats = stats;
-  update_kernel<true><<<fedb_ceil_div(kNumParams, 256), 256, 0, s>>>(U, W);
+  update_kernel<true><<<kUpdateBlocks, 256, 0, s>>>(U, W);
   FEDB_LAUNCH_OK();
   return 0;
 }
@@ -692,7 +749,7 @@ extern "C" int fedb_lenet_grad(const fedb_lenet_t* net, const float* images_f32,
   U.param = net->param; U.momentum = net->momentum; U.dparam = dparam;
   for (int i = 0; i < 10; ++i) U.off[i] = net->off[i];
   U.lr = 0.f; U.mu = 0.f; U.wd = 0.f; U.B = B; U.stats = loss_out;   // loss_out: 4 floats like stats
-  update_kernel<false><<<fedb_ceil_div(kNumParams, 256), 256, 0, s>>>(U, W);
+  update_kernel<false><<<kUpdateBlocks, 256, 0, s>>>(U, W);
   FEDB_LAUNCH_OK();
   return 0;
 }
