@@ -69,10 +69,10 @@ struct Params {
 // shared-memory plan of the sample kernel (floats)
 struct Sm {
   static constexpr int img = 0;                       // 3072
-  static constexpr int w1 = img + 3072;               // 452 (450 used)
-  static constexpr int b1 = w1 + 452;                 // 8
-  static constexpr int w2 = b1 + 8;                   // 2400
-  static constexpr int b2 = w2 + 2400;                // 16
+  static constexpr int w1 = img + 3072;               // 18 filters x 28 (25 used: rows padded for 128-bit loads)
+  static constexpr int b1 = w1 + 18 * 28;             // 8
+  static constexpr int w2 = b1 + 8;                   // 96 filters x 28
+  static constexpr int b2 = w2 + 96 * 28;             // 16
   static constexpr int p1 = b2 + 16;                  // 1176
   static constexpr int flat = p1 + NP1;               // 400
   static constexpr int h1 = flat + NFLAT;             // 120
@@ -112,19 +112,29 @@ __device__ __forceinline__ void conv5_relu_pool(const float* __restrict__ in, co
 #pragma unroll 1
   for (int ci = 0; ci < CI; ++ci) {
     float patch[6][6];
-    const float* src = in + ci * IN_W * IN_W + y0 * IN_W + x0;
+    const float* src = in + ci * IN_W * IN_W + y0 * IN_W + x0;     // even offset: rows are 8-byte aligned
 #pragma unroll
     for (int r = 0; r < 6; ++r)
 #pragma unroll
-      for (int s = 0; s < 6; ++s) patch[r][s] = src[r * IN_W + s];
+      for (int s = 0; s < 6; s += 2) {
+        const float2 v = *reinterpret_cast<const float2*>(src + r * IN_W + s);
+        patch[r][s] = v.x;
+        patch[r][s + 1] = v.y;
+      }
 #pragma unroll
     for (int c = 0; c < CO_PER_THREAD; ++c) {
-      const float* wk = w + ((co0 + c) * CI + ci) * 25;
+      float wreg[28];                                               // one padded 5x5 filter: 7 x LDS.128
+      const float4* wk4 = reinterpret_cast<const float4*>(w + ((co0 + c) * CI + ci) * 28);
+#pragma unroll
+      for (int t = 0; t < 7; ++t) {
+        const float4 v = wk4[t];
+        wreg[4 * t] = v.x; wreg[4 * t + 1] = v.y; wreg[4 * t + 2] = v.z; wreg[4 * t + 3] = v.w;
+      }
 #pragma unroll
       for (int r = 0; r < 5; ++r)
 #pragma unroll
         for (int s = 0; s < 5; ++s) {
-          const float wv = wk[r * 5 + s];
+          const float wv = wreg[r * 5 + s];
           acc[c][0] = fmaf(wv, patch[r][s], acc[c][0]);
           acc[c][1] = fmaf(wv, patch[r][s + 1], acc[c][1]);
           acc[c][2] = fmaf(wv, patch[r + 1][s], acc[c][2]);
@@ -255,9 +265,15 @@ __global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* _
         if (tid + kThreads * j < 768) reinterpret_cast<float4*>(s_img)[tid + kThreads * j] = v[j];
     }
 #pragma unroll
-    for (int j = 0; j < NW2V; ++j)
-      if (tid + kThreads * j < NW2 / 4) reinterpret_cast<float4*>(s_w2)[tid + kThreads * j] = w2v[j];
-    if (tid < NW1) s_w1[tid] = w1v;
+    for (int j = 0; j < NW2V; ++j) {
+      const int i = 4 * (tid + kThreads * j);
+      if (i < NW2) {
+        const float v[4] = {w2v[j].x, w2v[j].y, w2v[j].z, w2v[j].w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) s_w2[((i + q) / 25) * 28 + (i + q) % 25] = v[q];
+      }
+    }
+    if (tid < NW1) s_w1[(tid / 25) * 28 + tid % 25] = w1v;
     if (tid < C1) s_b1[tid] = __ldg(P.b1 + tid);
     if (tid < C2) s_b2[tid] = __ldg(P.b2 + tid);
   }
@@ -418,7 +434,7 @@ __global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* _
     const int k = s_idx2[e];
     const int pos = e % 25, py = pos / 5, px = pos % 5;
     s_g2[e] = s_flat[e] > 0.f ? s_dflat[e] : 0.f;
-    s_pos2[e] = (2 * py + (k >> 1)) * 10 + (2 * px + (k & 1));
+    s_pos2[e] = (2 * py + (k >> 1)) * 14 + (2 * px + (k & 1));       // offset of the arg-max inside a 14x14 p1 plane
   }
   __syncthreads();
 
@@ -429,10 +445,7 @@ __global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* _
     const float* src = s_p1 + ci * 196 + r * 14 + s;
     float acc = 0.f;
 #pragma unroll 5
-    for (int pos = 0; pos < 25; ++pos) {
-      const int q = s_pos2[co * 25 + pos];
-      acc = fmaf(s_g2[co * 25 + pos], src[(q / 10) * 14 + (q % 10)], acc);
-    }
+    for (int pos = 0; pos < 25; ++pos) acc = fmaf(s_g2[co * 25 + pos], src[s_pos2[co * 25 + pos]], acc);
     part[OFF_W2 + e] = acc;
   }
   if (tid < C2) {
@@ -450,12 +463,12 @@ __global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* _
     for (int e = warp & 7; e < NFLAT; e += 8) {
       const float g = s_g2[e];
       if (g != 0.f && lane < 25) {
-        const int co = e / 25, q = s_pos2[e];
-        const int base = ((q / 10) + r) * 14 + (q % 10) + s;
+        const int co = e / 25;
+        const int base = s_pos2[e] + r * 14 + s;
 #pragma unroll
         for (int c = 0; c < 3; ++c) {
           const int ci = ci0 + c;
-          acc[ci * 196 + base] = fmaf(g, s_w2[(co * C1 + ci) * 25 + lane], acc[ci * 196 + base]);
+          acc[ci * 196 + base] = fmaf(g, s_w2[(co * C1 + ci) * 28 + lane], acc[ci * 196 + base]);
         }
       }
       __syncwarp();
@@ -469,7 +482,7 @@ __global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* _
     const int k = s_idx1[e];
     const int pos = e % 196, py = pos / 14, px = pos % 14;
     s_g1[e] = s_p1[e] > 0.f ? d : 0.f;
-    s_pos1[e] = (2 * py + (k >> 1)) * 28 + (2 * px + (k & 1));
+    s_pos1[e] = (2 * py + (k >> 1)) * 32 + (2 * px + (k & 1));       // offset of the arg-max inside a 32x32 image plane
   }
   __syncthreads();
   // conv1 weight gradient: 450 outputs, each split in four quarters of the 196 positions so all threads have work
@@ -480,10 +493,7 @@ __global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* _
     float acc = 0.f;
     const int lo = hf * 49;
 #pragma unroll 7
-    for (int pos = lo; pos < lo + 49; ++pos) {
-      const int q = s_pos1[co * 196 + pos];
-      acc = fmaf(s_g1[co * 196 + pos], src[(q / 28) * 32 + (q % 28)], acc);
-    }
+    for (int pos = lo; pos < lo + 49; ++pos) acc = fmaf(s_g1[co * 196 + pos], src[s_pos1[co * 196 + pos]], acc);
     s_half[e] = acc;
   }
   __syncthreads();
