@@ -57,7 +57,10 @@ class FedGroup:
         self.round = 0
         self.side_stream = torch.cuda.Stream(device=self.device, priority=0)
         self._agg_done = torch.cuda.Event()
+        self._repl_done = torch.cuda.Event()
+        self._side_ctrl = K.new_ctrl(trainer.device)      # completion counter of the side-stream copy kernel
         self._common_base = False
+        self._repl_pending = False
         if codec == "fp8":
             dev = trainer.device
             self.residual = torch.zeros(self.man.n_f32, dtype=torch.float32, device=dev)
@@ -89,9 +92,12 @@ class FedGroup:
         live = self.live
         me = live.index(self.rank)
         begin, end = split_ranges(self.man.n_f32, len(live))[me]
+        # NVLink budget: every rank already RECEIVES (N-1) shards as reads and (N-1) shards as broadcast writes.
+        # The server's global model is therefore not written by the peers (that would add (N-1) more inbound
+        # shards on the primary's GPU): after K-AGG the primary's own client arena IS the global model, and it
+        # copies it into the aux arena locally (below).  Only the opt-in "fused" mode writes the replica here.
         fused_repl = self.repl_mode == "fused" and self.backup_rank != self.primary_rank
-        dst = [bufs[self.primary_rank].aux_f32_ptr()]
-        dst_i64 = [bufs[self.primary_rank].aux_i64_ptr()]
+        dst, dst_i64 = [], []
         if fused_repl:
             dst.append(bufs[self.backup_rank].aux_f32_ptr())
             dst_i64.append(bufs[self.backup_rank].aux_i64_ptr())
@@ -122,13 +128,29 @@ class FedGroup:
             self.base.copy_(self.trainer.arena.f32[:self.man.n_f32])
             self._common_base = True
         self.round += 1
-        if self.repl_mode == "overlap" and self.rank == self.primary_rank and self.backup_rank != self.primary_rank:
-            # K-REPL: primary -> backup peer copy on a side stream, overlapped with what follows
+        if self.rank == self.primary_rank:
+            # Server-side copy + K-REPL on a side stream, overlapped with what follows (eval, next local pass):
+            # ONE kernel reads the primary's fresh client arena and writes the global model (local HBM) and, in
+            # "overlap" mode, the backup's replica (peer stores over NVLink), then stamps the replica's version.
             self._agg_done.record(torch.cuda.current_stream(self.device))
             self.side_stream.wait_event(self._agg_done)
+            me_buf, bk = bufs[self.primary_rank], bufs[self.backup_rank]
+            to_replica = self.repl_mode == "overlap" and self.backup_rank != self.primary_rank and bk.base != 0
+            d32 = [me_buf.aux_f32_ptr()] + ([bk.aux_f32_ptr()] if to_replica else [])
+            d64 = [me_buf.aux_i64_ptr()] + ([bk.aux_i64_ptr()] if to_replica else [])
             with torch.cuda.stream(self.side_stream):
-                K.replicate(self.replica_arena, self.global_arena,
-                            self.peers.buffers[self.backup_rank].ctrl(), self.round)
+                K.fedavg_raw([me_buf.client_f32_ptr()], d32, 0, self.man.n_f32, ctrl_local=self._side_ctrl.data_ptr(),
+                             src_i64=[me_buf.client_i64_ptr()], dst_i64=d64, n_i64=self.man.n_i64,
+                             version=self.round, dst_ctrl=[0] + ([bk.ctrl_ptr] if to_replica else []))
+            self._repl_done.record(self.side_stream)
+            self._repl_pending = True
+
+    def before_local_pass(self) -> None:
+        """The side-stream copy READS the primary's client arena; the next local pass WRITES it.  Evaluation may
+        overlap the copy, training may not: callers invoke this right before they enqueue a training pass."""
+        if self._repl_pending:
+            torch.cuda.current_stream(self.device).wait_event(self._repl_done)
+            self._repl_pending = False
 
     def check(self) -> None:
         """Raises if a bounded spin gave up (peer died / never arrived).  Costs one 4-byte D2H read."""

@@ -56,6 +56,7 @@ class GpuFederation:
         everything is only enqueued (device-timed benchmarking)."""
         live = self.group.live
         batches = self.trainer.shard(live.index(self.rank), self.world) if self.rank in live else []
+        self.group.before_local_pass()
         self.engine.train_pass(batches, upload=upload, sync=False)
         self.group.aggregate()
         if self.evaluate:
@@ -94,6 +95,7 @@ class PeerWorker:
         if live is not None:
             fed.group.set_live(live)
         batches = fed.trainer.shard(rank, world)
+        fed.group.before_local_pass()
         st = fed.engine.train_pass(batches, upload=True, sync=True)
         fed.group.aggregate()
         return st
