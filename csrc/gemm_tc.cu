@@ -247,23 +247,48 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     const int row = m0 + q * 32 + lane;
     mbar_wait(accum_ready, 0);
     tc_fence_after();
+    // accum_ready also means every MMA has consumed its smem stage: the ring is free and becomes the staging
+    // tile of the epilogue.  Each lane owns one accumulator ROW (tcgen05.ld 32x32b), but a row-per-lane global
+    // store is 32 scattered 64-byte pieces; staging through smem turns the write-out into whole 512-byte rows.
+    constexpr int PITCH = BN + 4;                            // floats; +4 keeps 128-bit smem accesses conflict-free
+    float* stage = reinterpret_cast<float*>(smem) + (size_t)(q * 32) * PITCH;
+    const bool vec_ok = !g.atomic_out && (g.ldd % 4 == 0) && (g.N % 4 == 0) && ((reinterpret_cast<uintptr_t>(g.D) & 15) == 0);
     if (num_k > 0) {
 #pragma unroll 1
       for (int c0 = 0; c0 < BN; c0 += 16) {
         float v[16];
         tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
-        if (row < g.M) {
+#pragma unroll
+        for (int j = 0; j < 16; ++j) {
+          const int col = n0 + c0 + j;
+          if (g.bias != nullptr && blockIdx.z == 0 && col < g.N) v[j] += g.bias[col];
+          if (g.relu) v[j] = fmaxf(v[j], 0.f);
+        }
+        if (vec_ok) {
+#pragma unroll
+          for (int j = 0; j < 16; j += 4)
+            *reinterpret_cast<float4*>(stage + lane * PITCH + c0 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+        } else if (row < g.M) {
           float* drow = g.D + (long long)row * g.ldd + n0 + c0;
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
-            const int col = n0 + c0 + j;
-            if (col < g.N) {
-              float x = v[j];
-              if (g.bias != nullptr && blockIdx.z == 0) x += g.bias[col];
-              if (g.relu) x = fmaxf(x, 0.f);
-              if (g.atomic_out) atomicAdd(drow + j, x);
-              else drow[j] = x;
+            if (n0 + c0 + j < g.N) {
+              if (g.atomic_out) atomicAdd(drow + j, v[j]);
+              else drow[j] = v[j];
             }
+          }
+        }
+      }
+      if (vec_ok) {
+        __syncwarp();                                        // a warp reads back only the 32 rows it staged itself
+        for (int r = 0; r < 32; ++r) {
+          const int grow = m0 + q * 32 + r;
+          if (grow >= g.M) break;
+          for (int c4 = lane; c4 < BN / 4; c4 += 32) {
+            const int col = n0 + 4 * c4;
+            if (col < g.N)
+              *reinterpret_cast<float4*>(g.D + (long long)grow * g.ldd + col) =
+                  *reinterpret_cast<const float4*>(stage + r * PITCH + 4 * c4);
           }
         }
       }
