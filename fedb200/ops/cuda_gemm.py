@@ -28,6 +28,9 @@ def _f(name):
             "fedb_gemm_bf16_tn": [vp, vp, vp, i, i, i, ll, ll, ll, i, i, vp],
             "fedb_cast_bf16": [vp, vp, ll, vp],
             "fedb_transpose": [vp, vp, i, i, vp],
+            "fedb_conv3x3_tf32": [vp, vp, vp, vp, i, i, i, i, i, i, vp],
+            "fedb_pack3x3": [vp, vp, i, i, i, vp],
+            "fedb_conv3x3_wgrad_bf16": [vp, vp, vp, i, i, i, i, i, i, vp],
         }[name]
         _fns[name] = _lib.bind(name, C.c_int, sig)
     return _fns[name]
@@ -76,7 +79,37 @@ def _is_pointwise(shp) -> bool:
             and Cc % 32 == 0 and K % 32 == 0 and N * H * W >= MIN_PIXELS)
 
 
+def _pow2(v: int) -> bool:
+    return v >= 1 and (v & (v - 1)) == 0
+
+
+def _is_3x3(shp, cin, cout) -> bool:
+    """3x3 / stride 1 / pad 1 / ungrouped, `cin` (the GEMM's reduction channels) a multiple of 32, power-of-two maps."""
+    N, H, W, Cc, K, R, S, P, Q, sh, sw, ph, pw, groups = shp
+    return (R == 3 and S == 3 and sh == 1 and sw == 1 and ph == 1 and pw == 1 and groups == 1 and cin % 32 == 0
+            and cout % 4 == 0 and _pow2(H) and _pow2(W) and 2 <= W <= 32 and N * H * W >= MIN_PIXELS
+            and (128 // W <= H or (128 // (W * H)) >= 1))
+
+
+def pack3x3(w, mode: int) -> torch.Tensor:
+    K, Cc = w.shape[0], w.shape[1]
+    out = torch.empty(K * Cc * 9, dtype=torch.float32, device=w.device)
+    check(_f("fedb_pack3x3")(w.data_ptr(), out.data_ptr(), K, Cc, mode, current_stream()), "fedb_pack3x3")
+    _lib.count_launch()
+    return out
+
+
+def conv3x3_tf32(x, wk, y, bias, N, H, W, cin, cout, relu=False):
+    check(_f("fedb_conv3x3_tf32")(x.data_ptr(), wk.data_ptr(), y.data_ptr(), 0 if bias is None else bias.data_ptr(),
+                                  N, H, W, cin, cout, int(relu), current_stream()), "fedb_conv3x3_tf32")
+    _lib.count_launch()
+
+
 def conv_forward(x, w, bias, y, shp) -> bool:
+    if _is_3x3(shp, shp[3], shp[4]):
+        N, H, W, Cc, K = shp[:5]
+        conv3x3_tf32(x, pack3x3(w, 0), y, bias, N, H, W, Cc, K)      # implicit GEMM, shifted TMA boxes per tap
+        return True
     if not _is_pointwise(shp):
         return False
     N, H, W, Cc, K = shp[:5]
@@ -85,6 +118,10 @@ def conv_forward(x, w, bias, y, shp) -> bool:
 
 
 def conv_dgrad(dy, w, dx, shp) -> bool:
+    if _is_3x3(shp, shp[4], shp[3]):
+        N, H, W, Cc, K = shp[:5]
+        conv3x3_tf32(dy, pack3x3(w, 1), dx, None, N, H, W, K, Cc)    # dX = conv3x3(dY, flipped + transposed filter)
+        return True
     if not _is_pointwise(shp):
         return False
     N, H, W, Cc, K = shp[:5]
@@ -94,6 +131,21 @@ def conv_dgrad(dy, w, dx, shp) -> bool:
 
 
 def conv_wgrad(x, dy, dw, db, shp) -> bool:
+    if _is_3x3(shp, shp[3], shp[4]) and shp[3] % 64 == 0 and shp[4] % 64 == 0:
+        N, H, W, Cc, K = shp[:5]
+        pix = N * H * W
+        tiles = ((K + 127) // 128) * ((Cc + 127) // 128) * 9
+        splits = max(1, min(pix // 256, 444 // max(tiles, 1)))
+        dwk = torch.zeros(K * 9 * Cc, dtype=torch.float32, device=x.device)
+        dy16, x16 = cast_bf16(dy), cast_bf16(x)      # keep both alive: two temporaries would share one allocation
+        check(_f("fedb_conv3x3_wgrad_bf16")(dy16.data_ptr(), x16.data_ptr(), dwk.data_ptr(), N, H, W, Cc, K,
+                                            splits, current_stream()), "fedb_conv3x3_wgrad_bf16")
+        _lib.count_launch()
+        check(_f("fedb_pack3x3")(dwk.data_ptr(), dw.data_ptr(), K, Cc, 2, current_stream()), "fedb_pack3x3")   # += into OIHW
+        _lib.count_launch()
+        if db is not None:
+            db += dy.sum(dim=(0, 2, 3))
+        return True
     if not _is_pointwise(shp) or shp[3] % 64 or shp[4] % 64:
         return False
     N, H, W, Cc, K = shp[:5]

@@ -67,3 +67,26 @@ def test_pointwise_conv_uses_tensor_cores_and_matches(G):
     torch.testing.assert_close(xb.grad.cpu(), xa.grad, rtol=2e-3, atol=2e-2)
     # the weight gradient reads bf16 copies of dY and X: per-term error 2^-8, ~0.1 absolute after 512 terms of N(0,1)
     torch.testing.assert_close(wb.grad.cpu(), wa.grad, rtol=1e-2, atol=0.4)
+
+
+@pytest.mark.parametrize("B,C,K,HW", [(4, 64, 64, 32), (8, 64, 128, 16), (16, 128, 256, 8), (32, 256, 512, 4), (64, 512, 512, 2),
+                                      (5, 32, 32, 8)])
+def test_conv3x3_implicit_gemm_fwd_and_dgrad(G, B, C, K, HW):
+    """3x3 / stride 1 / pad 1 convolution as an implicit GEMM: every filter tap is a shifted 4-D TMA box of the NHWC
+    activation (the zero padding comes from TMA's out-of-bounds fill)."""
+    import torch.nn.functional as TF
+    from fedb200.ops import functional as F
+    torch.manual_seed(4)
+    x = torch.randn(B, C, HW, HW)
+    w = torch.randn(K, C, 3, 3) * 0.05
+    bias = torch.randn(K)
+    xa, wa = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+    xb, wb = x.clone().to(DEV).requires_grad_(True), w.clone().to(DEV).requires_grad_(True)
+    ya = TF.conv2d(xa, wa, bias, padding=1)
+    yb = F.conv2d(xb, wb, bias.to(DEV), 1, 1, 1)
+    scale = float(ya.detach().abs().max())
+    torch.testing.assert_close(yb.cpu(), ya.detach(), rtol=3e-3, atol=3e-3 * scale)
+    g = torch.randn_like(ya)
+    ya.backward(g), yb.backward(g.to(DEV))
+    torch.testing.assert_close(xb.grad.cpu(), xa.grad, rtol=3e-3, atol=3e-3 * float(xa.grad.abs().max()))
+    torch.testing.assert_close(wb.grad.cpu(), wa.grad, rtol=1e-2, atol=1e-2 * float(wa.grad.abs().max()))
