@@ -137,17 +137,19 @@ __global__ void __launch_bounds__(256) conv_wgrad_kernel(const float* __restrict
 }
 
 // ------------------------------------------------------------------------------------ batch norm
-// NHWC: element (row, c) at row*C + c.  Block = 32 channels x 8 row-lanes.
-__global__ void __launch_bounds__(256) bn_stats_kernel(const float* __restrict__ x, float* __restrict__ mean,
-                                                      float* __restrict__ invstd, float* __restrict__ run_mean,
-                                                      float* __restrict__ run_var, long long rows, int C, float eps,
-                                                      float momentum) {
+// NHWC: element (row, c) at row*C + c.  Block = 32 channels x 8 row-lanes over ONE chunk of rows; grid =
+// (C/32, chunks).  Partial sums go to scratch[chunk][2][C]; a finalize kernel combines the chunks in a fixed order
+// (deterministic, no atomics) - with one block per 32 channels only C/32 SMs would stream the whole tensor.
+__global__ void __launch_bounds__(256) bn_partial_kernel(const float* __restrict__ x, float* __restrict__ scratch, long long rows,
+                                                        int C, long long rows_per_chunk) {
   __shared__ float s_sum[8][33], s_sq[8][33];
   const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
   const int ch = blockIdx.x * 32 + cx;
+  const long long r0 = (long long)blockIdx.y * rows_per_chunk;
+  const long long r1 = r0 + rows_per_chunk < rows ? r0 + rows_per_chunk : rows;
   float sum = 0.f, sq = 0.f;
   if (ch < C)
-    for (long long r = ry; r < rows; r += 8) {
+    for (long long r = r0 + ry; r < r1; r += 8) {
       const float v = x[r * C + ch];
       sum += v;
       sq = fmaf(v, v, sq);
@@ -158,16 +160,31 @@ __global__ void __launch_bounds__(256) bn_stats_kernel(const float* __restrict__
   if (ry == 0 && ch < C) {
 #pragma unroll
     for (int j = 1; j < 8; ++j) { sum += s_sum[j][cx]; sq += s_sq[j][cx]; }
-    const float m = sum / (float)rows;
-    float var = sq / (float)rows - m * m;
-    var = var < 0.f ? 0.f : var;
-    mean[ch] = m;
-    invstd[ch] = rsqrtf(var + eps);
-    if (run_mean != nullptr) {
-      const float unbiased = rows > 1 ? var * (float)rows / (float)(rows - 1) : var;
-      run_mean[ch] = (1.f - momentum) * run_mean[ch] + momentum * m;
-      run_var[ch] = (1.f - momentum) * run_var[ch] + momentum * unbiased;
-    }
+    scratch[((long long)blockIdx.y * 2 + 0) * C + ch] = sum;
+    scratch[((long long)blockIdx.y * 2 + 1) * C + ch] = sq;
+  }
+}
+
+__global__ void __launch_bounds__(128) bn_finalize_kernel(const float* __restrict__ scratch, int chunks, float* __restrict__ mean,
+                                                         float* __restrict__ invstd, float* __restrict__ run_mean,
+                                                         float* __restrict__ run_var, long long rows, int C, float eps,
+                                                         float momentum) {
+  const int ch = blockIdx.x * 128 + threadIdx.x;
+  if (ch >= C) return;
+  float sum = 0.f, sq = 0.f;
+  for (int k = 0; k < chunks; ++k) {
+    sum += scratch[((long long)k * 2 + 0) * C + ch];
+    sq += scratch[((long long)k * 2 + 1) * C + ch];
+  }
+  const float m = sum / (float)rows;
+  float var = sq / (float)rows - m * m;
+  var = var < 0.f ? 0.f : var;
+  mean[ch] = m;
+  invstd[ch] = rsqrtf(var + eps);
+  if (run_mean != nullptr) {
+    const float unbiased = rows > 1 ? var * (float)rows / (float)(rows - 1) : var;
+    run_mean[ch] = (1.f - momentum) * run_mean[ch] + momentum * m;
+    run_var[ch] = (1.f - momentum) * run_var[ch] + momentum * unbiased;
   }
 }
 
@@ -189,19 +206,21 @@ __global__ void bn_eval_prep_kernel(const float* __restrict__ run_mean, const fl
   if (ch < C) { mean[ch] = run_mean[ch]; invstd[ch] = rsqrtf(run_var[ch] + eps); }
 }
 
-// pass 1 of the backward: per-channel sum(dz) and sum(dz * xhat), dz = dy * act'(z)
-__global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const float* __restrict__ x, const float* __restrict__ dy,
-                                                           const float* __restrict__ mean, const float* __restrict__ invstd,
-                                                           const float* __restrict__ gamma, const float* __restrict__ beta,
-                                                           float* __restrict__ dgamma, float* __restrict__ dbeta,
-                                                           long long rows, int C, int act) {
+// pass 1 of the backward: per-channel sum(dz) and sum(dz * xhat), dz = dy * act'(z); chunked like the forward stats
+__global__ void __launch_bounds__(256) bn_bwd_partial_kernel(const float* __restrict__ x, const float* __restrict__ dy,
+                                                            const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                            const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                            float* __restrict__ scratch, long long rows, int C, int act,
+                                                            long long rows_per_chunk) {
   __shared__ float s_a[8][33], s_b[8][33];
   const int cx = threadIdx.x & 31, ry = threadIdx.x >> 5;
   const int ch = blockIdx.x * 32 + cx;
+  const long long r0 = (long long)blockIdx.y * rows_per_chunk;
+  const long long r1 = r0 + rows_per_chunk < rows ? r0 + rows_per_chunk : rows;
   float sa = 0.f, sb = 0.f;
   if (ch < C) {
     const float m = mean[ch], is = invstd[ch], g = gamma[ch], b = beta[ch];
-    for (long long r = ry; r < rows; r += 8) {
+    for (long long r = r0 + ry; r < r1; r += 8) {
       const float xh = (x[r * C + ch] - m) * is;
       float d = dy[r * C + ch];
       if (act) d *= act_bwd(fmaf(xh, g, b), act);
@@ -215,9 +234,22 @@ __global__ void __launch_bounds__(256) bn_bwd_reduce_kernel(const float* __restr
   if (ry == 0 && ch < C) {
 #pragma unroll
     for (int j = 1; j < 8; ++j) { sa += s_a[j][cx]; sb += s_b[j][cx]; }
-    dbeta[ch] = sa;
-    dgamma[ch] = sb;
+    scratch[((long long)blockIdx.y * 2 + 0) * C + ch] = sa;
+    scratch[((long long)blockIdx.y * 2 + 1) * C + ch] = sb;
   }
+}
+
+__global__ void __launch_bounds__(128) bn_bwd_finalize_kernel(const float* __restrict__ scratch, int chunks,
+                                                             float* __restrict__ dgamma, float* __restrict__ dbeta, int C) {
+  const int ch = blockIdx.x * 128 + threadIdx.x;
+  if (ch >= C) return;
+  float sa = 0.f, sb = 0.f;
+  for (int k = 0; k < chunks; ++k) {
+    sa += scratch[((long long)k * 2 + 0) * C + ch];
+    sb += scratch[((long long)k * 2 + 1) * C + ch];
+  }
+  dbeta[ch] = sa;
+  dgamma[ch] = sb;
 }
 
 // pass 2: dx = gamma * invstd * (dz - mean(dz) - xhat * mean(dz * xhat))
@@ -454,10 +486,30 @@ extern "C" int fedb_nn_conv_wgrad(const float* x, const float* dy, float* dw, fl
   return 0;
 }
 
+// how many row chunks for a [rows x C] reduction so that ~4 blocks land on every SM (bounded by the scratch size)
+static int bn_chunks(long long rows, int C, long long scratch_floats, long long* rows_per_chunk) {
+  const int cgroups = fedb_ceil_div(C, 32);
+  long long want = (long long)fedb_num_sms() * 4 / cgroups;
+  if (want < 1) want = 1;
+  const long long by_rows = (rows + 63) / 64;                  // at least 64 rows per chunk
+  if (want > by_rows) want = by_rows;
+  const long long by_scratch = scratch_floats / (2LL * C);
+  if (want > by_scratch) want = by_scratch;
+  if (want < 1) want = 1;
+  *rows_per_chunk = (rows + want - 1) / want;
+  return (int)((rows + *rows_per_chunk - 1) / *rows_per_chunk);
+}
+
 extern "C" int fedb_nn_bn_fwd(const float* x, float* y, float* mean, float* invstd, float* run_mean, float* run_var,
                               const float* gamma, const float* beta, long long rows, int C, float eps, float momentum,
-                              int training, int act, void* stream) {
-  if (training) bn_stats_kernel<<<fedb_ceil_div(C, 32), 256, 0, S_>>>(x, mean, invstd, run_mean, run_var, rows, C, eps, momentum);
+                              int training, int act, float* scratch, long long scratch_floats, void* stream) {
+  if (training) {
+    FEDB_REQUIRE(scratch != nullptr && scratch_floats >= 2LL * C, "fedb_nn_bn_fwd: scratch of at least 2*C floats required");
+    long long rpc = 0;
+    const int chunks = bn_chunks(rows, C, scratch_floats, &rpc);
+    bn_partial_kernel<<<dim3(fedb_ceil_div(C, 32), chunks), 256, 0, S_>>>(x, scratch, rows, C, rpc);
+    bn_finalize_kernel<<<fedb_ceil_div(C, 128), 128, 0, S_>>>(scratch, chunks, mean, invstd, run_mean, run_var, rows, C, eps, momentum);
+  }
   else bn_eval_prep_kernel<<<fedb_ceil_div(C, 128), 128, 0, S_>>>(run_mean, run_var, mean, invstd, C, eps);
   bn_apply_kernel<<<grid_for(rows * C), 256, 0, S_>>>(x, y, mean, invstd, gamma, beta, rows * C, C, act);
   FEDB_LAUNCH_OK();
@@ -465,8 +517,12 @@ extern "C" int fedb_nn_bn_fwd(const float* x, float* y, float* mean, float* invs
 }
 extern "C" int fedb_nn_bn_bwd(const float* x, const float* dy, float* dx, const float* mean, const float* invstd,
                               const float* gamma, const float* beta, float* dgamma, float* dbeta, long long rows, int C,
-                              int act, int training, void* stream) {
-  bn_bwd_reduce_kernel<<<fedb_ceil_div(C, 32), 256, 0, S_>>>(x, dy, mean, invstd, gamma, beta, dgamma, dbeta, rows, C, act);
+                              int act, int training, float* scratch, long long scratch_floats, void* stream) {
+  FEDB_REQUIRE(scratch != nullptr && scratch_floats >= 2LL * C, "fedb_nn_bn_bwd: scratch of at least 2*C floats required");
+  long long rpc = 0;
+  const int chunks = bn_chunks(rows, C, scratch_floats, &rpc);
+  bn_bwd_partial_kernel<<<dim3(fedb_ceil_div(C, 32), chunks), 256, 0, S_>>>(x, dy, mean, invstd, gamma, beta, scratch, rows, C, act, rpc);
+  bn_bwd_finalize_kernel<<<fedb_ceil_div(C, 128), 128, 0, S_>>>(scratch, chunks, dgamma, dbeta, C);
   bn_bwd_apply_kernel<<<grid_for(rows * C), 256, 0, S_>>>(x, dy, dx, mean, invstd, gamma, beta, dgamma, dbeta, rows * C, C,
                                                          1.f / (float)rows, act, training);
   FEDB_LAUNCH_OK();

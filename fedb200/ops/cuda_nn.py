@@ -17,6 +17,7 @@ from ._lib import check, current_stream, lib
 
 CL = torch.channels_last
 ACT = {"none": 0, "relu": 1, "swish": 2, "sigmoid": 3}
+_BN_CHUNKS = 160          # upper bound of row chunks per BatchNorm reduction (scratch = 2 * C * chunks floats)
 
 _vp, _i, _ll, _f = C.c_void_p, C.c_int, C.c_longlong, C.c_float
 _BOUND = False
@@ -32,8 +33,8 @@ def _bind():
         "fedb_nn_conv_fwd": [_vp, _vp, _vp, _vp, ip, _vp],
         "fedb_nn_conv_dgrad": [_vp, _vp, _vp, ip, _vp],
         "fedb_nn_conv_wgrad": [_vp, _vp, _vp, _vp, ip, _vp],
-        "fedb_nn_bn_fwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _f, _f, _i, _i, _vp],
-        "fedb_nn_bn_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _i, _i, _vp],
+        "fedb_nn_bn_fwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _f, _f, _i, _i, _vp, _ll, _vp],
+        "fedb_nn_bn_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _i, _i, _vp, _ll, _vp],
         "fedb_nn_act_fwd": [_vp, _vp, _ll, _i, _vp],
         "fedb_nn_act_bwd": [_vp, _vp, _vp, _ll, _i, _vp],
         "fedb_nn_add_act": [_vp, _vp, _vp, _ll, _i, _vp],
@@ -134,9 +135,10 @@ class _BatchNorm(torch.autograd.Function):
         y = torch.empty_like(x, memory_format=CL)
         mean = torch.empty(Cc, dtype=torch.float32, device=x.device)
         invstd = torch.empty(Cc, dtype=torch.float32, device=x.device)
+        scratch = torch.empty(2 * Cc * _BN_CHUNKS, dtype=torch.float32, device=x.device) if training else None
         _call("fedb_nn_bn_fwd", x.data_ptr(), y.data_ptr(), mean.data_ptr(), invstd.data_ptr(), run_mean.data_ptr(),
               run_var.data_ptr(), gamma.data_ptr(), beta.data_ptr(), rows, Cc, eps, momentum, int(training), act,
-              current_stream(), launches=2)
+              _p(scratch), 2 * Cc * _BN_CHUNKS, current_stream(), launches=3 if training else 2)
         ctx.save_for_backward(x, gamma, beta, mean, invstd)
         ctx.act, ctx.rows, ctx.training = act, rows, bool(training)
         return y
@@ -149,9 +151,10 @@ class _BatchNorm(torch.autograd.Function):
         dx = torch.empty_like(x, memory_format=CL)
         dgamma = torch.empty(Cc, dtype=torch.float32, device=x.device)
         dbeta = torch.empty(Cc, dtype=torch.float32, device=x.device)
+        scratch = torch.empty(2 * Cc * _BN_CHUNKS, dtype=torch.float32, device=x.device)
         _call("fedb_nn_bn_bwd", x.data_ptr(), dy.data_ptr(), dx.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
               gamma.data_ptr(), beta.data_ptr(), dgamma.data_ptr(), dbeta.data_ptr(), ctx.rows, Cc, ctx.act,
-              int(ctx.training), current_stream(), launches=2)
+              int(ctx.training), scratch.data_ptr(), 2 * Cc * _BN_CHUNKS, current_stream(), launches=3)
         return dx, dgamma, dbeta, None, None, None, None, None, None
 
 
