@@ -150,7 +150,8 @@ struct GemmArgs {
   // activation, one per filter tap, with out-of-bounds rows/columns zero-filled by the TMA unit (= the padding)
   int conv;            // 0: plain GEMM
   int Cin, H, W;       // activation geometry
-  int bw, bh, bn;      // box: bw*bh*bn == 128 output pixels = one M tile (bw == W)
+  int bw, bh, bn;      // box: bw*bh*bn == 128 output pixels = one M tile (bw == W); H, W are the OUTPUT map
+  int cstride, cpad, fs;   // convolution stride, padding, filter size (fs x fs taps)
 };
 
 // smem stage layout: A tile then B tile, each a multiple of 1024 B (swizzle atom)
@@ -216,11 +217,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             const int per_tap = g.Cin / BK;
             const int kk = k0 / BK;
             const int tap = kk / per_tap, c0 = (kk % per_tap) * BK;
-            const int r = tap / 3, sx = tap % 3;
+            const int r = tap / g.fs, sx = tap % g.fs;
             int n_img, h0;
             if (g.bn == 1) { const int tpi = g.H / g.bh; n_img = blockIdx.x / tpi; h0 = (blockIdx.x % tpi) * g.bh; }
             else           { n_img = blockIdx.x * g.bn; h0 = 0; }
-            tma_load_4d(a_dst, &mapA, &full[s], c0, sx - 1, h0 + r - 1, n_img);   // box [32 ch x bw x bh x bn]
+            // box [32 ch x bw x bh x bn] output pixels; with stride 2 the tensor map itself skips every other input
+            // pixel (elementStrides), so the same 128 x 32 tile lands in shared memory
+            tma_load_4d(a_dst, &mapA, &full[s], c0, sx - g.cpad, h0 * g.cstride + r - g.cpad, n_img);
             tma_load_2d(b_dst, &mapB, &full[s], k0, n0);
           } else {
             tma_load_2d(a_dst, &mapA, &full[s], k0, m0);                   // box [32 fp32 (K) x BM rows]
@@ -239,7 +242,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             else           { n_img = pt * g.bn; h0 = 0; }
 #pragma unroll
             for (int c = 0; c < Smem<BN, KIND>::kBN / 64; ++c)
-              tma_load_4d(b_dst + c * kChunkBytes, &mapB, &full[s], n0 + c * 64, tap % 3 - 1, h0 + tap / 3 - 1, n_img);
+              tma_load_4d(b_dst + c * kChunkBytes, &mapB, &full[s], n0 + c * 64, tap % g.fs - g.cpad,
+                          h0 * g.cstride + tap / g.fs - g.cpad, n_img);
           } else {
 #pragma unroll
             for (int c = 0; c < Smem<BN, KIND>::kBN / 64; ++c)
@@ -374,14 +378,16 @@ int make_map_2d(CUtensorMap* map, const void* base, int elem, long long rows, lo
 
 // 4-D NHWC activation [N][H][W][C] (fp32: elem 4, bf16: elem 2); box = [128 bytes of channels x bw x bh x bn],
 // 128B swizzle, zero fill outside
-int make_map_nhwc(CUtensorMap* map, const void* base, int elem, int N, int H, int W, int C, int bw, int bh, int bn) {
+int make_map_nhwc(CUtensorMap* map, const void* base, int elem, int N, int H, int W, int C, int bw, int bh, int bn,
+                  int estride = 1) {
   EncodeTiledFn enc;
   if (int rc = get_encode(&enc)) return rc;
   FEDB_REQUIRE(((uintptr_t)base & 15) == 0 && (C * elem) % 16 == 0, "conv_tc: activation base/pitch must be 16-byte aligned");
   cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
   cuuint64_t strides[3] = {(cuuint64_t)C * elem, (cuuint64_t)W * C * elem, (cuuint64_t)H * W * C * elem};
-  cuuint32_t box[4] = {(cuuint32_t)(128 / elem), (cuuint32_t)bw, (cuuint32_t)bh, (cuuint32_t)bn};
-  cuuint32_t estr[4] = {1, 1, 1, 1};
+  // with a traversal stride the box SPANS bw*stride input pixels and picks every stride-th one
+  cuuint32_t box[4] = {(cuuint32_t)(128 / elem), (cuuint32_t)(bw * estride), (cuuint32_t)(bh * estride), (cuuint32_t)bn};
+  cuuint32_t estr[4] = {1, (cuuint32_t)estride, (cuuint32_t)estride, 1};
   CUresult r = enc(map, elem == 4 ? CU_TENSOR_MAP_DATA_TYPE_FLOAT32 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 4, (void*)base, dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
                    CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return fedb_fail((int)r, __FILE__, __LINE__, "cuTensorMapEncodeTiled (NHWC) failed");
@@ -391,15 +397,16 @@ int make_map_nhwc(CUtensorMap* map, const void* base, int elem, int N, int H, in
 // mode 0 (forward):  Wk[k][(r*3+s)*C + c] = W[k][c][r][s]
 // mode 1 (dgrad):    Wd[c][(r*3+s)*K + k] = W[k][c][2-r][2-s]     (transposed + spatially flipped filter)
 // mode 2 (unpack):   dW[k][c][r][s] += dWk[k][(r*3+s)*C + c]      (packed weight gradient back to OIHW)
-__global__ void __launch_bounds__(256) pack3x3_kernel(const float* __restrict__ w, float* __restrict__ out, int K, int C, int mode) {
-  const int total = K * C * 9;
+__global__ void __launch_bounds__(256) pack3x3_kernel(const float* __restrict__ w, float* __restrict__ out, int K, int C, int mode,
+                                                     int T /* taps: 9 or 1 */) {
+  const int total = K * C * T;
   for (int i = blockIdx.x * 256 + threadIdx.x; i < total; i += gridDim.x * 256) {
     if (mode == 0) {
-      const int c = i % C, tap = (i / C) % 9, k = i / (9 * C);
-      out[i] = w[(k * C + c) * 9 + tap];
+      const int c = i % C, tap = (i / C) % T, k = i / (T * C);
+      out[i] = w[(k * C + c) * T + tap];
     } else if (mode == 2) {
-      const int c = i % C, tap = (i / C) % 9, k = i / (9 * C);
-      out[(k * C + c) * 9 + tap] += w[i];
+      const int c = i % C, tap = (i / C) % T, k = i / (T * C);
+      out[(k * C + c) * T + tap] += w[i];
     } else {
       const int k = i % K, tap = (i / K) % 9, c = i / (9 * K);
       out[i] = w[(k * C + c) * 9 + (8 - tap)];
@@ -454,7 +461,7 @@ int run_gemm(int kind, const void* A, const void* B, float* D, const float* bias
   splits = (K + kps - 1) / kps;
   g.relu = relu;
   g.atomic_out = (splits > 1 || accumulate) ? 1 : 0;
-  g.conv = 0; g.Cin = g.H = g.W = g.bw = g.bh = g.bn = 0;
+  g.conv = 0; g.Cin = g.H = g.W = g.bw = g.bh = g.bn = 0; g.cstride = 1; g.cpad = 0; g.fs = 1;
   return kind == 0 ? dispatch_bn<0>(bn, ma, mb, g, splits, s) : dispatch_bn<1>(bn, ma, mb, g, splits, s);
 }
 
@@ -496,46 +503,61 @@ extern "C" int fedb_gemm_bf16_tn(const uint16_t* At, const uint16_t* Bt, float* 
   return run_gemm(1, At, Bt, D, nullptr, M, N, K, lda, ldb, ldd, 0, splits, accumulate, (cudaStream_t)stream);
 }
 
-// Y[N,H,W,Cout] = conv3x3(X[N,H,W,Cin], stride 1, pad 1) as an implicit GEMM on the tensor cores.
-// Wk is the packed filter [Cout][9*Cin] (fedb_pack3x3 mode 0; mode 1 + swapped channel roles gives the dgrad).
-extern "C" int fedb_conv3x3_tf32(const float* X, const float* Wk, float* Y, const float* bias, int N, int H, int W, int Cin,
-                                 int Cout, int relu, void* stream) {
-  FEDB_REQUIRE(Cin % 32 == 0 && Cout % 4 == 0, "fedb_conv3x3_tf32: Cin must be a multiple of 32");
-  FEDB_REQUIRE(W <= 32 && (W & (W - 1)) == 0 && (H & (H - 1)) == 0 && W >= 2, "fedb_conv3x3_tf32: H, W powers of two, W <= 32");
-  const int bw = W;
+// Y[N,P,Q,Cout] = conv(X[N,H,W,Cin]; fs x fs filter, stride 1|2, padding) as an implicit GEMM on the tensor cores.
+// Wk is the packed filter [Cout][fs*fs*Cin] (fedb_pack_filter mode 0; for 3x3/stride 1, mode 1 + swapped channel
+// roles gives the data gradient).  P = H/stride, Q = W/stride ("same"-style geometry of the CIFAR zoo).
+extern "C" int fedb_conv_tf32(const float* X, const float* Wk, float* Y, const float* bias, int N, int H, int W, int Cin,
+                              int Cout, int fs, int stride, int pad, int relu, void* stream) {
+  FEDB_REQUIRE(Cin % 32 == 0 && Cout % 4 == 0, "fedb_conv_tf32: Cin must be a multiple of 32");
+  FEDB_REQUIRE((fs == 3 && pad == 1) || (fs == 1 && pad == 0), "fedb_conv_tf32: 3x3/pad 1 or 1x1/pad 0");
+  FEDB_REQUIRE(stride == 1 || stride == 2, "fedb_conv_tf32: stride 1 or 2");
+  const int P = H / stride, Q = W / stride;
+  FEDB_REQUIRE(Q <= 32 && Q >= 2 && (Q & (Q - 1)) == 0 && (P & (P - 1)) == 0 && P * stride == H && Q * stride == W,
+               "fedb_conv_tf32: output maps must be powers of two, width <= 32");
+  const int bw = Q;
   int bh = 128 / bw;
-  if (bh > H) bh = H;
+  if (bh > P) bh = P;
   const int bn = 128 / (bw * bh);
-  FEDB_REQUIRE(bw * bh * bn == 128 && (bn == 1 || bh == H), "fedb_conv3x3_tf32: unsupported tile geometry");
-  const int M = N * H * W, K = 9 * Cin;
+  FEDB_REQUIRE(bw * bh * bn == 128 && (bn == 1 || bh == P), "fedb_conv_tf32: unsupported tile geometry");
+  const int M = N * P * Q, K = fs * fs * Cin;
   const int bnt = Cout >= 128 ? 128 : (Cout > 32 ? 64 : 32);
   CUtensorMap ma, mb;
-  if (int rc = make_map_nhwc(&ma, X, 4, N, H, W, Cin, bw, bh, bn)) return rc;
+  if (int rc = make_map_nhwc(&ma, X, 4, N, H, W, Cin, bw, bh, bn, stride)) return rc;
   if (int rc = make_map_2d(&mb, Wk, 4, Cout, K, K, 32, bnt)) return rc;
   GemmArgs g;
   g.D = Y; g.bias = bias; g.ldd = Cout; g.M = M; g.N = Cout; g.K = K; g.k_per_split = K; g.relu = relu; g.atomic_out = 0;
-  g.conv = 1; g.Cin = Cin; g.H = H; g.W = W; g.bw = bw; g.bh = bh; g.bn = bn;
+  g.conv = 1; g.Cin = Cin; g.H = P; g.W = Q; g.bw = bw; g.bh = bh; g.bn = bn; g.cstride = stride; g.cpad = pad; g.fs = fs;
   return dispatch_bn<0>(bnt, ma, mb, g, 1, (cudaStream_t)stream);
 }
 
-// dWk[Cout][9*Cin] (+)= sum over pixels of dY[pix][Cout]^T * shift_tap(X)[pix][Cin]: bf16 copies of dY and X (NHWC),
-// reduction over the pixels split across CTAs, partial tiles combined with red.global.add (dWk zeroed by the caller).
-extern "C" int fedb_conv3x3_wgrad_bf16(const uint16_t* dY, const uint16_t* X, float* dWk, int N, int H, int W, int Cin, int Cout,
-                                       int splits, void* stream) {
-  FEDB_REQUIRE(Cin % 64 == 0 && Cout % 64 == 0, "fedb_conv3x3_wgrad_bf16: channels must be multiples of 64");
-  FEDB_REQUIRE(W <= 32 && (W & (W - 1)) == 0 && (H & (H - 1)) == 0 && W >= 2, "fedb_conv3x3_wgrad_bf16: H, W powers of two, W <= 32");
-  const int bw = W;
+extern "C" int fedb_conv3x3_tf32(const float* X, const float* Wk, float* Y, const float* bias, int N, int H, int W, int Cin,
+                                 int Cout, int relu, void* stream) {
+  return fedb_conv_tf32(X, Wk, Y, bias, N, H, W, Cin, Cout, 3, 1, 1, relu, stream);
+}
+
+// dWk[Cout][fs*fs*Cin] (+)= sum over output pixels of dY[pix][Cout]^T * shift_tap(X)[pix][Cin]: bf16 copies of dY and X
+// (NHWC), reduction over the pixels split across CTAs, partial tiles combined with red.global.add (dWk zeroed by the
+// caller).  Strided convolutions read X through a tensor map with element strides.
+extern "C" int fedb_conv_wgrad_bf16(const uint16_t* dY, const uint16_t* X, float* dWk, int N, int H, int W, int Cin, int Cout,
+                                    int fs, int stride, int pad, int splits, void* stream) {
+  FEDB_REQUIRE(Cin % 64 == 0 && Cout % 64 == 0, "fedb_conv_wgrad_bf16: channels must be multiples of 64");
+  FEDB_REQUIRE((fs == 3 && pad == 1) || (fs == 1 && pad == 0), "fedb_conv_wgrad_bf16: 3x3/pad 1 or 1x1/pad 0");
+  FEDB_REQUIRE(stride == 1 || stride == 2, "fedb_conv_wgrad_bf16: stride 1 or 2");
+  const int P = H / stride, Q = W / stride;
+  FEDB_REQUIRE(Q <= 32 && Q >= 2 && (Q & (Q - 1)) == 0 && (P & (P - 1)) == 0 && P * stride == H && Q * stride == W,
+               "fedb_conv_wgrad_bf16: output maps must be powers of two, width <= 32");
+  const int bw = Q;
   int bh = 64 / bw;
-  if (bh > H) bh = H;
+  if (bh > P) bh = P;
   const int bn = 64 / (bw * bh);
-  FEDB_REQUIRE(bw * bh * bn == 64 && (bn == 1 || bh == H), "fedb_conv3x3_wgrad_bf16: unsupported tile geometry");
-  const int pix = N * H * W;
+  FEDB_REQUIRE(bw * bh * bn == 64 && (bn == 1 || bh == P), "fedb_conv_wgrad_bf16: unsupported tile geometry");
+  const int pix = N * P * Q, taps = fs * fs;
   const int bnt = Cin >= 128 ? 128 : 64;
   CUtensorMap ma, mb;
-  if (int rc = make_map_2d(&ma, dY, 2, pix, Cout, Cout, 64, 64)) return rc;          // A^T: [K=pix][M=Cout]
-  if (int rc = make_map_nhwc(&mb, X, 2, N, H, W, Cin, bw, bh, bn)) return rc;         // B^T: shifted [pix][Cin]
+  if (int rc = make_map_2d(&ma, dY, 2, pix, Cout, Cout, 64, 64)) return rc;                  // A^T: [K=pix][M=Cout]
+  if (int rc = make_map_nhwc(&mb, X, 2, N, H, W, Cin, bw, bh, bn, stride)) return rc;        // B^T: shifted [pix][Cin]
   GemmArgs g;
-  g.D = dWk; g.bias = nullptr; g.ldd = 9LL * Cin; g.M = Cout; g.N = Cin;
+  g.D = dWk; g.bias = nullptr; g.ldd = (long long)taps * Cin; g.M = Cout; g.N = Cin;
   const int ktiles = (pix + 63) / 64;
   if (splits < 1) splits = 1;
   if (splits > ktiles) splits = ktiles;
@@ -543,10 +565,10 @@ extern "C" int fedb_conv3x3_wgrad_bf16(const uint16_t* dY, const uint16_t* X, fl
   g.K = ktiles * 64; g.k_per_split = tiles_per_split * 64;
   splits = (ktiles + tiles_per_split - 1) / tiles_per_split;
   g.relu = 0; g.atomic_out = 1;
-  g.conv = 2; g.Cin = Cin; g.H = H; g.W = W; g.bw = bw; g.bh = bh; g.bn = bn;
+  g.conv = 2; g.Cin = Cin; g.H = P; g.W = Q; g.bw = bw; g.bh = bh; g.bn = bn; g.cstride = stride; g.cpad = pad; g.fs = fs;
   static bool attr128 = false, attr64 = false;
   cudaStream_t s = (cudaStream_t)stream;
-  dim3 grid(fedb_ceil_div(Cout, BM), fedb_ceil_div(Cin, bnt) * 9, splits);
+  dim3 grid(fedb_ceil_div(Cout, BM), fedb_ceil_div(Cin, bnt) * taps, splits);
   if (bnt == 128) {
     if (!attr128) { FEDB_CHECK(cudaFuncSetAttribute(gemm_tc_kernel<128, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem<128, 1>::kTotal)); attr128 = true; }
     gemm_tc_kernel<128, 1><<<grid, kThreads, Smem<128, 1>::kTotal, s>>>(ma, mb, g);
@@ -558,10 +580,25 @@ extern "C" int fedb_conv3x3_wgrad_bf16(const uint16_t* dY, const uint16_t* X, fl
   return 0;
 }
 
+extern "C" int fedb_conv3x3_wgrad_bf16(const uint16_t* dY, const uint16_t* X, float* dWk, int N, int H, int W, int Cin, int Cout,
+                                       int splits, void* stream) {
+  return fedb_conv_wgrad_bf16(dY, X, dWk, N, H, W, Cin, Cout, 3, 1, 1, splits, stream);
+}
+
+// filter (un)packing for fs*fs = taps (9 or 1); see pack3x3_kernel for the modes
+extern "C" int fedb_pack_filter(const float* w_oihw, float* out, int K, int C, int mode, int taps, void* stream) {
+  FEDB_REQUIRE(taps == 9 || (taps == 1 && mode != 1), "fedb_pack_filter: taps 9, or 1 for modes 0/2");
+  int blocks = fedb_ceil_div((long long)K * C * taps, 256);
+  if (blocks > fedb_num_sms() * 8) blocks = fedb_num_sms() * 8;
+  pack3x3_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w_oihw, out, K, C, mode, taps);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+
 extern "C" int fedb_pack3x3(const float* w_oihw, float* out, int K, int C, int mode, void* stream) {
   int blocks = fedb_ceil_div((long long)K * C * 9, 256);
   if (blocks > fedb_num_sms() * 8) blocks = fedb_num_sms() * 8;
-  pack3x3_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w_oihw, out, K, C, mode);
+  pack3x3_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w_oihw, out, K, C, mode, 9);
   FEDB_LAUNCH_OK();
   return 0;
 }

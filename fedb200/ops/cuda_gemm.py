@@ -31,6 +31,9 @@ def _f(name):
             "fedb_conv3x3_tf32": [vp, vp, vp, vp, i, i, i, i, i, i, vp],
             "fedb_pack3x3": [vp, vp, i, i, i, vp],
             "fedb_conv3x3_wgrad_bf16": [vp, vp, vp, i, i, i, i, i, i, vp],
+            "fedb_conv_tf32": [vp, vp, vp, vp, i, i, i, i, i, i, i, i, i, vp],
+            "fedb_conv_wgrad_bf16": [vp, vp, vp, i, i, i, i, i, i, i, i, i, vp],
+            "fedb_pack_filter": [vp, vp, i, i, i, i, vp],
         }[name]
         _fns[name] = _lib.bind(name, C.c_int, sig)
     return _fns[name]
@@ -91,6 +94,27 @@ def _is_3x3(shp, cin, cout) -> bool:
             and (128 // W <= H or (128 // (W * H)) >= 1))
 
 
+def _strided(shp):
+    """(fs, stride, pad) when the layer is a stride-2 3x3/pad-1 or 1x1/pad-0 ungrouped convolution whose OUTPUT maps
+    are powers of two (the down-sampling layers of the ResNet / DLA / RegNet families), else None."""
+    N, H, W, Cc, K, R, S, P, Q, sh, sw, ph, pw, groups = shp
+    if groups != 1 or R != S or sh != 2 or sw != 2 or H % 2 or W % 2:
+        return None
+    if not ((R == 3 and ph == 1 and pw == 1) or (R == 1 and ph == 0 and pw == 0)):
+        return None
+    if not (_pow2(P) and _pow2(Q) and 2 <= Q <= 32 and P * 2 == H and Q * 2 == W and N * P * Q >= MIN_PIXELS):
+        return None
+    return R, 2, ph
+
+
+def pack_filter(w, mode: int, taps: int) -> torch.Tensor:
+    K, Cc = w.shape[0], w.shape[1]
+    out = torch.empty(K * Cc * taps, dtype=torch.float32, device=w.device)
+    check(_f("fedb_pack_filter")(w.data_ptr(), out.data_ptr(), K, Cc, mode, taps, current_stream()), "fedb_pack_filter")
+    _lib.count_launch()
+    return out
+
+
 def pack3x3(w, mode: int) -> torch.Tensor:
     K, Cc = w.shape[0], w.shape[1]
     out = torch.empty(K * Cc * 9, dtype=torch.float32, device=w.device)
@@ -109,6 +133,15 @@ def conv_forward(x, w, bias, y, shp) -> bool:
     if _is_3x3(shp, shp[3], shp[4]):
         N, H, W, Cc, K = shp[:5]
         conv3x3_tf32(x, pack3x3(w, 0), y, bias, N, H, W, Cc, K)      # implicit GEMM, shifted TMA boxes per tap
+        return True
+    st = _strided(shp)
+    if st is not None and shp[3] % 32 == 0 and shp[4] % 4 == 0:
+        N, H, W, Cc, K = shp[:5]
+        fs, stride, pad = st
+        wk = pack_filter(w, 0, 9) if fs == 3 else w                  # a 1x1 filter already is [Cout][Cin]
+        check(_f("fedb_conv_tf32")(x.data_ptr(), wk.data_ptr(), y.data_ptr(), 0 if bias is None else bias.data_ptr(),
+                                   N, H, W, Cc, K, fs, stride, pad, 0, current_stream()), "fedb_conv_tf32")
+        _lib.count_launch()
         return True
     if not _is_pointwise(shp):
         return False
@@ -143,6 +176,24 @@ def conv_wgrad(x, dy, dw, db, shp) -> bool:
         _lib.count_launch()
         check(_f("fedb_pack3x3")(dwk.data_ptr(), dw.data_ptr(), K, Cc, 2, current_stream()), "fedb_pack3x3")   # += into OIHW
         _lib.count_launch()
+        if db is not None:
+            db += dy.sum(dim=(0, 2, 3))
+        return True
+    st = _strided(shp)
+    if st is not None and shp[3] % 64 == 0 and shp[4] % 64 == 0:
+        N, H, W, Cc, K = shp[:5]
+        fs, stride, pad = st
+        taps, pix = fs * fs, N * shp[7] * shp[8]
+        tiles = ((K + 127) // 128) * ((Cc + 127) // 128) * taps
+        splits = max(1, min(pix // 256, 444 // max(tiles, 1)))
+        dy16, x16 = cast_bf16(dy), cast_bf16(x)
+        dwk = torch.zeros(K * taps * Cc, dtype=torch.float32, device=x.device) if taps > 1 else dw
+        check(_f("fedb_conv_wgrad_bf16")(dy16.data_ptr(), x16.data_ptr(), dwk.data_ptr(), N, H, W, Cc, K, fs, stride, pad,
+                                         splits, current_stream()), "fedb_conv_wgrad_bf16")
+        _lib.count_launch()
+        if taps > 1:
+            check(_f("fedb_pack_filter")(dwk.data_ptr(), dw.data_ptr(), K, Cc, 2, taps, current_stream()), "fedb_pack_filter")
+            _lib.count_launch()
         if db is not None:
             db += dy.sum(dim=(0, 2, 3))
         return True

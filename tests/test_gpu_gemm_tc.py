@@ -90,3 +90,25 @@ def test_conv3x3_implicit_gemm_fwd_and_dgrad(G, B, C, K, HW):
     ya.backward(g), yb.backward(g.to(DEV))
     torch.testing.assert_close(xb.grad.cpu(), xa.grad, rtol=3e-3, atol=3e-3 * float(xa.grad.abs().max()))
     torch.testing.assert_close(wb.grad.cpu(), wa.grad, rtol=1e-2, atol=1e-2 * float(wa.grad.abs().max()))
+
+
+@pytest.mark.parametrize("B,C,K,HW,fs", [(4, 64, 128, 32, 3), (8, 128, 256, 16, 3), (16, 256, 512, 8, 3), (4, 64, 128, 32, 1),
+                                         (16, 256, 512, 8, 1), (64, 64, 64, 4, 3)])
+def test_strided_conv_on_tensor_cores(G, B, C, K, HW, fs):
+    """Stride-2 3x3 / 1x1 convolutions: the TMA tensor map skips every other input pixel (element strides), so the
+    forward and the weight gradient reuse the implicit-GEMM kernel; the data gradient stays on the generic kernel."""
+    import torch.nn.functional as TF
+    from fedb200.ops import _lib, functional as F
+    torch.manual_seed(5)
+    x = torch.randn(B, C, HW, HW)
+    w = torch.randn(K, C, fs, fs) * 0.05
+    pad = fs // 2
+    xa, wa = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+    xb, wb = x.clone().to(DEV).requires_grad_(True), w.clone().to(DEV).requires_grad_(True)
+    ya = TF.conv2d(xa, wa, None, 2, pad)
+    yb = F.conv2d(xb, wb, None, 2, pad, 1)
+    torch.testing.assert_close(yb.cpu(), ya.detach(), rtol=3e-3, atol=3e-3 * float(ya.detach().abs().max()))
+    g = torch.randn_like(ya)
+    ya.backward(g), yb.backward(g.to(DEV))
+    torch.testing.assert_close(xb.grad.cpu(), xa.grad, rtol=1e-3, atol=1e-4 * float(xa.grad.abs().max()) + 1e-5)
+    torch.testing.assert_close(wb.grad.cpu(), wa.grad, rtol=1e-2, atol=1e-2 * float(wa.grad.abs().max()))
