@@ -192,6 +192,72 @@ int fedb_mc_bind_and_map(fedb_mem_t* mc, const fedb_mem_t* local_mem, int device
 int fedb_fd_serve(const char* path, const int* fds, int n_fds, int n_clients, int timeout_ms);
 int fedb_fd_fetch(const char* path, int* out_fds, int n_fds, int timeout_ms);
 
+/* ------------------------------------------------------------------ tensor-core GEMM / convolution (csrc/gemm_tc.cu)
+ * tcgen05.mma with TMEM accumulators, operands staged by TMA through a 4-stage mbarrier ring, 128x128 output tiles,
+ * optional split-K (fp32 red.add into D).  Everything is row-major fp32 in HBM unless noted; leading dimensions in
+ * elements.  These carry the model zoo's convolutions (reference: src/models/*.py nn.Conv2d / nn.Linear, which the
+ * reference leaves to ATen on the CPU). */
+/* D[M,N] (+)= A[M,K] * B[N,K]^T (+ bias[N]) (relu).  TF32 inputs, fp32 accumulate.  K % 32 == 0, N % 4 == 0. */
+int fedb_gemm_tf32(const float* A, const float* B, float* D, const float* bias, int M, int N, int K, long long lda,
+                   long long ldb, long long ldd, int relu, int splits, int accumulate, void* stream);
+/* D[M,N] (+)= At[K,M]^T * Bt[K,N] with bf16 inputs stored reduction-major (the weight-gradient shape: both operands
+ * are activations [pixels, channels]).  M % 64 == 0, N % 64 == 0, K % 64 == 0. */
+int fedb_gemm_bf16_tn(const uint16_t* At, const uint16_t* Bt, float* D, int M, int N, int K, long long lda, long long ldb,
+                      long long ldd, int splits, int accumulate, void* stream);
+/* Implicit-GEMM convolution on NHWC fp32: Y[N,H/stride,W/stride,Cout] = conv(X[N,H,W,Cin], Wk) (+bias)(relu).
+ * fs/pad: 3/1 or 1/0; stride 1 or 2; output maps must be powers of two with width 2..32; Cin % 32 == 0.
+ * Wk is the filter packed by fedb_pack_filter mode 0 ([Cout][tap][Cin]).  The data gradient of a stride-1 layer is the
+ * same call on dY with the mode-1 packing (flipped taps, channels swapped). */
+int fedb_conv_tf32(const float* X, const float* Wk, float* Y, const float* bias, int N, int H, int W, int Cin, int Cout, int fs,
+                   int stride, int pad, int relu, void* stream);
+int fedb_conv3x3_tf32(const float* X, const float* Wk, float* Y, const float* bias, int N, int H, int W, int Cin, int Cout,
+                      int relu, void* stream);
+/* Weight gradient: dWk[Cout][tap][Cin] += dY^T * shifted(X), bf16 inputs (fedb_cast_bf16), fp32 accumulate, split over
+ * pixels.  dWk must be zeroed by the caller; fedb_pack_filter mode 2 turns it back into OIHW.  Channels % 64 == 0. */
+int fedb_conv_wgrad_bf16(const uint16_t* dY, const uint16_t* X, float* dWk, int N, int H, int W, int Cin, int Cout, int fs,
+                         int stride, int pad, int splits, void* stream);
+int fedb_conv3x3_wgrad_bf16(const uint16_t* dY, const uint16_t* X, float* dWk, int N, int H, int W, int Cin, int Cout,
+                            int splits, void* stream);
+/* mode 0: OIHW -> [K][tap][C]; mode 1: OIHW -> [C][flipped tap][K] (data gradient); mode 2: [K][tap][C] -> OIHW */
+int fedb_pack_filter(const float* w_oihw, float* out, int K, int C, int mode, int taps, void* stream);
+int fedb_pack3x3(const float* w_oihw, float* out, int K, int C, int mode, void* stream);
+int fedb_cast_bf16(const float* src, uint16_t* dst, long long n, void* stream);          /* n % 4 == 0 */
+int fedb_transpose(const float* in, float* out, int rows, int cols, void* stream);        /* out[cols][rows] */
+
+/* ------------------------------------------------------------------ generic NHWC layer kernels (csrc/nn_generic.cu)
+ * Every layer type the model zoo uses (reference: src/models/*.py), for the shapes the tensor-core path does not
+ * take: grouped / depthwise / odd-sized convolutions, batch norm, activations, pooling, channel cat/slice/shuffle,
+ * squeeze-excite gates, drop-connect masks, the classifier.
+ * shape14 = {N,H,W,C,K,R,S,P,Q,stride_h,stride_w,pad_h,pad_w,groups}; shape12 = {N,H,W,C,P,Q,kh,kw,sh,sw,ph,pw}.
+ * act: 0 none, 1 relu, 2 sigmoid, 3 swish. */
+int fedb_nn_weight_transpose(const float* w, float* wt, float* wt2, int K, int Cg, int R, int S, void* stream);
+int fedb_nn_conv_fwd(const float* x, const float* wt, const float* bias, float* y, const int* shape14, void* stream);
+int fedb_nn_conv_dgrad(const float* dy, const float* wt2, float* dx, const int* shape14, void* stream);
+int fedb_nn_conv_wgrad(const float* x, const float* dy, float* dw, float* dbias, const int* shape14, void* stream);
+/* Batch norm over rows = N*H*W of an NHWC tensor.  scratch: caller-owned floats used for the chunked two-pass
+ * reduction (at least 2*C; more chunks = more parallelism).  Training mode updates the running statistics (N4). */
+int fedb_nn_bn_fwd(const float* x, float* y, float* mean, float* invstd, float* run_mean, float* run_var, const float* gamma,
+                   const float* beta, long long rows, int C, float eps, float momentum, int training, int act, float* scratch,
+                   long long scratch_floats, void* stream);
+int fedb_nn_bn_bwd(const float* x, const float* dy, float* dx, const float* mean, const float* invstd, const float* gamma,
+                   const float* beta, float* dgamma, float* dbeta, long long rows, int C, int act, int training, float* scratch,
+                   long long scratch_floats, void* stream);
+int fedb_nn_act_fwd(const float* x, float* y, long long n, int act, void* stream);
+int fedb_nn_act_bwd(const float* x, const float* dy, float* dx, long long n, int act, void* stream);
+int fedb_nn_add_act(const float* a, const float* b, float* y, long long n, int act, void* stream);
+/* mode 0: y = x * s[n][c] (squeeze-excite gate); mode 1: y = x * s[n] (drop-connect / per-sample mask) */
+int fedb_nn_scale(const float* x, const float* s, float* y, long long total, long long per_sample, int C, int mode, void* stream);
+int fedb_nn_scale_bwd_gate(const float* x, const float* dy, float* ds, int HW, int C, int N, void* stream);
+int fedb_nn_bernoulli_mask(float* m, long long n, float keep, uint64_t seed, const uint64_t* ctr_dev, void* stream);
+int fedb_nn_pool_fwd(const float* x, float* y, int* arg, const int* shape12, int is_max, void* stream);
+int fedb_nn_pool_bwd(const float* dy, const int* arg, float* dx, const int* shape12, int is_max, void* stream);
+/* out[row][dst_off + j] (+)= in[row][src(j)]: cat, slice and (shuffle_groups > 1) channel shuffle in one kernel */
+int fedb_nn_channel_copy(const float* in, float* out, long long rows, int Cin, int Cout, int src_off, int dst_off, int width,
+                         int shuffle_groups, int accumulate, void* stream);
+int fedb_nn_linear_fwd(const float* x, const float* W, const float* bias, float* y, int B, int K, int J, int act, void* stream);
+int fedb_nn_linear_bwd(const float* dy, const float* x, const float* W, float* dx, float* dW, float* db, int B, int K, int J,
+                       void* stream);
+
 #ifdef __cplusplus
 }
 #endif
