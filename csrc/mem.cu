@@ -334,3 +334,12 @@ extern "C" int fedb_fd_fetch(const char* path, int* out_fds, int n_fds, int time
     usleep(20000);
   }
 }
+
+// Asynchronous copy between any two of {pinned host, device, peer device} on `stream`.  Exists so that the step
+// engine can put the H2D copies of a round's inputs INSIDE the captured round graph (memcpy nodes on a forked
+// branch, steps depending on their own chunk only) without going through the framework allocator's bookkeeping.
+extern "C" int fedb_copy_async(void* dst, const void* src, uint64_t bytes, void* stream) {
+  if (bytes == 0) return 0;
+  FEDB_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, (cudaStream_t)stream));
+  return 0;
+}

@@ -8,8 +8,10 @@ Two paths, both hand-written kernels end to end:
   ``fedb200.ops.cuda_nn``) under autograd, CE + fused SGD kernels, the step captured in a CUDA
   graph as well.
 
-Per pass the shard's images/labels are copied host->device from pinned memory on a side stream
-(overlapped with the previous work where possible); loss / accuracy counters are read back once.
+Per pass the shard's images/labels are copied host->device from pinned memory IN CHUNKS on a forked
+copy stream; step i only waits for the chunk that holds its batch, so the copy engine runs under the
+step kernels.  The fork/join is captured with the steps: the H2D copies are memcpy nodes of the round
+graph (one graph launch = upload + every step of the pass).  Loss / accuracy counters are read back once.
 """
 from __future__ import annotations
 
@@ -80,26 +82,60 @@ class CudaEngine:
             self._shards[key] = sh
         return sh
 
-    def _upload(self, sh: dict) -> None:
-        """H2D of this pass's inputs from pinned memory (counted by bench.py's e2e figure)."""
+    def _h2d(self, dst: torch.Tensor, src: torch.Tensor, lo: int, hi: int, stream) -> None:
+        """rows [lo, hi) of a pinned host tensor -> the same rows of its device twin, as ONE async copy."""
+        if hi <= lo:
+            return
+        row = src[0].numel() * src.element_size() if src.dim() > 1 else src.element_size()
+        _lib.check(_lib.lib().fedb_copy_async(dst.data_ptr() + lo * row, src.data_ptr() + lo * row, (hi - lo) * row,
+                                              stream.cuda_stream), "fedb_copy_async")
+
+    def _streamed(self, pairs, bounds: List[int], work, upload: bool) -> None:
+        """Runs work(i) for every chunk i = rows [bounds[i], bounds[i+1]) on the current stream.  With ``upload`` the
+        rows of every (device, pinned) pair are first copied H2D chunk by chunk on the copy stream, and work(i) waits
+        for chunk i only.  Works live and under stream capture (fork / join through events)."""
         cur = torch.cuda.current_stream(self.dev)
-        self.copy_stream.wait_stream(cur)
-        with torch.cuda.stream(self.copy_stream):
-            sh["dx"].copy_(sh["hx"], non_blocking=True)
-            sh["dy"].copy_(sh["hy"], non_blocking=True)
-        cur.wait_stream(self.copy_stream)
-        self.h2d_bytes_last = sh["hx"].numel() + sh["hy"].numel() * 8
+        if not upload:
+            for i in range(len(bounds) - 1):
+                work(i)
+            return
+        side = self.copy_stream
+        side.wait_stream(cur)                                         # fork
+        ready = []
+        for i in range(len(bounds) - 1):
+            for d, h in pairs:
+                self._h2d(d, h, bounds[i], bounds[i + 1], side)
+            ev = torch.cuda.Event()
+            ev.record(side)
+            ready.append(ev)
+        for i, ev in enumerate(ready):
+            cur.wait_event(ev)
+            work(i)
+        cur.wait_stream(side)                                         # join
 
     # ------------------------------------------------------------------ training pass
-    def _issue_steps(self, sh: dict) -> None:
-        off = 0
-        for i, n in enumerate(sh["sizes"]):
-            x, y = sh["dx"][off:off + n], sh["dy"][off:off + n]
-            if self.is_lenet:
-                self.plan.train_step(x, y, step_seed=i + 1)
-            else:
-                self._generic_step(x, y, i + 1)
-            off += n
+    COPY_CHUNK_STEPS = 8        # batches per H2D chunk (LeNet: 3 MB ~ 60 us on PCIe 5, one step is ~50 us)
+
+    def _issue_steps(self, sh: dict, upload: bool = False) -> None:
+        sizes = sh["sizes"]
+        offs = [0]
+        for n in sizes:
+            offs.append(offs[-1] + n)
+        g = self.COPY_CHUNK_STEPS
+        first = list(range(0, len(sizes), g))                        # first step of every chunk
+        bounds = [offs[f] for f in first] + [offs[-1]]
+
+        def work(c):
+            for i in range(first[c], min(first[c] + g, len(sizes))):
+                x, y = sh["dx"][offs[i]:offs[i + 1]], sh["dy"][offs[i]:offs[i + 1]]
+                if self.is_lenet:
+                    self.plan.train_step(x, y, step_seed=i + 1)
+                else:
+                    self._generic_step(x, y, i + 1)
+
+        self._streamed([(sh["dx"], sh["hx"]), (sh["dy"], sh["hy"])], bounds, work, upload)
+        if upload:
+            self.h2d_bytes_last = sh["hx"].numel() + sh["hy"].numel() * 8
 
     def _generic_step(self, x_u8, y, seed):
         a, cfg = self.arena, self.cfg
@@ -118,25 +154,28 @@ class CudaEngine:
             sh = self._shard(batches)
             if not sh["sizes"]:
                 return self.TrainStats()
-            if upload:
-                self._upload(sh)
+            upload = bool(upload)
             self.stats.zero_()
             self.seed_dev += 1
             if self.cfg.use_cuda_graph:
-                if sh["graph"] is None:
-                    self._issue_steps(sh)                      # warm-up (also sizes every workspace)
+                graphs = sh["graph"] if sh["graph"] is not None else {}
+                sh["graph"] = graphs
+                if upload not in graphs:
+                    self._issue_steps(sh, upload)              # warm-up (also sizes every workspace)
                     torch.cuda.synchronize(self.dev)
                     g = torch.cuda.CUDAGraph()
                     # the warm-up already trained one pass; that is a real pass, so count it and
-                    # capture the graph for the following rounds
+                    # capture the graph (with or without the H2D branch) for the following rounds
                     with torch.cuda.graph(g, stream=torch.cuda.Stream(device=self.dev)):
-                        self._issue_steps(sh)
-                    sh["graph"] = g
+                        self._issue_steps(sh, upload)
+                    graphs[upload] = g
                 else:
-                    sh["graph"].replay()
+                    graphs[upload].replay()
                     _lib.count_launch(self._launches_per_pass(sh))
+                    if upload:
+                        self.h2d_bytes_last = sh["hx"].numel() + sh["hy"].numel() * 8
             else:
-                self._issue_steps(sh)
+                self._issue_steps(sh, upload)
             self.arena.sgd_steps += len(sh["sizes"])
             return self.read_stats() if sync else None
 
@@ -173,38 +212,42 @@ class CudaEngine:
                     hx, hy = hx.pin_memory(), hy.pin_memory()
                 self._test_host = (hx, hy)
                 self._test_dev = (torch.empty_like(hx, device=self.dev), torch.empty_like(hy, device=self.dev))
+            upload = bool(upload)
             if upload:
-                cur = torch.cuda.current_stream(self.dev)
-                self.copy_stream.wait_stream(cur)
-                with torch.cuda.stream(self.copy_stream):
-                    self._test_dev[0].copy_(self._test_host[0], non_blocking=True)
-                    self._test_dev[1].copy_(self._test_host[1], non_blocking=True)
-                cur.wait_stream(self.copy_stream)
                 self.h2d_bytes_last += self._test_host[0].numel() + self._test_host[1].numel() * 8
             self.eval_stats.zero_()
             n = ds.test_x.shape[0]
+            pairs = list(zip(self._test_dev, self._test_host))
             if self.is_lenet:
-                if self.cfg.use_cuda_graph and self._eval_graph is not None:
-                    self._eval_graph.replay()
+                graphs = self._eval_graph if self._eval_graph is not None else {}
+                self._eval_graph = graphs
+                if self.cfg.use_cuda_graph and upload in graphs:
+                    graphs[upload].replay()
                     _lib.count_launch(2 * ((n + chunk - 1) // chunk))
                 else:
-                    def issue():
-                        for lo in range(0, n, chunk):
-                            self.plan.eval_batch(self._test_dev[0][lo:lo + chunk], self._test_dev[1][lo:lo + chunk],
-                                                 self.eval_stats)
-                    issue()
+                    bounds = list(range(0, n, chunk)) + [n]
+
+                    def work(c):
+                        lo, hi = bounds[c], bounds[c + 1]
+                        self.plan.eval_batch(self._test_dev[0][lo:hi], self._test_dev[1][lo:hi], self.eval_stats)
+
+                    self._streamed(pairs, bounds, work, upload)
                     if self.cfg.use_cuda_graph:
                         torch.cuda.synchronize(self.dev)
                         g = torch.cuda.CUDAGraph()
                         with torch.cuda.graph(g, stream=torch.cuda.Stream(device=self.dev)):
-                            issue()
-                        self._eval_graph = g
+                            self._streamed(pairs, bounds, work, upload)
+                        graphs[upload] = g
             else:
                 bs = self.cfg.test_batch_size
+                bounds = list(range(0, n, bs)) + [n]
+
+                def work(c):
+                    lo, hi = bounds[c], bounds[c + 1]
+                    x = K.prepare_batch(self._test_dev[0][lo:hi], nhwc=True)
+                    out = self.t.model(x)
+                    K.cross_entropy_raw(out.contiguous(), self._test_dev[1][lo:hi], None, None, self.eval_stats)
+
                 with torch.no_grad():
-                    for lo in range(0, n, bs):
-                        x = K.prepare_batch(self._test_dev[0][lo:lo + bs], nhwc=True)
-                        out = self.t.model(x)
-                        K.cross_entropy_raw(out.contiguous(), self._test_dev[1][lo:lo + bs], None, None,
-                                            self.eval_stats)
+                    self._streamed(pairs, bounds, work, upload)
             return self.read_stats("eval") if sync else None
