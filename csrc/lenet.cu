@@ -637,6 +637,200 @@ __global__ void __launch_bounds__(256) update_kernel(UpdateArgs U, Workspace W) 
   apply_update<kApply>(U, dst, g);
 }
 
+// ---------------------------------------------------------------------------------------------- evaluation kernel
+// Forward + loss/correct of kEvalS samples per CTA (the per-round evaluation of the global model on the test set, N8).
+// Compared with one sample per CTA: the classifier weights cross L2 once per kEvalS samples, every phase has kEvalS
+// times more independent work between two barriers (the phases of a single sample are latency-bound), and each
+// conv1 work item produces all six channels from one 6x6x3 patch.
+constexpr int kEvalS = 5;
+struct SmE {
+  static constexpr int img = 0;                                // S x 3072
+  static constexpr int w1 = img + kEvalS * 3072;
+  static constexpr int b1 = w1 + 18 * 28;
+  static constexpr int w2 = b1 + 8;
+  static constexpr int b2 = w2 + 96 * 28;
+  static constexpr int p1 = b2 + 16;                           // S x 1176
+  static constexpr int flat = p1 + kEvalS * NP1;               // S x 400
+  static constexpr int h1 = flat + kEvalS * NFLAT;             // S x 120
+  static constexpr int h2 = h1 + kEvalS * H1;                  // S x 84
+  static constexpr int lg = h2 + kEvalS * H2;                  // S x 16
+  static constexpr int total = lg + kEvalS * 16;
+};
+constexpr size_t kEvalSmemBytes = sizeof(float) * (size_t)SmE::total;
+
+// y[s][j] = act(b[j] + sum_k W[j][k] x[s][k]) for kEvalS samples at once.  LPR lanes share a row (32/LPR rows per warp
+// and iteration): a weight slice is loaded once and used for every sample, and a row sum costs log2(LPR) shuffles.
+template <int K, int J, int LPR, bool kRelu>
+__device__ __forceinline__ void matvec_multi(const float* __restrict__ W, const float* __restrict__ bias,
+                                             const float* __restrict__ x_s, float* __restrict__ y_s, int warp, int lane) {
+  constexpr int K4 = K / 4;
+  constexpr int RPW = 32 / LPR;
+  constexpr int T = (K4 + LPR - 1) / LPR;         // float4 slices per lane
+  constexpr int TC = T < 7 ? T : 7;               // slices in flight (register budget)
+  const int sub = lane / LPR, l = lane % LPR;
+  for (int j0 = warp * RPW; j0 < J; j0 += kWarps * RPW) {
+    const int j = j0 + sub;
+    float acc[kEvalS];
+#pragma unroll
+    for (int smp = 0; smp < kEvalS; ++smp) acc[smp] = 0.f;
+#pragma unroll
+    for (int t0 = 0; t0 < T; t0 += TC) {
+      float4 wv[TC];
+#pragma unroll
+      for (int t = 0; t < TC; ++t) {
+        const int k4 = l + LPR * (t0 + t);
+        wv[t] = (t0 + t < T && j < J && k4 < K4) ? ldg4(W + (size_t)j * K + 4 * k4) : make_float4(0.f, 0.f, 0.f, 0.f);
+      }
+#pragma unroll
+      for (int smp = 0; smp < kEvalS; ++smp)
+#pragma unroll
+        for (int t = 0; t < TC; ++t) {
+          const int k4 = l + LPR * (t0 + t);
+          if (t0 + t < T && k4 < K4) acc[smp] = dot4(wv[t], reinterpret_cast<const float4*>(x_s + smp * K)[k4], acc[smp]);
+        }
+    }
+#pragma unroll
+    for (int smp = 0; smp < kEvalS; ++smp) {
+      float v = acc[smp];
+#pragma unroll
+      for (int o = LPR / 2; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+      if (l == 0 && j < J) {
+        v += __ldg(bias + j);
+        y_s[smp * J + j] = kRelu ? fmaxf(v, 0.f) : v;
+      }
+    }
+  }
+}
+
+__global__ void __launch_bounds__(kThreads, 2) lenet_eval_kernel(const uint8_t* __restrict__ images, Params P,
+                                                               const int64_t* __restrict__ labels, int B,
+                                                               float* __restrict__ loss_rows, float* __restrict__ corr_rows) {
+  extern __shared__ __align__(16) float sm[];
+  float* s_img = sm + SmE::img;
+  float* s_w1 = sm + SmE::w1;
+  float* s_b1 = sm + SmE::b1;
+  float* s_w2 = sm + SmE::w2;
+  float* s_b2 = sm + SmE::b2;
+  float* s_p1 = sm + SmE::p1;
+  float* s_flat = sm + SmE::flat;
+  float* s_h1 = sm + SmE::h1;
+  float* s_h2 = sm + SmE::h2;
+  float* s_lg = sm + SmE::lg;
+  const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
+  const int n0 = blockIdx.x * kEvalS;
+  const int ns = min(kEvalS, B - n0);
+  if (ns <= 0) return;
+
+  // ---- phase 0: conv weights into padded rows; images as 128-bit loads (HWC bytes), scattered into CHW planes
+  {
+    constexpr int NW2V = (NW2 / 4 + kThreads - 1) / kThreads;
+    constexpr int NV = (kEvalS * 192 + kThreads - 1) / kThreads;      // 192 x 16 bytes per image
+    float4 w2v[NW2V];
+    uint4 pv[NV];
+#pragma unroll
+    for (int j = 0; j < NW2V; ++j) {
+      const int i4 = tid + kThreads * j;
+      w2v[j] = i4 < NW2 / 4 ? ldg4(P.w2 + 4 * i4) : make_float4(0.f, 0.f, 0.f, 0.f);
+    }
+    const uint4* src = reinterpret_cast<const uint4*>(images + (size_t)n0 * 3072);
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int i = tid + kThreads * j;
+      pv[j] = i < ns * 192 ? __ldg(src + i) : make_uint4(0u, 0u, 0u, 0u);
+    }
+    const float w1v = tid < NW1 ? __ldg(P.w1 + tid) : 0.f;
+    // samples that do not exist (last CTA) are zero images: their results are never written
+    for (int i = ns * 3072 + tid; i < kEvalS * 3072; i += kThreads) s_img[i] = 0.f;
+#pragma unroll
+    for (int j = 0; j < NV; ++j) {
+      const int i = tid + kThreads * j;
+      if (i < ns * 192) {
+        const int smp = i / 192, b0 = (i % 192) * 16;
+        const unsigned wds[4] = {pv[j].x, pv[j].y, pv[j].z, pv[j].w};
+#pragma unroll
+        for (int k = 0; k < 16; ++k) {
+          const int b = b0 + k, pix = b / 3, c = b - 3 * pix;
+          const float v = (float)((wds[k >> 2] >> (8 * (k & 3))) & 0xffu);
+          const float mean = c == 0 ? 0.4914f : (c == 1 ? 0.4822f : 0.4465f);
+          const float stdv = c == 0 ? 0.2023f : (c == 1 ? 0.1994f : 0.2010f);
+          s_img[smp * 3072 + c * 1024 + pix] = (v / 255.f - mean) / stdv;
+        }
+      }
+    }
+#pragma unroll
+    for (int j = 0; j < NW2V; ++j) {
+      const int i = 4 * (tid + kThreads * j);
+      if (i < NW2) {
+        const float v[4] = {w2v[j].x, w2v[j].y, w2v[j].z, w2v[j].w};
+#pragma unroll
+        for (int q = 0; q < 4; ++q) s_w2[((i + q) / 25) * 28 + (i + q) % 25] = v[q];
+      }
+    }
+    if (tid < NW1) s_w1[(tid / 25) * 28 + tid % 25] = w1v;
+    if (tid < C1) s_b1[tid] = __ldg(P.b1 + tid);
+    if (tid < C2) s_b2[tid] = __ldg(P.b2 + tid);
+  }
+  __syncthreads();
+
+  // ---- phase 1: conv1 + ReLU + pool, (sample, position) per item, all six channels from one patch
+  for (int item = tid; item < kEvalS * 196; item += kThreads) {
+    const int smp = item / 196, pos = item - smp * 196;
+    float o[C1];
+    uint8_t a[C1];
+    conv5_relu_pool<3, C1, 32>(s_img + smp * 3072, s_w1, s_b1, 0, pos / P1, pos % P1, o, a);
+#pragma unroll
+    for (int c = 0; c < C1; ++c) s_p1[smp * NP1 + c * 196 + pos] = o[c];
+  }
+  __syncthreads();
+
+  // ---- phase 2: conv2 + ReLU + pool, (sample, channel pair, position) per item
+  for (int item = tid; item < kEvalS * 200; item += kThreads) {
+    const int smp = item / 200, r = item - smp * 200;
+    const int cg = r / 25, pos = r - cg * 25;
+    float o[2];
+    uint8_t a[2];
+    conv5_relu_pool<C1, 2, P1>(s_p1 + smp * NP1, s_w2, s_b2, 2 * cg, pos / P2, pos % P2, o, a);
+    s_flat[smp * NFLAT + (2 * cg) * 25 + pos] = o[0];
+    s_flat[smp * NFLAT + (2 * cg + 1) * 25 + pos] = o[1];
+  }
+  __syncthreads();
+
+  // ---- phase 3: classifier
+  matvec_multi<NFLAT, H1, 8, true>(P.fw1, P.fb1, s_flat, s_h1, warp, lane);
+  __syncthreads();
+  matvec_multi<H1, H2, 8, true>(P.fw2, P.fb2, s_h1, s_h2, warp, lane);
+  __syncthreads();
+  for (int o = tid; o < kEvalS * NCLS; o += kThreads) {               // 84 x 10: one thread per logit
+    const int smp = o / NCLS, c = o - smp * NCLS;
+    float acc = __ldg(P.fb3 + c);
+#pragma unroll 4
+    for (int k = 0; k < H2; ++k) acc = fmaf(__ldg(P.fw3 + c * H2 + k), s_h2[smp * H2 + k], acc);
+    s_lg[smp * 16 + c] = acc;
+  }
+  __syncthreads();
+
+  // ---- phase 4: loss and correctness, one warp per sample
+  if (warp < ns) {
+    const int n = n0 + warp;
+    const float z = lane < NCLS ? s_lg[warp * 16 + lane] : -INFINITY;
+    float mx = z;
+    int arg = lane < NCLS ? lane : 1 << 20;
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float om = __shfl_xor_sync(0xffffffffu, mx, o);
+      const int oa = __shfl_xor_sync(0xffffffffu, arg, o);
+      if (om > mx || (om == mx && oa < arg)) { mx = om; arg = oa; }
+    }
+    const float se = warp_sum(lane < NCLS ? expf(z - mx) : 0.f);
+    const float lse = logf(se) + mx;
+    if (lane == 0) {
+      const int t = (int)labels[n];
+      loss_rows[n] = lse - s_lg[warp * 16 + t];
+      corr_rows[n] = (arg == t) ? 1.f : 0.f;
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256) stats_kernel(Workspace W, int B, float* __restrict__ stats) {
   __shared__ float sl[256], sc[256];
   float l = 0.f, c = 0.f;
@@ -672,6 +866,7 @@ int ensure_smem() {
     FEDB_CHECK(cudaFuncSetAttribute(lenet_sample_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
     FEDB_CHECK(cudaFuncSetAttribute(lenet_sample_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
     FEDB_CHECK(cudaFuncSetAttribute(lenet_sample_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
+    FEDB_CHECK(cudaFuncSetAttribute(lenet_eval_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kEvalSmemBytes));
     done = true;
   }
   return 0;
@@ -691,6 +886,7 @@ constexpr size_t kFwdSmemBytes = sizeof(float) * (size_t)Sm::fwd_end + 0;   // e
 }  // namespace
 
 extern "C" size_t fedb_lenet_workspace_bytes(int B) { return carve(nullptr, nullptr, B); }
+extern "C" size_t fedb_lenet_eval_bytes(int B) { return 2 * align_up(sizeof(float) * (size_t)B, 256); }
 
 extern "C" int fedb_lenet_train_step(const fedb_lenet_t* net, const uint8_t* images_u8, const int64_t* labels, int B,
                                      void* workspace, float* stats, uint64_t step_seed, void* stream) {
@@ -717,11 +913,15 @@ extern "C" int fedb_lenet_eval(const fedb_lenet_t* net, const uint8_t* images_u8
   FEDB_REQUIRE(net && images_u8 && labels && workspace && B > 0, "fedb_lenet_eval: bad arguments");
   if (int rc = ensure_smem()) return rc;
   if (int rc = check_offsets(net)) return rc;
+  // only the two per-sample rows are needed: [loss B | correct B], fedb_lenet_eval_bytes(B) bytes
   Workspace W;
-  carve(&W, workspace, B);
+  memset(&W, 0, sizeof(W));
+  W.loss_rows = (float*)workspace;
+  W.corr_rows = (float*)((char*)workspace + align_up(sizeof(float) * (size_t)B, 256));
   const Params P = make_params(net);
   cudaStream_t s = (cudaStream_t)stream;
-  lenet_sample_kernel<true, false><<<B, kThreads, kSmemBytes, s>>>(images_u8, P, W, labels, B, 0, 0ull, nullptr, nullptr);
+  FEDB_REQUIRE(((uintptr_t)images_u8 & 15) == 0, "fedb_lenet_eval: images must be 16-byte aligned");
+  lenet_eval_kernel<<<(B + kEvalS - 1) / kEvalS, kThreads, kEvalSmemBytes, s>>>(images_u8, P, labels, B, W.loss_rows, W.corr_rows);
   if (stats) stats_kernel<<<1, 256, 0, s>>>(W, B, stats);
   FEDB_LAUNCH_OK();
   return 0;

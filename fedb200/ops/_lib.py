@@ -72,6 +72,7 @@ _SIGS = {
     "fedb_cross_entropy": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_int, vp]),
     "fedb_prepare_batch": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, C.c_uint64, vp]),
     "fedb_lenet_workspace_bytes": (C.c_size_t, [C.c_int]),
+    "fedb_lenet_eval_bytes": (C.c_size_t, [C.c_int]),
     "fedb_lenet_train_step": (C.c_int, [C.POINTER(LeNetDesc), vp, vp, C.c_int, vp, vp, C.c_uint64, vp]),
     "fedb_lenet_eval": (C.c_int, [C.POINTER(LeNetDesc), vp, vp, C.c_int, vp, vp, vp]),
     "fedb_lenet_forward": (C.c_int, [C.POINTER(LeNetDesc), vp, vp, C.c_int, vp, vp, vp]),

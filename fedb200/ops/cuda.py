@@ -225,6 +225,7 @@ class LeNetPlan:
         self.workspace = None          # training workspace: its address is baked into captured graphs
         self.eval_batch_cap = 0
         self.eval_workspace = None     # separate, so growing it never invalidates a training graph
+        self._aux_cap, self._aux_workspace = 0, None
         self.stats = torch.zeros(4, dtype=torch.float32, device=arena.f32.device)   # loss, correct, samples, steps
         self.reserve(max_batch)
 
@@ -243,11 +244,21 @@ class LeNetPlan:
         _lib.count_launch(2)
 
     def _eval_ws(self, B: int) -> torch.Tensor:
+        """Evaluation only needs the two per-sample rows (loss, correct)."""
         if B > self.eval_batch_cap:
-            self.eval_workspace = torch.empty(lib().fedb_lenet_workspace_bytes(B), dtype=torch.uint8,
+            self.eval_workspace = torch.empty(lib().fedb_lenet_eval_bytes(B), dtype=torch.uint8,
                                               device=self.arena.f32.device)
             self.eval_batch_cap = B
         return self.eval_workspace
+
+    def _aux_ws(self, B: int) -> torch.Tensor:
+        """Full per-sample workspace for forward() / grad(): separate from the training one, whose address is baked
+        into captured graphs."""
+        if B > self._aux_cap:
+            self._aux_workspace = torch.empty(lib().fedb_lenet_workspace_bytes(B), dtype=torch.uint8,
+                                              device=self.arena.f32.device)
+            self._aux_cap = B
+        return self._aux_workspace
 
     def eval_batch(self, images_u8: torch.Tensor, labels: torch.Tensor, stats: Optional[torch.Tensor] = None) -> None:
         B = images_u8.shape[0]
@@ -261,7 +272,7 @@ class LeNetPlan:
         logits = torch.empty(B, 10, dtype=torch.float32, device=images.device)
         u8 = images.dtype == torch.uint8
         check(lib().fedb_lenet_forward(C.byref(self.desc), images.data_ptr() if u8 else 0,
-                                       0 if u8 else images.contiguous().data_ptr(), B, self._eval_ws(B).data_ptr(),
+                                       0 if u8 else images.contiguous().data_ptr(), B, self._aux_ws(B).data_ptr(),
                                        logits.data_ptr(), current_stream()), "fedb_lenet_forward")
         _lib.count_launch(1)
         return logits
@@ -271,7 +282,7 @@ class LeNetPlan:
         dparam = torch.zeros(self.arena.manifest.n_param, dtype=torch.float32, device=images_f32.device)
         loss = torch.zeros(4, dtype=torch.float32, device=images_f32.device)
         check(lib().fedb_lenet_grad(C.byref(self.desc), images_f32.contiguous().data_ptr(), labels.data_ptr(), B,
-                                    self._eval_ws(B).data_ptr(), dparam.data_ptr(), loss.data_ptr(),
+                                    self._aux_ws(B).data_ptr(), dparam.data_ptr(), loss.data_ptr(),
                                     current_stream()), "fedb_lenet_grad")
         _lib.count_launch(2)
         return dparam, loss[0]

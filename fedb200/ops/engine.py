@@ -36,6 +36,7 @@ class CudaEngine:
         self.copy_stream = torch.cuda.Stream(device=self.dev)
         self._shards: Dict[Tuple[int, ...], dict] = {}
         self._test_dev = None
+        self._test_resident = False
         self._eval_graph = None
         self.h2d_bytes_last = 0
         self.d2h_bytes_last = 0
@@ -90,10 +91,11 @@ class CudaEngine:
         _lib.check(_lib.lib().fedb_copy_async(dst.data_ptr() + lo * row, src.data_ptr() + lo * row, (hi - lo) * row,
                                               stream.cuda_stream), "fedb_copy_async")
 
-    def _streamed(self, pairs, bounds: List[int], work, upload: bool) -> None:
+    def _streamed(self, pairs, bounds: List[int], work, upload: bool, tail=None) -> None:
         """Runs work(i) for every chunk i = rows [bounds[i], bounds[i+1]) on the current stream.  With ``upload`` the
         rows of every (device, pinned) pair are first copied H2D chunk by chunk on the copy stream, and work(i) waits
-        for chunk i only.  Works live and under stream capture (fork / join through events)."""
+        for chunk i only; ``tail()`` then queues further copies behind them (they finish under the remaining work).
+        Works live and under stream capture (fork / join through events)."""
         cur = torch.cuda.current_stream(self.dev)
         if not upload:
             for i in range(len(bounds) - 1):
@@ -108,15 +110,30 @@ class CudaEngine:
             ev = torch.cuda.Event()
             ev.record(side)
             ready.append(ev)
+        if tail is not None:
+            tail(side)
         for i, ev in enumerate(ready):
             cur.wait_event(ev)
             work(i)
         cur.wait_stream(side)                                         # join
 
+    def _test_buffers(self):
+        if self._test_dev is None:
+            ds = self.t.dataset
+            hx, hy = ds.test_x.contiguous(), ds.test_y.contiguous()
+            if torch.cuda.is_available():
+                hx, hy = hx.pin_memory(), hy.pin_memory()
+            self._test_host = (hx, hy)
+            self._test_dev = (torch.empty_like(hx, device=self.dev), torch.empty_like(hy, device=self.dev))
+        return list(zip(self._test_dev, self._test_host))
+
+    def _test_bytes(self) -> int:
+        return self._test_host[0].numel() + self._test_host[1].numel() * 8
+
     # ------------------------------------------------------------------ training pass
     COPY_CHUNK_STEPS = 8        # batches per H2D chunk (LeNet: 3 MB ~ 60 us on PCIe 5, one step is ~50 us)
 
-    def _issue_steps(self, sh: dict, upload: bool = False) -> None:
+    def _issue_steps(self, sh: dict, upload: bool = False, with_test: bool = False) -> None:
         sizes = sh["sizes"]
         offs = [0]
         for n in sizes:
@@ -133,9 +150,12 @@ class CudaEngine:
                 else:
                     self._generic_step(x, y, i + 1)
 
-        self._streamed([(sh["dx"], sh["hx"]), (sh["dy"], sh["hy"])], bounds, work, upload)
-        if upload:
-            self.h2d_bytes_last = sh["hx"].numel() + sh["hy"].numel() * 8
+        def tail(side):                                              # the round's test set rides behind the shard
+            for d, h in self._test_buffers():
+                self._h2d(d, h, 0, h.shape[0], side)
+
+        self._streamed([(sh["dx"], sh["hx"]), (sh["dy"], sh["hy"])], bounds, work, upload,
+                       tail if (upload and with_test) else None)
 
     def _generic_step(self, x_u8, y, seed):
         a, cfg = self.arena, self.cfg
@@ -148,34 +168,42 @@ class CudaEngine:
         n = a.manifest.n_param
         K.sgd_step(a.f32[:n], a.grad, a.momentum, cfg.lr, cfg.momentum, cfg.weight_decay)
 
-    def train_pass(self, batches: List[int], upload: bool = True, sync: bool = True):
+    def train_pass(self, batches: List[int], upload: bool = True, sync: bool = True, with_test: bool = False):
+        """One local pass over the shard.  ``upload``: this pass's inputs are copied from pinned memory inside the
+        pass (chunked, overlapped); ``with_test``: the test set of the evaluation that follows the aggregation is
+        copied in the same pass, behind the shard, so that the next ``eval_pass(upload=True)`` finds it resident."""
         with torch.cuda.device(self.dev):
             self.t.model.train()
             sh = self._shard(batches)
             if not sh["sizes"]:
                 return self.TrainStats()
             upload = bool(upload)
+            with_test = bool(with_test) and upload
+            key = (upload, with_test)
             self.stats.zero_()
             self.seed_dev += 1
             if self.cfg.use_cuda_graph:
                 graphs = sh["graph"] if sh["graph"] is not None else {}
                 sh["graph"] = graphs
-                if upload not in graphs:
-                    self._issue_steps(sh, upload)              # warm-up (also sizes every workspace)
+                if key not in graphs:
+                    self._issue_steps(sh, upload, with_test)   # warm-up (also sizes every workspace)
                     torch.cuda.synchronize(self.dev)
                     g = torch.cuda.CUDAGraph()
                     # the warm-up already trained one pass; that is a real pass, so count it and
                     # capture the graph (with or without the H2D branch) for the following rounds
                     with torch.cuda.graph(g, stream=torch.cuda.Stream(device=self.dev)):
-                        self._issue_steps(sh, upload)
-                    graphs[upload] = g
+                        self._issue_steps(sh, upload, with_test)
+                    graphs[key] = g
                 else:
-                    graphs[upload].replay()
+                    graphs[key].replay()
                     _lib.count_launch(self._launches_per_pass(sh))
-                    if upload:
-                        self.h2d_bytes_last = sh["hx"].numel() + sh["hy"].numel() * 8
             else:
-                self._issue_steps(sh, upload)
+                self._issue_steps(sh, upload, with_test)
+            if upload:
+                self.h2d_bytes_last = sh["hx"].numel() + sh["hy"].numel() * 8
+                if with_test:
+                    self.h2d_bytes_last += self._test_bytes()
+            self._test_resident = with_test
             self.arena.sgd_steps += len(sh["sizes"])
             return self.read_stats() if sync else None
 
@@ -203,41 +231,40 @@ class CudaEngine:
 
     # ------------------------------------------------------------------ evaluation pass
     def eval_pass(self, upload: bool = True, sync: bool = True, chunk: int = 2000):
+        """Evaluation of the current model on the whole test set.  ``upload`` copies the test set H2D first, in chunks
+        that overlap the evaluation kernels - unless the preceding ``train_pass(with_test=True)`` of this round already
+        brought it over, in which case the pass is a single launch over the resident copy."""
         with torch.cuda.device(self.dev):
             self.t.model.eval()
             ds = self.t.dataset
-            if self._test_dev is None:
-                hx, hy = ds.test_x.contiguous(), ds.test_y.contiguous()
-                if torch.cuda.is_available():
-                    hx, hy = hx.pin_memory(), hy.pin_memory()
-                self._test_host = (hx, hy)
-                self._test_dev = (torch.empty_like(hx, device=self.dev), torch.empty_like(hy, device=self.dev))
-            upload = bool(upload)
-            if upload:
-                self.h2d_bytes_last += self._test_host[0].numel() + self._test_host[1].numel() * 8
+            pairs = self._test_buffers()
+            copy = bool(upload) and not self._test_resident
+            self._test_resident = False
+            if copy:
+                self.h2d_bytes_last += self._test_bytes()
             self.eval_stats.zero_()
             n = ds.test_x.shape[0]
-            pairs = list(zip(self._test_dev, self._test_host))
             if self.is_lenet:
+                step = chunk if copy else n
+                bounds = list(range(0, n, step)) + [n]
+
+                def work(c):
+                    lo, hi = bounds[c], bounds[c + 1]
+                    self.plan.eval_batch(self._test_dev[0][lo:hi], self._test_dev[1][lo:hi], self.eval_stats)
+
                 graphs = self._eval_graph if self._eval_graph is not None else {}
                 self._eval_graph = graphs
-                if self.cfg.use_cuda_graph and upload in graphs:
-                    graphs[upload].replay()
-                    _lib.count_launch(2 * ((n + chunk - 1) // chunk))
+                if self.cfg.use_cuda_graph and copy in graphs:
+                    graphs[copy].replay()
+                    _lib.count_launch(2 * (len(bounds) - 1))
                 else:
-                    bounds = list(range(0, n, chunk)) + [n]
-
-                    def work(c):
-                        lo, hi = bounds[c], bounds[c + 1]
-                        self.plan.eval_batch(self._test_dev[0][lo:hi], self._test_dev[1][lo:hi], self.eval_stats)
-
-                    self._streamed(pairs, bounds, work, upload)
+                    self._streamed(pairs, bounds, work, copy)
                     if self.cfg.use_cuda_graph:
                         torch.cuda.synchronize(self.dev)
                         g = torch.cuda.CUDAGraph()
                         with torch.cuda.graph(g, stream=torch.cuda.Stream(device=self.dev)):
-                            self._streamed(pairs, bounds, work, upload)
-                        graphs[upload] = g
+                            self._streamed(pairs, bounds, work, copy)
+                        graphs[copy] = g
             else:
                 bs = self.cfg.test_batch_size
                 bounds = list(range(0, n, bs)) + [n]
@@ -249,5 +276,5 @@ class CudaEngine:
                     K.cross_entropy_raw(out.contiguous(), self._test_dev[1][lo:hi], None, None, self.eval_stats)
 
                 with torch.no_grad():
-                    self._streamed(pairs, bounds, work, upload)
+                    self._streamed(pairs, bounds, work, copy)
             return self.read_stats("eval") if sync else None

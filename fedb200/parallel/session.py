@@ -57,7 +57,7 @@ class GpuFederation:
         live = self.group.live
         batches = self.trainer.shard(live.index(self.rank), self.world) if self.rank in live else []
         self.group.before_local_pass()
-        self.engine.train_pass(batches, upload=upload, sync=False)
+        self.engine.train_pass(batches, upload=upload, sync=False, with_test=self.evaluate)
         self.group.aggregate()
         if self.evaluate:
             self.engine.eval_pass(upload=upload, sync=False)
@@ -96,7 +96,7 @@ class PeerWorker:
             fed.group.set_live(live)
         batches = fed.trainer.shard(rank, world)
         fed.group.before_local_pass()
-        st = fed.engine.train_pass(batches, upload=True, sync=True)
+        st = fed.engine.train_pass(batches, upload=True, sync=True, with_test=True)
         fed.group.aggregate()
         return st
 

@@ -244,15 +244,17 @@ def test_lenet_train_steps_match_torch_sgd(K):
     assert abs(float(st[0]) - tot_loss) < 1e-3 and int(st[1]) == tot_correct and int(st[2]) == 384 and int(st[3]) == 3
 
 
-def test_lenet_eval_counts(K):
+@pytest.mark.parametrize("n", [1000, 503, 3])
+def test_lenet_eval_counts(K, n):
+    """The evaluation kernel packs five samples per CTA: sizes that are / are not multiples of five, and a lone CTA."""
     ref, _, arena = _lenet_pair(3)
     plan = K.LeNetPlan(arena)
-    ds = D.synthetic_cifar(8, 1000, seed=4)
+    ds = D.synthetic_cifar(8, n, seed=4)
     stats = torch.zeros(4, device=DEV)
     plan.eval_batch(ds.test_x.to(DEV), ds.test_y.to(DEV), stats)
     with torch.no_grad():
         out = ref(D.normalize_batch(ds.test_x))
-    assert int(stats[1]) == int((out.argmax(1) == ds.test_y).sum()) and int(stats[2]) == 1000
+    assert int(stats[1]) == int((out.argmax(1) == ds.test_y).sum()) and int(stats[2]) == n
     assert abs(float(stats[0]) - float(torch.nn.functional.cross_entropy(out, ds.test_y))) < 1e-4
 
 
