@@ -27,6 +27,10 @@ constexpr int H1 = 120, H2 = 84, NCLS = 10;
 constexpr int NW1 = C1 * 3 * 25, NW2 = C2 * C1 * 25;   // 450, 2400
 constexpr int CONV_PART = 2880;                // [w1 450 | b1 6 | w2 2400 | b2 16] padded
 constexpr int OFF_B1 = 450, OFF_W2 = 456, OFF_B2 = 2856;
+// Image planes of the TRAINING kernel are padded in shared memory: row stride 38, plane stride 1218.  The weight
+// gradient of conv1 reads img[ci][y+r][x+s] with lanes spread over (r, ci): banks 6r + 2ci are all distinct, whereas
+// the natural 32/1024 strides put every (r, ci) of a tap column into the same bank (measured: 35 % of the kernel).
+constexpr int IW = 38, IPLANE = 32 * IW + 2;
 constexpr int kThreads = 512;          // sample kernel: 16 warps per sample keep the issue slots fed
 constexpr int kWarps = kThreads / 32;
 
@@ -68,8 +72,8 @@ struct Params {
 
 // shared-memory plan of the sample kernel (floats)
 struct Sm {
-  static constexpr int img = 0;                       // 3072
-  static constexpr int w1 = img + 3072;               // 18 filters x 28 (25 used: rows padded for 128-bit loads)
+  static constexpr int img = 0;                       // 3 padded planes
+  static constexpr int w1 = img + 3 * IPLANE + 2;     // 18 filters x 28 (25 used: rows padded for 128-bit loads)
   static constexpr int b1 = w1 + 18 * 28;             // 8
   static constexpr int w2 = b1 + 8;                   // 96 filters x 28
   static constexpr int b2 = w2 + 96 * 28;             // 16
@@ -87,8 +91,8 @@ struct Sm {
   static constexpr int g2 = fwd_end;                  // 400
   static constexpr int g1 = g2 + NFLAT;               // 1176
   static constexpr int dp1 = g1 + NP1;                // 8 x 1176 (also the 8 x 400 partials of d(flat), and 2 x 120 of dh1)
-  static constexpr int half = dp1 + 8 * NP1;          // 4 x 450
-  static constexpr int pos2 = half + 4 * NW1;         // 400 ints
+  static constexpr int half = dp1 + 8 * NP1;          // 5 x 450
+  static constexpr int pos2 = half + 5 * NW1 + 2;     // 400 ints
   static constexpr int pos1 = pos2 + NFLAT;           // 1176 ints
   static constexpr int idx1 = pos1 + NP1;             // 1176 bytes = 294 words
   static constexpr int idx2 = idx1 + 296;             // 400 bytes = 100 words
@@ -98,7 +102,7 @@ constexpr size_t kSmemBytes = sizeof(float) * (size_t)Sm::total;
 
 // conv (valid, 5x5) + ReLU + 2x2 max-pool for one output position and CO output channels,
 // input planes in shared memory.  Returns pooled values and the argmax slot (0..3).
-template <int CI, int CO_PER_THREAD, int IN_W>
+template <int CI, int CO_PER_THREAD, int IN_W, int PLANE = IN_W * IN_W>
 __device__ __forceinline__ void conv5_relu_pool(const float* __restrict__ in, const float* __restrict__ w,
                                                 const float* __restrict__ bias, int co0, int py, int px,
                                                 float (&out)[CO_PER_THREAD], uint8_t (&arg)[CO_PER_THREAD]) {
@@ -112,7 +116,7 @@ __device__ __forceinline__ void conv5_relu_pool(const float* __restrict__ in, co
 #pragma unroll 1
   for (int ci = 0; ci < CI; ++ci) {
     float patch[6][6];
-    const float* src = in + ci * IN_W * IN_W + y0 * IN_W + x0;     // even offset: rows are 8-byte aligned
+    const float* src = in + ci * PLANE + y0 * IN_W + x0;           // even offset: rows are 8-byte aligned
 #pragma unroll
     for (int r = 0; r < 6; ++r)
 #pragma unroll
@@ -207,7 +211,10 @@ __global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* _
                                                                const int64_t* __restrict__ labels, int B, int augment,
                                                                unsigned long long seed,
                                                                const unsigned long long* __restrict__ seed_dev,
-                                                               float* __restrict__ logits_out) {
+                                                               float* __restrict__ logits_out,
+                                                               long long* __restrict__ phase_clk = nullptr) {
+  // phase_clk (debug, normally null): CTA 0 stamps clock64() at every phase boundary (tools/prof_lenet.py --phases)
+#define FEDB_PHASE_MARK(i) do { if (phase_clk != nullptr && blockIdx.x == 0 && threadIdx.x == 0) phase_clk[i] = clock64(); } while (0)
   extern __shared__ __align__(16) float sm[];
   float* s_img = sm + Sm::img;
   float* s_w1 = sm + Sm::w1;
@@ -225,6 +232,7 @@ __global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* _
   const int n = blockIdx.x, tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   if (n >= B) return;
 
+  FEDB_PHASE_MARK(0);
   // ------------------------------------------------------------------ phase 0: stage image + conv weights
   {
     constexpr int NW2V = (NW2 / 4 + kThreads - 1) / kThreads;     // float4 loads of conv2.weight per thread
@@ -253,7 +261,8 @@ __global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* _
         const int c = (tid + kThreads * j) >> 10;
         const float mean = c == 0 ? 0.4914f : (c == 1 ? 0.4822f : 0.4465f);
         const float stdv = c == 0 ? 0.2023f : (c == 1 ? 0.1994f : 0.2010f);
-        s_img[tid + kThreads * j] = (px[j] / 255.f - mean) / stdv;
+        const int e = tid + kThreads * j;
+        s_img[c * IPLANE + ((e >> 5) & 31) * IW + (e & 31)] = (px[j] / 255.f - mean) / stdv;
       }
     } else {
       const float* img = (const float*)images + (size_t)n * 3072;
@@ -261,8 +270,14 @@ __global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* _
 #pragma unroll
       for (int j = 0; j < 2; ++j) v[j] = tid + kThreads * j < 768 ? ldg4(img + 4 * (tid + kThreads * j)) : make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-      for (int j = 0; j < 2; ++j)
-        if (tid + kThreads * j < 768) reinterpret_cast<float4*>(s_img)[tid + kThreads * j] = v[j];
+      for (int j = 0; j < 2; ++j) {
+        const int e = 4 * (tid + kThreads * j);                  // 4 consecutive pixels of one row
+        if (e < 3072) {
+          float* d = s_img + (e >> 10) * IPLANE + ((e >> 5) & 31) * IW + (e & 31);
+          reinterpret_cast<float2*>(d)[0] = make_float2(v[j].x, v[j].y);
+          reinterpret_cast<float2*>(d)[1] = make_float2(v[j].z, v[j].w);
+        }
+      }
     }
 #pragma unroll
     for (int j = 0; j < NW2V; ++j) {
@@ -279,13 +294,14 @@ __global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* _
   }
   __syncthreads();
 
+  FEDB_PHASE_MARK(1);
   // ------------------------------------------------------------------ phase 1: conv1 + ReLU + pool
   if (tid < 2 * P1 * P1) {                     // (position, half of the output channels) per thread
     const int pos = tid % 196, hf = tid / 196;
     const int py = pos / P1, px = pos % P1;
     float o[3];
     uint8_t a[3];
-    conv5_relu_pool<3, 3, 32>(s_img, s_w1, s_b1, 3 * hf, py, px, o, a);
+    conv5_relu_pool<3, 3, IW, IPLANE>(s_img, s_w1, s_b1, 3 * hf, py, px, o, a);
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
       s_p1[(3 * hf + c) * 196 + pos] = o[c];
@@ -294,18 +310,23 @@ __global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* _
   }
   __syncthreads();
 
+  FEDB_PHASE_MARK(2);
   // ------------------------------------------------------------------ phase 2: conv2 + ReLU + pool
-  if (tid < NFLAT) {                           // (position, output channel) per thread
-    const int pos = tid % 25, co = tid / 25;
+  if (tid < NFLAT / 2) {                       // (position, pair of output channels) per thread: the phase is bound
+    const int pos = tid % 25, cg = tid / 25;   // by shared-memory loads, and a patch now feeds two channels
     const int py = pos / P2, px = pos % P2;
-    float o[1];
-    uint8_t a[1];
-    conv5_relu_pool<C1, 1, P1>(s_p1, s_w2, s_b2, co, py, px, o, a);
-    s_flat[tid] = o[0];                        // co * 25 + pos: NCHW flatten order == fc1's input order
-    s_idx2[tid] = a[0];
+    float o[2];
+    uint8_t a[2];
+    conv5_relu_pool<C1, 2, P1>(s_p1, s_w2, s_b2, 2 * cg, py, px, o, a);
+#pragma unroll
+    for (int c = 0; c < 2; ++c) {
+      s_flat[(2 * cg + c) * 25 + pos] = o[c];  // co * 25 + pos: NCHW flatten order == fc1's input order
+      s_idx2[(2 * cg + c) * 25 + pos] = a[c];
+    }
   }
   __syncthreads();
 
+  FEDB_PHASE_MARK(3);
   // ------------------------------------------------------------------ phase 3: classifier forward
   matvec<NFLAT, H1, 5, true>(P.fw1, P.fb1, s_flat, s_h1, warp, lane);
   __syncthreads();
@@ -314,6 +335,7 @@ __global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* _
   matvec<H2, NCLS, 1, false>(P.fw3, P.fb3, s_h2, s_lg, warp, lane);
   __syncthreads();
 
+  FEDB_PHASE_MARK(4);
   // ------------------------------------------------------------------ phase 4: softmax cross-entropy
   if (warp == 0) {
     const float z = lane < NCLS ? s_lg[lane] : -INFINITY;
@@ -351,6 +373,7 @@ __global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* _
   int* s_pos2 = reinterpret_cast<int*>(sm + Sm::pos2);
   int* s_pos1 = reinterpret_cast<int*>(sm + Sm::pos1);
 
+  FEDB_PHASE_MARK(5);
   // ------------------------------------------------------------------ phase 5: classifier backward (data path)
   // dh2[j] = relu'(h2[j]) * sum_c dlg[c] W3[c][j]
   if (tid < H2) {
@@ -378,6 +401,7 @@ __global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* _
   if (tid < H1)
     s_dh1[tid] = s_h1[tid] > 0.f ? ((s_dp1[tid] + s_dp1[H1 + tid]) + (s_dp1[2 * H1 + tid] + s_dp1[3 * H1 + tid])) : 0.f;
   __syncthreads();
+  FEDB_PHASE_MARK(6);
   // dflat[k] = sum_j dh1[j] W1[j][k]: warps 0..14 own rows [8w, 8w+8), lanes own float4 slices of k
   if (warp < 15) {
     float4 acc[4];
@@ -422,12 +446,14 @@ __global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* _
   }
   __syncthreads();
 
+  FEDB_PHASE_MARK(7);
   // publish the rows kernel U needs (coalesced)
   for (int e = tid; e < NFLAT; e += kThreads) W.flat[(size_t)n * NFLAT + e] = s_flat[e];
   if (tid < H1) { W.h1[(size_t)n * H1 + tid] = s_h1[tid]; W.dh1[(size_t)n * H1 + tid] = s_dh1[tid]; }
   if (tid < H2) { W.h2[(size_t)n * H2 + tid] = s_h2[tid]; W.dh2[(size_t)n * H2 + tid] = s_dh2[tid]; }
   if (tid < NCLS) W.dlogits[(size_t)n * NCLS + tid] = s_dlg[tid];
 
+  FEDB_PHASE_MARK(8);
   // ------------------------------------------------------------------ phase 6: feature extractor backward
   for (int e = tid; e < 8 * NP1; e += kThreads) s_dp1[e] = 0.f;
   for (int e = tid; e < NFLAT; e += kThreads) {
@@ -438,21 +464,30 @@ __global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* _
   }
   __syncthreads();
 
+  FEDB_PHASE_MARK(9);
   float* part = W.conv_part + (size_t)n * CONV_PART;
   // conv2 weight gradient: dW2[co][ci][r][s] = sum_pos g2[co][pos] * p1[ci][y+r][x+s]
-  for (int e = tid; e < NW2; e += kThreads) {
-    const int s = e % 5, r = (e / 5) % 5, ci = (e / 25) % C1, co = e / 150;
-    const float* src = s_p1 + ci * 196 + r * 14 + s;
-    float acc = 0.f;
+  // one thread per (co, ci, filter row): the five taps of the row share the loads of g2 and of the arg-max offset
+  if (tid < NW2 / 5) {
+    const int r = tid % 5, ci = (tid / 5) % C1, co = tid / 30;
+    const float* src = s_p1 + ci * 196 + r * 14;
+    float acc[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll 5
-    for (int pos = 0; pos < 25; ++pos) acc = fmaf(s_g2[co * 25 + pos], src[s_pos2[co * 25 + pos]], acc);
-    part[OFF_W2 + e] = acc;
+    for (int pos = 0; pos < 25; ++pos) {
+      const float g = s_g2[co * 25 + pos];
+      const float* q = src + s_pos2[co * 25 + pos];
+#pragma unroll
+      for (int t = 0; t < 5; ++t) acc[t] = fmaf(g, q[t], acc[t]);
+    }
+#pragma unroll
+    for (int t = 0; t < 5; ++t) part[OFF_W2 + tid * 5 + t] = acc[t];
   }
   if (tid < C2) {
     float acc = 0.f;
     for (int pos = 0; pos < 25; ++pos) acc += s_g2[tid * 25 + pos];
     part[OFF_B2 + tid] = acc;
   }
+  FEDB_PHASE_MARK(10);
   // conv2 data gradient, sparse scatter: each non-zero of d(conv2 out) touches a 5x5 patch of every input channel.
   // Warps w and w+8 share accumulator copy w%8 but own disjoint input channels (0-2 / 3-5); each copy's owners
   // walk non-zeros w%8, w%8+8, ...; lanes are the 25 taps.
@@ -475,6 +510,7 @@ __global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* _
     }
   }
   __syncthreads();
+  FEDB_PHASE_MARK(11);
   for (int e = tid; e < NP1; e += kThreads) {
     float d = 0.f;
 #pragma unroll
@@ -482,28 +518,48 @@ __global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* _
     const int k = s_idx1[e];
     const int pos = e % 196, py = pos / 14, px = pos % 14;
     s_g1[e] = s_p1[e] > 0.f ? d : 0.f;
-    s_pos1[e] = (2 * py + (k >> 1)) * 32 + (2 * px + (k & 1));       // offset of the arg-max inside a 32x32 image plane
+    s_pos1[e] = (2 * py + (k >> 1)) * IW + (2 * px + (k & 1));       // offset of the arg-max inside a padded image plane
   }
   __syncthreads();
-  // conv1 weight gradient: 450 outputs, each split in four quarters of the 196 positions so all threads have work
-  for (int e = tid; e < 4 * NW1; e += kThreads) {
-    const int hf = e / NW1, o = e % NW1;
-    const int s = o % 5, r = (o / 5) % 5, ci = (o / 25) % 3, co = o / 75;
-    const float* src = s_img + ci * 1024 + r * 32 + s;
-    float acc = 0.f;
-    const int lo = hf * 49;
-#pragma unroll 7
-    for (int pos = lo; pos < lo + 49; ++pos) acc = fmaf(s_g1[co * 196 + pos], src[s_pos1[co * 196 + pos]], acc);
-    s_half[e] = acc;
+  FEDB_PHASE_MARK(12);
+  // conv1 weight gradient: one thread per (fifth of the positions, co, ci, filter row); the five taps of the row
+  // share g1 and the arg-max offset, which come in as 128-bit loads for four positions at a time.  Lanes run over
+  // (r, ci) first: with the padded planes their addresses fall into distinct banks.
+  if (tid < 5 * 90) {
+    const int o = tid % 90, q5 = tid / 90;
+    const int r = o % 5, ci = (o / 5) % 3, co = o / 15;
+    const float* src = s_img + ci * IPLANE + r * IW;
+    const int lo = q5 * 40, n4 = q5 < 4 ? 10 : 9;                   // 4 x 40 + 36 positions
+    const float4* g4 = reinterpret_cast<const float4*>(s_g1 + co * 196 + lo);
+    const int4* p4 = reinterpret_cast<const int4*>(s_pos1 + co * 196 + lo);
+    float acc[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
+#pragma unroll 2
+    for (int i = 0; i < n4; ++i) {
+      const float4 g = g4[i];
+      const int4 pp = p4[i];
+      const float gv[4] = {g.x, g.y, g.z, g.w};
+      const int pv[4] = {pp.x, pp.y, pp.z, pp.w};
+#pragma unroll
+      for (int k = 0; k < 4; ++k) {
+        const float* q = src + pv[k];
+#pragma unroll
+        for (int t = 0; t < 5; ++t) acc[t] = fmaf(gv[k], q[t], acc[t]);
+      }
+    }
+#pragma unroll
+    for (int t = 0; t < 5; ++t) s_half[q5 * NW1 + o * 5 + t] = acc[t];   // o * 5 + t == co*75 + ci*25 + r*5 + s
   }
   __syncthreads();
+  FEDB_PHASE_MARK(13);
   for (int o = tid; o < NW1; o += kThreads)
-    part[o] = (s_half[o] + s_half[NW1 + o]) + (s_half[2 * NW1 + o] + s_half[3 * NW1 + o]);
+    part[o] = ((s_half[o] + s_half[NW1 + o]) + (s_half[2 * NW1 + o] + s_half[3 * NW1 + o])) + s_half[4 * NW1 + o];
   if (tid < C1) {
     float acc = 0.f;
     for (int pos = 0; pos < 196; ++pos) acc += s_g1[tid * 196 + pos];
     part[OFF_B1 + tid] = acc;
   }
+  FEDB_PHASE_MARK(14);
+#undef FEDB_PHASE_MARK
 }
 
 // ------------------------------------------------------------------------------------ kernel U
@@ -518,22 +574,26 @@ struct UpdateArgs {
 };
 
 // Block roles (grid = kUpdateBlocks):
-//   [0, 60)   fc1.weight tiles: 8 rows (j) x 128 cols (k) of dW1 = dh1^T flat      (15 x 4 tiles)
-//   [60, 71)  fc2.weight tiles: 8 x 128 of dW2 = dh2^T h1                           (11 x 1)
-//   [71, 73)  fc3.weight tiles: 8 x 128 of dW3 = dlogits^T h2                       (2 x 1)
-//   [73, 86)  one thread per remaining parameter: fc biases (column sums of dout) and the conv partial sums
-// Weight tiles stream the batch through shared memory in chunks of 32 samples (next chunk prefetched into
-// registers while the current one is consumed), every thread owns 1 row x 4 consecutive columns, and the batch
-// is summed in sample order - fixed, so the step is reproducible.  The SGD update (K10) is the epilogue.
-constexpr int kUpdateBlocks = 86;
+//   [0, 60)    fc1.weight tiles: 8 rows (j) x 128 cols (k) of dW1 = dh1^T flat      (15 x 4 tiles)
+//   [60, 71)   fc2.weight tiles: 8 x 128 of dW2 = dh2^T h1                           (11 x 1)
+//   [71, 73)   fc3.weight tiles: 8 x 128 of dW3 = dlogits^T h2                       (2 x 1)
+//   [73, 170)  32 of the remaining parameters per block (fc biases = column sums of dout, conv partial sums):
+//              warp w sums samples [16w, 16w+16) of a 128-sample chunk, lanes are parameters (coalesced rows)
+//   170        loss / accuracy counters (K13)
+// The whole kernel is a handful of dependent memory round trips, so every block issues ALL loads of a 128-sample
+// chunk (and of the parameter / momentum words it will update) before it touches the first one.  Summation orders
+// are fixed (sample order inside a group, groups in order), so a step is reproducible run to run.
 constexpr int kRestParams = H1 + H2 + NCLS + NW1 + C1 + NW2 + C2;   // 3086
+constexpr int kRestBlocks = (kRestParams + 31) / 32;                 // 97
+constexpr int kUpdateBlocks = 73 + kRestBlocks + 1;
+constexpr int kUChunk = 128;                                         // samples staged per pass
+constexpr size_t kUpdateSmemBytes = sizeof(float) * (size_t)(kUChunk * 128 + kUChunk * 8);
 
 template <bool kApply>
-__device__ __forceinline__ void apply_update(const UpdateArgs& U, long long dst, float g) {
+__device__ __forceinline__ void apply_update(const UpdateArgs& U, long long dst, float g, float p, float m) {
   if constexpr (kApply) {
-    const float p = U.param[dst];
     const float g1 = __fadd_rn(g, __fmul_rn(U.wd, p));
-    const float v = __fadd_rn(__fmul_rn(U.mu, U.momentum[dst]), g1);
+    const float v = __fadd_rn(__fmul_rn(U.mu, m), g1);
     U.momentum[dst] = v;
     U.param[dst] = __fadd_rn(p, __fmul_rn(-U.lr, v));
   } else {
@@ -543,11 +603,12 @@ __device__ __forceinline__ void apply_update(const UpdateArgs& U, long long dst,
 
 template <bool kApply>
 __global__ void __launch_bounds__(256) update_kernel(UpdateArgs U, Workspace W) {
-  __shared__ __align__(16) float s_in[32 * 128];
-  __shared__ float s_dout[32 * 8];
+  extern __shared__ __align__(16) float usm[];
   const int B = U.B, b = blockIdx.x, tid = threadIdx.x;
 
   if (b < 73) {
+    float* s_in = usm;                                          // [128 samples][128 cols]
+    float* s_dout = usm + kUChunk * 128;                        // [128 samples][8 rows]
     int J, K, jt, kt;
     const float *dout, *in;
     long long off;
@@ -556,85 +617,119 @@ __global__ void __launch_bounds__(256) update_kernel(UpdateArgs U, Workspace W) 
     else             { J = NCLS; K = H2; jt = b - 71; kt = 0; dout = W.dlogits; in = W.h2; off = U.off[8]; }
     const int tj = tid >> 5, tk4 = tid & 31;
     const int j = jt * 8 + tj, k = kt * 128 + tk4 * 4;          // this thread's outputs: (j, k..k+3)
-    // loader roles: tile of `in` is 32 samples x 128 cols = 1024 float4 (4 per thread); tile of dout is 32 x 8
-    const int lk4 = tid & 31, ls = tid >> 5;                    // float4 column, sample row (+8 per step)
-    const int dj = tid & 7, ds = tid >> 3;                      // dout: column, sample row
+    const bool mine = j < J && k < K;
+    const long long dst = off + (long long)j * K + k;           // multiple of 4 floats: segments are 32-float aligned
+    float4 p4 = make_float4(0.f, 0.f, 0.f, 0.f), m4 = p4;
+    if (kApply && mine) {
+      p4 = *reinterpret_cast<const float4*>(U.param + dst);
+      m4 = *reinterpret_cast<const float4*>(U.momentum + dst);
+    }
+    // loader roles: float4 column lk4 of sample rows ls, ls+8, ...; dout element (ds, dj)
+    const int lk4 = tid & 31, ls = tid >> 5;
+    const int dj = tid & 7, ds = tid >> 3;
     const bool lk_ok = kt * 128 + lk4 * 4 < K;                  // K is a multiple of 4
     const bool dj_ok = jt * 8 + dj < J;
-    float4 pre_in[4];
-    float pre_d;
-    auto fetch = [&](int s0) {
+    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
+    for (int s0 = 0; s0 < B; s0 += kUChunk) {
+      float4 vin[16];
+      float vd[4];
 #pragma unroll
-      for (int r = 0; r < 4; ++r) {
-        const int s = s0 + ls + 8 * r;
-        pre_in[r] = (lk_ok && s < B) ? __ldg(reinterpret_cast<const float4*>(in + (size_t)s * K + kt * 128) + lk4)
+      for (int r = 0; r < 16; ++r) {
+        const int sidx = s0 + ls + 8 * r;
+        vin[r] = (lk_ok && sidx < B) ? __ldg(reinterpret_cast<const float4*>(in + (size_t)sidx * K + kt * 128) + lk4)
                                      : make_float4(0.f, 0.f, 0.f, 0.f);
       }
-      const int s = s0 + ds;
-      pre_d = (dj_ok && s < B) ? __ldg(dout + (size_t)s * J + jt * 8 + dj) : 0.f;
-    };
-    float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
-    fetch(0);
-    for (int s0 = 0; s0 < B; s0 += 32) {
-      __syncthreads();                                          // previous chunk fully consumed
 #pragma unroll
-      for (int r = 0; r < 4; ++r) reinterpret_cast<float4*>(s_in)[(ls + 8 * r) * 32 + lk4] = pre_in[r];
-      s_dout[ds * 8 + dj] = pre_d;
+      for (int r = 0; r < 4; ++r) {
+        const int sidx = s0 + ds + 32 * r;
+        vd[r] = (dj_ok && sidx < B) ? __ldg(dout + (size_t)sidx * J + jt * 8 + dj) : 0.f;
+      }
+      if (s0 > 0) __syncthreads();                              // previous chunk fully consumed
+#pragma unroll
+      for (int r = 0; r < 16; ++r) reinterpret_cast<float4*>(s_in)[(ls + 8 * r) * 32 + lk4] = vin[r];
+#pragma unroll
+      for (int r = 0; r < 4; ++r) s_dout[(ds + 32 * r) * 8 + dj] = vd[r];
       __syncthreads();
-      if (s0 + 32 < B) fetch(s0 + 32);                          // next chunk in flight during the FMAs
+      const int ns = min(kUChunk, B - s0);
 #pragma unroll 8
-      for (int s = 0; s < 32; ++s) {
-        const float d = s_dout[s * 8 + tj];
-        const float4 x = reinterpret_cast<const float4*>(s_in)[s * 32 + tk4];
+      for (int sidx = 0; sidx < ns; ++sidx) {
+        const float d = s_dout[sidx * 8 + tj];
+        const float4 x = reinterpret_cast<const float4*>(s_in)[sidx * 32 + tk4];
         acc.x = fmaf(d, x.x, acc.x);
         acc.y = fmaf(d, x.y, acc.y);
         acc.z = fmaf(d, x.z, acc.z);
         acc.w = fmaf(d, x.w, acc.w);
       }
     }
-    if (j < J && k < K) {
-      const long long dst = off + (long long)j * K + k;
-      apply_update<kApply>(U, dst + 0, acc.x);
-      apply_update<kApply>(U, dst + 1, acc.y);
-      apply_update<kApply>(U, dst + 2, acc.z);
-      apply_update<kApply>(U, dst + 3, acc.w);
+    if (mine) {
+      apply_update<kApply>(U, dst + 0, acc.x, p4.x, m4.x);
+      apply_update<kApply>(U, dst + 1, acc.y, p4.y, m4.y);
+      apply_update<kApply>(U, dst + 2, acc.z, p4.z, m4.z);
+      apply_update<kApply>(U, dst + 3, acc.w, p4.w, m4.w);
     }
     return;
   }
 
-  if (b == 73 && tid < 32 && U.stats != nullptr) {   // K13: counters stay on the device
-    float l = 0.f, c = 0.f;
-    for (int s = tid; s < B; s += 32) { l += W.loss_rows[s]; c += W.corr_rows[s]; }
-    l = warp_sum(l);
-    c = warp_sum(c);
-    if (tid == 0) {
-      U.stats[0] += l / (float)B;
-      U.stats[1] += c;
-      U.stats[2] += (float)B;
-      U.stats[3] += 1.f;
+  if (b == kUpdateBlocks - 1) {                      // K13: counters stay on the device
+    if (tid < 32 && U.stats != nullptr) {
+      float l = 0.f, c = 0.f;
+      for (int sidx = tid; sidx < B; sidx += 32) { l += W.loss_rows[sidx]; c += W.corr_rows[sidx]; }
+      l = warp_sum(l);
+      c = warp_sum(c);
+      if (tid == 0) {
+        U.stats[0] += l / (float)B;
+        U.stats[1] += c;
+        U.stats[2] += (float)B;
+        U.stats[3] += 1.f;
+      }
+    }
+    return;
+  }
+
+  // ---- remaining parameters: lane = parameter, warp = group of 16 samples
+  float* s_part = usm;                                           // [8 warps][32]
+  const int lane = tid & 31, w = tid >> 5;
+  const int i = (b - 73) * 32 + lane;
+  const bool ok = i < kRestParams;
+  const float* src = nullptr;
+  size_t stride = 0;
+  long long dst = 0;
+  if (ok) {
+    if (i < H1)                  { src = W.dh1 + i; stride = H1; dst = U.off[5] + i; }
+    else if (i < H1 + H2)        { src = W.dh2 + (i - H1); stride = H2; dst = U.off[7] + (i - H1); }
+    else if (i < H1 + H2 + NCLS) { src = W.dlogits + (i - H1 - H2); stride = NCLS; dst = U.off[9] + (i - H1 - H2); }
+    else {
+      const int c = i - (H1 + H2 + NCLS);                        // position inside the conv partial row
+      src = W.conv_part + c;
+      stride = CONV_PART;
+      if (c < OFF_B1)      dst = U.off[0] + c;
+      else if (c < OFF_W2) dst = U.off[1] + (c - OFF_B1);
+      else if (c < OFF_B2) dst = U.off[2] + (c - OFF_W2);
+      else                 dst = U.off[3] + (c - OFF_B2);
     }
   }
-  const int i = (b - 73) * 256 + tid;
-  if (i >= kRestParams) return;
-  const float* src;
-  size_t stride;
-  long long dst;
-  if (i < H1)                  { src = W.dh1 + i; stride = H1; dst = U.off[5] + i; }
-  else if (i < H1 + H2)        { src = W.dh2 + (i - H1); stride = H2; dst = U.off[7] + (i - H1); }
-  else if (i < H1 + H2 + NCLS) { src = W.dlogits + (i - H1 - H2); stride = NCLS; dst = U.off[9] + (i - H1 - H2); }
-  else {
-    const int c = i - (H1 + H2 + NCLS);                          // position inside the conv partial row
-    src = W.conv_part + c;
-    stride = CONV_PART;
-    if (c < OFF_B1)      dst = U.off[0] + c;
-    else if (c < OFF_W2) dst = U.off[1] + (c - OFF_B1);
-    else if (c < OFF_B2) dst = U.off[2] + (c - OFF_W2);
-    else                 dst = U.off[3] + (c - OFF_B2);
-  }
+  float p = 0.f, m = 0.f;
+  if (kApply && ok && w == 0) { p = U.param[dst]; m = U.momentum[dst]; }
   float g = 0.f;
-#pragma unroll 16
-  for (int s = 0; s < B; ++s) g += __ldg(src + (size_t)s * stride);
-  apply_update<kApply>(U, dst, g);
+  for (int s0 = 0; s0 < B; s0 += kUChunk) {
+    float v[16];
+#pragma unroll
+    for (int r = 0; r < 16; ++r) {
+      const int sidx = s0 + 16 * w + r;
+      v[r] = (ok && sidx < B) ? __ldg(src + (size_t)sidx * stride) : 0.f;
+    }
+    float part = 0.f;
+#pragma unroll
+    for (int r = 0; r < 16; ++r) part += v[r];
+    if (s0 > 0) __syncthreads();
+    s_part[w * 32 + lane] = part;
+    __syncthreads();
+    if (w == 0) {
+#pragma unroll
+      for (int q = 0; q < 8; ++q) g += s_part[q * 32 + lane];
+    }
+  }
+  if (w == 0 && ok) apply_update<kApply>(U, dst, g, p, m);
 }
 
 // ---------------------------------------------------------------------------------------------- evaluation kernel
@@ -867,6 +962,8 @@ int ensure_smem() {
     FEDB_CHECK(cudaFuncSetAttribute(lenet_sample_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
     FEDB_CHECK(cudaFuncSetAttribute(lenet_sample_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
     FEDB_CHECK(cudaFuncSetAttribute(lenet_eval_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kEvalSmemBytes));
+    FEDB_CHECK(cudaFuncSetAttribute(update_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kUpdateSmemBytes));
+    FEDB_CHECK(cudaFuncSetAttribute(update_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kUpdateSmemBytes));
     done = true;
   }
   return 0;
@@ -876,6 +973,7 @@ int check_offsets(const fedb_lenet_t* net) {
   for (int i = 0; i < 10; ++i)
     FEDB_REQUIRE(net->off[i] % 4 == 0, "fedb_lenet: parameter offsets must be multiples of 4 elements (16-byte loads)");
   FEDB_REQUIRE(((uintptr_t)net->param & 15) == 0, "fedb_lenet: arena must be 16-byte aligned");
+  FEDB_REQUIRE(((uintptr_t)net->momentum & 15) == 0, "fedb_lenet: momentum buffer must be 16-byte aligned");
   return 0;
 }
 
@@ -903,7 +1001,22 @@ extern "C" int fedb_lenet_train_step(const fedb_lenet_t* net, const uint8_t* ima
   U.param = net->param; U.momentum = net->momentum; U.dparam = nullptr;
   for (int i = 0; i < 10; ++i) U.off[i] = net->off[i];
   U.lr = net->lr; U.mu = net->mu; U.wd = net->weight_decay; U.B = B; U.stats = stats;
-  update_kernel<true><<<kUpdateBlocks, 256, 0, s>>>(U, W);
+  update_kernel<true><<<kUpdateBlocks, 256, kUpdateSmemBytes, s>>>(U, W);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+
+// Debug: runs the sample kernel of a training step once and leaves CTA 0's clock64() stamps of the 15 phase
+// boundaries in clk_dev[0..14] (SM cycles).  Used by tools/prof_lenet.py --phases.
+extern "C" int fedb_lenet_phase_clocks(const fedb_lenet_t* net, const uint8_t* images_u8, const int64_t* labels, int B,
+                                       void* workspace, long long* clk_dev, void* stream) {
+  FEDB_REQUIRE(net && images_u8 && labels && workspace && clk_dev && B > 0, "fedb_lenet_phase_clocks: bad arguments");
+  if (int rc = ensure_smem()) return rc;
+  Workspace W;
+  carve(&W, workspace, B);
+  const Params P = make_params(net);
+  lenet_sample_kernel<true, true><<<B, kThreads, kSmemBytes, (cudaStream_t)stream>>>(
+      images_u8, P, W, labels, B, 0, 0ull, nullptr, nullptr, clk_dev);
   FEDB_LAUNCH_OK();
   return 0;
 }
@@ -959,7 +1072,7 @@ extern "C" int fedb_lenet_grad(const fedb_lenet_t* net, const float* images_f32,
   U.param = net->param; U.momentum = net->momentum; U.dparam = dparam;
   for (int i = 0; i < 10; ++i) U.off[i] = net->off[i];
   U.lr = 0.f; U.mu = 0.f; U.wd = 0.f; U.B = B; U.stats = loss_out;   // loss_out: 4 floats like stats
-  update_kernel<false><<<kUpdateBlocks, 256, 0, s>>>(U, W);
+  update_kernel<false><<<kUpdateBlocks, 256, kUpdateSmemBytes, s>>>(U, W);
   FEDB_LAUNCH_OK();
   return 0;
 }

@@ -156,6 +156,9 @@ typedef struct {
 } fedb_lenet_t;
 
 size_t fedb_lenet_workspace_bytes(int B);
+/* debug: clock64() stamps of CTA 0 at the 15 phase boundaries of the sample kernel (tools/prof_lenet.py --phases) */
+int fedb_lenet_phase_clocks(const fedb_lenet_t* net, const uint8_t* images_u8, const int64_t* labels, int B,
+                            void* workspace, long long* clk_dev, void* stream);
 size_t fedb_lenet_eval_bytes(int B);   /* workspace of fedb_lenet_eval: two rows of B floats (always <= workspace_bytes(B)) */
 int fedb_lenet_train_step(const fedb_lenet_t* net, const uint8_t* images_u8, const int64_t* labels,
                           int B, void* workspace, float* stats, uint64_t step_seed, void* stream);

@@ -28,3 +28,27 @@ a.record()
 for _ in range(20): g.replay()
 b.record(); torch.cuda.synchronize()
 print("graph: us per step", a.elapsed_time(b) * 1000 / (20 * 8))
+
+if "--phases" in sys.argv:
+    # per-phase SM cycles of CTA 0 of one sample-kernel launch (debug clock stamps, csrc/lenet.cu)
+    import ctypes as C
+    from fedb200.ops import _lib
+    L = _lib.lib()
+    L.fedb_lenet_phase_clocks.restype = C.c_int
+    L.fedb_lenet_phase_clocks.argtypes = [C.c_void_p] * 3 + [C.c_int] + [C.c_void_p] * 3
+    clk = torch.zeros(16, dtype=torch.int64, device="cuda")
+    names = ["stage image+weights", "conv1+relu+pool", "conv2+relu+pool", "fc1/fc2/fc3 forward", "softmax-CE",
+             "fc backward dh2, dh1", "fc backward dflat (+reduce)", "publish rows", "unpool2 + zero dp1", "conv2 wgrad",
+             "conv2 dgrad scatter", "reduce dp1 + unpool1", "conv1 wgrad", "conv1 wgrad reduce + bias"]
+    tot = None
+    for rep in range(5):
+        _lib.check(L.fedb_lenet_phase_clocks(C.byref(plan.desc), x[:128].data_ptr(), y[:128].data_ptr(), 128,
+                                             plan.workspace.data_ptr(), clk.data_ptr(), None), "phase clocks")
+        torch.cuda.synchronize()
+        c = clk.cpu().tolist()
+        d = [c[i + 1] - c[i] for i in range(14)]
+        tot = d if tot is None else [min(a, b) for a, b in zip(tot, d)]
+    s = sum(tot)
+    print(f"phase cycles (min of 5), total {s} cycles = {s / 1.965e3:.1f} us at 1965 MHz")
+    for nme, v in zip(names, tot):
+        print(f"  {nme:28s} {v:7d}  {100 * v / s:5.1f} %")
