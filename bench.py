@@ -13,8 +13,9 @@ test set.  Model: LeNet, the zoo's small CNN.  N clients = N GPUs, one process p
   python bench.py --impl reference --gpus 2 --steps 3 --warmup 1       # unmodified reference
 
 Prints ONE JSON line (rank 0).  `value` is device-timed (CUDA events, max over ranks) with the inputs
-resident on the GPU; `e2e` is the same metric through ``GpuFederation.run_round()`` including the H2D
-copy of every round's inputs from pinned memory and the D2H read of the round's loss/accuracy.
+resident on the GPU; `e2e` is the same metric through ``GpuFederation.run_round_async()`` (wall clock) including the
+H2D copy of every round's inputs from pinned memory and the D2H read of every round's loss/accuracy/status; the
+host reads round r's result after it has enqueued round r+1.
 """
 from __future__ import annotations
 
@@ -176,8 +177,13 @@ def run_ours(a) -> dict:
     # ---------------------------------------------------------------- end to end through the public API
     barrier()
     t0 = time.perf_counter()
+    pending = None
     for _ in range(a.steps):
-        last = fed.run_round(upload=True, sync=True)
+        h = fed.run_round_async(upload=True)        # H2D of the round's inputs + D2H of its result are inside
+        if pending is not None:
+            last = pending.result()                 # result of the previous round, read while this one runs
+        pending = h
+    last = pending.result()
     barrier()
     e2e_s = max_over_ranks(time.perf_counter() - t0)
     h2d, d2h = fed.h2d_bytes_per_round(), fed.d2h_bytes_per_round()

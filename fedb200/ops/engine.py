@@ -221,6 +221,33 @@ class CudaEngine:
         st.loss_sum, st.correct, st.samples, st.steps = float(s[0]), int(s[1]), int(s[2]), int(s[3])
         return st
 
+    # ---- pipelined result read-back: the copy is enqueued with the round, the host reads it one round later
+    def enqueue_round_stats(self, status_word: Optional[torch.Tensor] = None):
+        """Queues the D2H copy of this round's counters (train 4 + eval 4 floats, plus an optional int32 status word
+        such as the K-AGG flag status) into a pinned slot and returns a ticket for ``fetch_round_stats``.  Nothing
+        blocks here, so the next round can be enqueued while this one still runs."""
+        if not hasattr(self, "_ring"):
+            self._ring = [(torch.zeros(8, dtype=torch.float32).pin_memory(), torch.zeros(1, dtype=torch.int32).pin_memory(),
+                           torch.cuda.Event()) for _ in range(4)]
+            self._ring_next = 0
+        buf, st, ev = self._ring[self._ring_next]
+        self._ring_next = (self._ring_next + 1) % len(self._ring)
+        with torch.cuda.device(self.dev):
+            buf[:4].copy_(self.stats, non_blocking=True)
+            buf[4:].copy_(self.eval_stats, non_blocking=True)
+            if status_word is not None:
+                st.copy_(status_word, non_blocking=True)
+            else:
+                st.zero_()
+            ev.record(torch.cuda.current_stream(self.dev))
+        self.d2h_bytes_last = 36
+        return buf, st, ev
+
+    def fetch_round_stats(self, ticket):
+        buf, st, ev = ticket
+        ev.synchronize()
+        return self._to_stats(buf[:4]), self._to_stats(buf[4:]), int(st[0]) & 0xFFFFFFFF
+
     def read_round_stats(self):
         """Train + eval counters of a round in ONE pinned D2H copy (32 bytes) and one sync."""
         self._pinned_stats[:4].copy_(self.stats, non_blocking=True)

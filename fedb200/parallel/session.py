@@ -19,6 +19,7 @@ from typing import Optional
 import torch
 
 from ..control.trainer import LocalTrainer, TrainerConfig
+from ..ops import _lib
 from ..utils import data as D
 from .group import FedGroup
 
@@ -68,6 +69,15 @@ class GpuFederation:
         self.group.check()
         return out
 
+    def run_round_async(self, upload: bool = True) -> "RoundHandle":
+        """One federated round, enqueued only.  The round's loss / accuracy counters and the K-AGG status travel to a
+        pinned slot at the end of the round; ``handle.result()`` waits for exactly that copy.  Calling it after the
+        NEXT round has been enqueued keeps the GPU busy across the round boundary (up to three rounds may be in flight)."""
+        self.run_round(upload=upload, sync=False)
+        c = self.group.peers.me.ctrl()
+        off = _lib.CTRL_OFF["status"] // 4
+        return RoundHandle(self, self.engine.enqueue_round_stats(c[off:off + 1]))
+
     def h2d_bytes_per_round(self) -> int:
         return self.engine.h2d_bytes_last
 
@@ -76,6 +86,18 @@ class GpuFederation:
 
     def close(self):
         self.group.close()
+
+
+class RoundHandle:
+    def __init__(self, fed: GpuFederation, ticket):
+        self.fed, self.ticket = fed, ticket
+
+    def result(self):
+        train, ev, status = self.fed.engine.fetch_round_stats(self.ticket)
+        if status:
+            raise _lib.FedbError(f"K-AGG flag wait failed on rank {self.fed.rank}: status {status} "
+                                 "(1 = a peer never arrived, 2 = a peer never finished, 3 = aborted)")
+        return train, ev
 
 
 class PeerWorker:

@@ -1,0 +1,46 @@
+"""GpuFederation on one GPU (world = 1): the public round API that bench.py times.
+
+The reference's round (src/server.py:120-153) with a single client is: local pass, "average" of one model, push back,
+evaluation.  Checks: the streamed-upload graphs compute what the resident-input graphs compute, and the pipelined
+result read-back returns the same numbers as the blocking one.
+"""
+import pytest
+import torch
+
+from fedb200.utils import data as D
+
+pytestmark = pytest.mark.gpu
+
+
+def _fed(seed, **kw):
+    from fedb200.parallel.session import GpuFederation
+    ds = D.synthetic_cifar(128 * 20 + 17, 1003, seed=3)
+    return GpuFederation(model="LeNet", rank=0, world=1, device=0, dataset=ds, seed=seed, tag=f"t-sess-{seed}-{len(kw)}", **kw)
+
+
+def test_round_is_reproducible_across_upload_modes_and_async():
+    a, b, c = _fed(11), _fed(11), _fed(11)
+    outs = {"sync": [], "resident": [], "async": []}
+    pending = None
+    for r in range(4):
+        outs["sync"].append(a.run_round(upload=True, sync=True))
+        if r == 0:
+            outs["resident"].append(b.run_round(upload=True, sync=True))     # first round brings the inputs over
+        else:
+            b.run_round(upload=False, sync=False)
+            outs["resident"].append(b.engine.read_round_stats())
+        h = c.run_round_async(upload=True)
+        if pending is not None:
+            outs["async"].append(pending.result())
+        pending = h
+    outs["async"].append(pending.result())
+    for mode in ("resident", "async"):
+        for (t0, e0), (t1, e1) in zip(outs["sync"], outs[mode]):
+            assert t0.steps == t1.steps == 21 and t0.samples == t1.samples == 128 * 20 + 17
+            assert t0.loss_sum == t1.loss_sum and t0.correct == t1.correct, mode
+            assert e0.samples == e1.samples == 1003 and e0.loss_sum == e1.loss_sum and e0.correct == e1.correct, mode
+    pa = a.trainer.arena.f32.clone()
+    assert torch.equal(pa, b.trainer.arena.f32) and torch.equal(pa, c.trainer.arena.f32)
+    assert a.h2d_bytes_per_round() == (128 * 20 + 17) * (3072 + 8) + 1003 * (3072 + 8)
+    for f in (a, b, c):
+        f.close()

@@ -33,8 +33,12 @@ METRICS = [
 ]
 
 
+FILTER = os.environ.get("NCU_KERNEL", "")       # e.g. NCU_KERNEL=regex:update_kernel restricts every page to it
+
+
 def ncu(args):
-    return subprocess.run(["ncu"] + args, capture_output=True, text=True).stdout
+    extra = ["--kernel-name", FILTER, "--launch-count", "1"] if FILTER else []
+    return subprocess.run(["ncu"] + args + extra, capture_output=True, text=True).stdout
 
 
 def raw_rows(rep):

@@ -52,3 +52,28 @@ if "--phases" in sys.argv:
     print(f"phase cycles (min of 5), total {s} cycles = {s / 1.965e3:.1f} us at 1965 MHz")
     for nme, v in zip(names, tot):
         print(f"  {nme:28s} {v:7d}  {100 * v / s:5.1f} %")
+
+if "--split" in sys.argv:
+    # back-to-back sample kernels only (the debug entry launches just that kernel): step time - this = update + gaps
+    import ctypes as C
+    from fedb200.ops import _lib
+    L = _lib.lib()
+    L.fedb_lenet_phase_clocks.restype = C.c_int
+    L.fedb_lenet_phase_clocks.argtypes = [C.c_void_p] * 3 + [C.c_int] + [C.c_void_p] * 3
+    clk = torch.zeros(16, dtype=torch.int64, device="cuda")
+    st = torch.cuda.current_stream().cuda_stream
+
+    def only_sample():
+        for s in range(8):
+            _lib.check(L.fedb_lenet_phase_clocks(C.byref(plan.desc), x[s * 128:(s + 1) * 128].data_ptr(),
+                                                 y[s * 128:(s + 1) * 128].data_ptr(), 128, plan.workspace.data_ptr(),
+                                                 clk.data_ptr(), torch.cuda.current_stream().cuda_stream), "phase clocks")
+    only_sample(); torch.cuda.synchronize()
+    g2 = torch.cuda.CUDAGraph()
+    with torch.cuda.graph(g2):
+        only_sample()
+    g2.replay(); torch.cuda.synchronize()
+    a.record()
+    for _ in range(20): g2.replay()
+    b.record(); torch.cuda.synchronize()
+    print("graph: us per sample kernel alone", a.elapsed_time(b) * 1000 / (20 * 8))
