@@ -151,8 +151,17 @@ struct GemmArgs {
   int conv;            // 0: plain GEMM
   int Cin, H, W;       // activation geometry
   int bw, bh, bn;      // box: bw*bh*bn == 128 output pixels = one M tile (bw == W); H, W are the OUTPUT map
-  int cstride, cpad, fs;   // convolution stride, padding, filter size (fs x fs taps)
+  int cstride, cpad, fs;   // convolution stride, padding, taps per filter ROW (tap t -> row t / fs, column t % fs)
+  // output scatter of the parity-decomposed data gradient of a stride-2 convolution: tile row (n, p, q) of the
+  // [N, H, W] sub-grid is written to pixel (n, p*ostride + oy, q*ostride + ox) of the [N, H*ostride, W*ostride] map
+  int ostride, oy, ox;     // ostride <= 1: rows are written in place
 };
+
+__device__ __forceinline__ long long out_row(const GemmArgs& g, int row) {
+  if (g.ostride <= 1) return row;
+  const int q = row % g.W, p = (row / g.W) % g.H, n = row / (g.W * g.H);
+  return ((long long)(n * g.H + p) * g.ostride + g.oy) * (g.W * g.ostride) + q * g.ostride + g.ox;
+}
 
 // smem stage layout: A tile then B tile, each a multiple of 1024 B (swizzle atom)
 template <int BN, int KIND>
@@ -307,7 +316,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
           for (int j = 0; j < 16; j += 4)
             *reinterpret_cast<float4*>(stage + lane * PITCH + c0 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
         } else if (row < g.M) {
-          float* drow = g.D + (long long)row * g.ldd + (long long)tap * g.Cin + n0 + c0;
+          float* drow = g.D + out_row(g, row) * g.ldd + (long long)tap * g.Cin + n0 + c0;
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
             if (n0 + c0 + j < g.N) {
@@ -322,10 +331,11 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         for (int r = 0; r < 32; ++r) {
           const int grow = m0 + q * 32 + r;
           if (grow >= g.M) break;
+          const long long orow = out_row(g, grow);
           for (int c4 = lane; c4 < BN / 4; c4 += 32) {
             const int col = n0 + 4 * c4;
             if (col < g.N)
-              *reinterpret_cast<float4*>(g.D + (long long)grow * g.ldd + col) =
+              *reinterpret_cast<float4*>(g.D + orow * g.ldd + col) =
                   *reinterpret_cast<const float4*>(stage + r * PITCH + 4 * c4);
           }
         }
@@ -462,6 +472,7 @@ int run_gemm(int kind, const void* A, const void* B, float* D, const float* bias
   g.relu = relu;
   g.atomic_out = (splits > 1 || accumulate) ? 1 : 0;
   g.conv = 0; g.Cin = g.H = g.W = g.bw = g.bh = g.bn = 0; g.cstride = 1; g.cpad = 0; g.fs = 1;
+  g.ostride = g.oy = g.ox = 0;
   return kind == 0 ? dispatch_bn<0>(bn, ma, mb, g, splits, s) : dispatch_bn<1>(bn, ma, mb, g, splits, s);
 }
 
@@ -527,7 +538,69 @@ extern "C" int fedb_conv_tf32(const float* X, const float* Wk, float* Y, const f
   GemmArgs g;
   g.D = Y; g.bias = bias; g.ldd = Cout; g.M = M; g.N = Cout; g.K = K; g.k_per_split = K; g.relu = relu; g.atomic_out = 0;
   g.conv = 1; g.Cin = Cin; g.H = P; g.W = Q; g.bw = bw; g.bh = bh; g.bn = bn; g.cstride = stride; g.cpad = pad; g.fs = fs;
+  g.ostride = g.oy = g.ox = 0;
   return dispatch_bn<0>(bnt, ma, mb, g, 1, (cudaStream_t)stream);
+}
+
+// Filters of the four output-parity classes of a stride-2 3x3/pad-1 data gradient, K-major for the GEMM:
+//   class (a, b), a = h % 2, b = w % 2 of the dX pixel; rows: a == 0 -> filter row 1 (dY row p'), a == 1 -> filter row 2
+//   (dY row p') then row 0 (dY row p'+1); columns likewise.  out = [class][c][tap][k], classes (0,0),(0,1),(1,0),(1,1)
+//   with 1, 2, 2, 4 taps: class offsets 0, 1, 3, 5 in units of C*K floats.
+__global__ void __launch_bounds__(256) pack_dgrad_s2_kernel(const float* __restrict__ w, float* __restrict__ out, int K, int C) {
+  const int total = 9 * K * C;
+  for (int i = blockIdx.x * 256 + threadIdx.x; i < total; i += gridDim.x * 256) {
+    const int unit = i / (K * C);                       // 0..8: which (class, tap)
+    const int cls = unit < 1 ? 0 : (unit < 3 ? 1 : (unit < 5 ? 2 : 3));
+    const int base = cls == 0 ? 0 : (cls == 1 ? 1 : (cls == 2 ? 3 : 5));
+    const int a = cls >> 1, b = cls & 1;
+    const int T = (a + 1) * (b + 1), fc = b + 1;
+    const int j = i - base * K * C;                     // index inside the class: (c * T + t) * K + k
+    const int k = j % K, t = (j / K) % T, c = j / (K * T);
+    const int rr = t / fc, ss = t % fc;
+    const int r = a == 0 ? 1 : (rr == 0 ? 2 : 0), sx = b == 0 ? 1 : (ss == 0 ? 2 : 0);
+    out[i] = w[((k * C + c) * 3 + r) * 3 + sx];
+  }
+}
+
+extern "C" int fedb_pack_dgrad_s2(const float* w_oihw, float* out, int K, int C, void* stream) {
+  int blocks = fedb_ceil_div((long long)K * C * 9, 256);
+  if (blocks > fedb_num_sms() * 8) blocks = fedb_num_sms() * 8;
+  pack_dgrad_s2_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w_oihw, out, K, C);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+
+// Data gradient of a stride-2 convolution as stride-1 implicit GEMMs over the four parity classes of dX (each class
+// sees a dense 1x1 / 1x2 / 2x1 / 2x2 filter over dY), written straight into the interleaved positions of dX by the
+// epilogue.  dY [N,P,Q,Cout], dX [N,2P,2Q,Cin].  fs == 3: Wcls from fedb_pack_dgrad_s2.  fs == 1: Wcls = W^T
+// ([Cin][Cout]); only class (0,0) receives gradient, the caller zero-fills dX first.
+extern "C" int fedb_conv_dgrad_s2_tf32(const float* dY, const float* Wcls, float* dX, int N, int P, int Q, int Cout, int Cin,
+                                       int fs, void* stream) {
+  FEDB_REQUIRE(Cout % 32 == 0 && Cin % 4 == 0, "fedb_conv_dgrad_s2_tf32: Cout % 32, Cin % 4");
+  FEDB_REQUIRE(fs == 1 || fs == 3, "fedb_conv_dgrad_s2_tf32: 1x1 or 3x3");
+  FEDB_REQUIRE(Q <= 32 && Q >= 2 && (Q & (Q - 1)) == 0 && (P & (P - 1)) == 0, "fedb_conv_dgrad_s2_tf32: dY maps must be powers of two");
+  const int bw = Q;
+  int bh = 128 / bw;
+  if (bh > P) bh = P;
+  const int bn = 128 / (bw * bh);
+  FEDB_REQUIRE(bw * bh * bn == 128 && (bn == 1 || bh == P), "fedb_conv_dgrad_s2_tf32: unsupported tile geometry");
+  const int bnt = Cin >= 128 ? 128 : (Cin > 32 ? 64 : 32);
+  CUtensorMap ma, mb;
+  if (int rc = make_map_nhwc(&ma, dY, 4, N, P, Q, Cout, bw, bh, bn, 1)) return rc;
+  const int ncls = fs == 3 ? 4 : 1;
+  const int base[4] = {0, 1, 3, 5};
+  for (int cls = 0; cls < ncls; ++cls) {
+    const int a = cls >> 1, b = cls & 1;
+    const int taps = fs == 3 ? (a + 1) * (b + 1) : 1;
+    const int K = taps * Cout;
+    if (int rc = make_map_2d(&mb, Wcls + (size_t)base[cls] * Cin * Cout, 4, Cin, K, K, 32, bnt)) return rc;
+    GemmArgs g;
+    g.D = dX; g.bias = nullptr; g.ldd = Cin; g.M = N * P * Q; g.N = Cin; g.K = K; g.k_per_split = K; g.relu = 0; g.atomic_out = 0;
+    g.conv = 1; g.Cin = Cout; g.H = P; g.W = Q; g.bw = bw; g.bh = bh; g.bn = bn; g.cstride = 1; g.cpad = 0; g.fs = b + 1;
+    g.ostride = 2; g.oy = a; g.ox = b;
+    if (int rc = dispatch_bn<0>(bnt, ma, mb, g, 1, (cudaStream_t)stream)) return rc;
+  }
+  return 0;
 }
 
 extern "C" int fedb_conv3x3_tf32(const float* X, const float* Wk, float* Y, const float* bias, int N, int H, int W, int Cin,
@@ -566,6 +639,7 @@ extern "C" int fedb_conv_wgrad_bf16(const uint16_t* dY, const uint16_t* X, float
   splits = (ktiles + tiles_per_split - 1) / tiles_per_split;
   g.relu = 0; g.atomic_out = 1;
   g.conv = 2; g.Cin = Cin; g.H = P; g.W = Q; g.bw = bw; g.bh = bh; g.bn = bn; g.cstride = stride; g.cpad = pad; g.fs = fs;
+  g.ostride = g.oy = g.ox = 0;
   static bool attr128 = false, attr64 = false;
   cudaStream_t s = (cudaStream_t)stream;
   dim3 grid(fedb_ceil_div(Cout, BM), fedb_ceil_div(Cin, bnt) * taps, splits);

@@ -34,6 +34,8 @@ def _f(name):
             "fedb_conv_tf32": [vp, vp, vp, vp, i, i, i, i, i, i, i, i, i, vp],
             "fedb_conv_wgrad_bf16": [vp, vp, vp, i, i, i, i, i, i, i, i, i, vp],
             "fedb_pack_filter": [vp, vp, i, i, i, i, vp],
+            "fedb_pack_dgrad_s2": [vp, vp, i, i, vp],
+            "fedb_conv_dgrad_s2_tf32": [vp, vp, vp, i, i, i, i, i, i, vp],
         }[name]
         _fns[name] = _lib.bind(name, C.c_int, sig)
     return _fns[name]
@@ -154,6 +156,22 @@ def conv_dgrad(dy, w, dx, shp) -> bool:
     if _is_3x3(shp, shp[4], shp[3]):
         N, H, W, Cc, K = shp[:5]
         conv3x3_tf32(dy, pack3x3(w, 1), dx, None, N, H, W, K, Cc)    # dX = conv3x3(dY, flipped + transposed filter)
+        return True
+    st = _strided(shp)
+    if st is not None and shp[4] % 32 == 0 and shp[3] % 4 == 0:
+        # stride 2: four parity classes of dX, each a dense stride-1 implicit GEMM over dY, scattered by the epilogue
+        N, H, W, Cc, K, _, _, P, Q = shp[:9]
+        fs = st[0]
+        if fs == 3:
+            wc = torch.empty(9 * K * Cc, dtype=torch.float32, device=w.device)
+            check(_f("fedb_pack_dgrad_s2")(w.data_ptr(), wc.data_ptr(), K, Cc, current_stream()), "fedb_pack_dgrad_s2")
+            _lib.count_launch()
+        else:
+            wc = transpose(w, K, Cc)
+            dx.zero_()                                   # only the even/even pixels of dX receive gradient
+        check(_f("fedb_conv_dgrad_s2_tf32")(dy.data_ptr(), wc.data_ptr(), dx.data_ptr(), N, P, Q, K, Cc, fs,
+                                            current_stream()), "fedb_conv_dgrad_s2_tf32")
+        _lib.count_launch(4 if fs == 3 else 1)
         return True
     if not _is_pointwise(shp):
         return False

@@ -222,6 +222,12 @@ int fedb_conv3x3_tf32(const float* X, const float* Wk, float* Y, const float* bi
  * pixels.  dWk must be zeroed by the caller; fedb_pack_filter mode 2 turns it back into OIHW.  Channels % 64 == 0. */
 int fedb_conv_wgrad_bf16(const uint16_t* dY, const uint16_t* X, float* dWk, int N, int H, int W, int Cin, int Cout, int fs,
                          int stride, int pad, int splits, void* stream);
+/* Data gradient of a stride-2 3x3/pad-1 or 1x1 convolution, decomposed by the parity of the dX pixel into four stride-1
+ * implicit GEMMs whose epilogues write the interleaved positions of dX [N,2P,2Q,Cin] directly.  dY is [N,P,Q,Cout].
+ * fs == 3: Wcls from fedb_pack_dgrad_s2 (9*Cin*Cout floats).  fs == 1: Wcls = W^T and dX must be zero-filled first. */
+int fedb_pack_dgrad_s2(const float* w_oihw, float* out, int K, int C, void* stream);
+int fedb_conv_dgrad_s2_tf32(const float* dY, const float* Wcls, float* dX, int N, int P, int Q, int Cout, int Cin, int fs,
+                            void* stream);
 int fedb_conv3x3_wgrad_bf16(const uint16_t* dY, const uint16_t* X, float* dWk, int N, int H, int W, int Cin, int Cout,
                             int splits, void* stream);
 /* mode 0: OIHW -> [K][tap][C]; mode 1: OIHW -> [C][flipped tap][K] (data gradient); mode 2: [K][tap][C] -> OIHW */

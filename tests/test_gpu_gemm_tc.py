@@ -96,7 +96,8 @@ def test_conv3x3_implicit_gemm_fwd_and_dgrad(G, B, C, K, HW):
                                          (16, 256, 512, 8, 1), (64, 64, 64, 4, 3)])
 def test_strided_conv_on_tensor_cores(G, B, C, K, HW, fs):
     """Stride-2 3x3 / 1x1 convolutions: the TMA tensor map skips every other input pixel (element strides), so the
-    forward and the weight gradient reuse the implicit-GEMM kernel; the data gradient stays on the generic kernel."""
+    forward and the weight gradient reuse the implicit-GEMM kernel; the data gradient is decomposed by the parity of the
+    dX pixel into four dense stride-1 implicit GEMMs over dY whose epilogues write the interleaved pixels."""
     import torch.nn.functional as TF
     from fedb200.ops import _lib, functional as F
     torch.manual_seed(5)
@@ -110,5 +111,6 @@ def test_strided_conv_on_tensor_cores(G, B, C, K, HW, fs):
     torch.testing.assert_close(yb.cpu(), ya.detach(), rtol=3e-3, atol=3e-3 * float(ya.detach().abs().max()))
     g = torch.randn_like(ya)
     ya.backward(g), yb.backward(g.to(DEV))
-    torch.testing.assert_close(xb.grad.cpu(), xa.grad, rtol=1e-3, atol=1e-4 * float(xa.grad.abs().max()) + 1e-5)
+    # the data gradient runs as four parity-class implicit GEMMs in TF32
+    torch.testing.assert_close(xb.grad.cpu(), xa.grad, rtol=3e-3, atol=3e-3 * float(xa.grad.abs().max()))
     torch.testing.assert_close(wb.grad.cpu(), wa.grad, rtol=1e-2, atol=1e-2 * float(wa.grad.abs().max()))
