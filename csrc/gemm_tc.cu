@@ -26,7 +26,8 @@
 namespace {
 
 constexpr int BM = 128;          // UMMA M
-constexpr int STAGES = 4;
+constexpr int STAGES = 4;   // BN <= 64; a 128-wide tile takes 3 so that two CTAs (2 x 97 KB) share an SM: one CTA's
+                            // epilogue and pipeline ramp then overlap the other's main loop
 // KIND 0: tf32, both operands K-major.   stage = [rows][32 fp32] (128 B rows), 4 MMAs of K=8 per stage
 // KIND 1: bf16, both operands MN-major.  stage = chunks of 64 bf16 (128 B) x 64 K-rows, 4 MMAs of K=16 per stage
 template <int KIND> struct Kind;
@@ -170,17 +171,19 @@ struct Smem {
   static constexpr int kABytes = BM * Kind<KIND>::kBK * Kind<KIND>::kElem;     // 16 KiB
   static constexpr int kBBytes = kBN * Kind<KIND>::kBK * Kind<KIND>::kElem;
   static constexpr int kStage = kABytes + kBBytes;
-  static constexpr int kTotal = STAGES * kStage + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int kStages = kStage > 24 * 1024 ? 3 : STAGES;
+  static constexpr int kTotal = kStages * kStage + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
 template <int BN, int KIND>
-__global__ void __launch_bounds__(kThreads, 1)
+__global__ void __launch_bounds__(kThreads, 2)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, GemmArgs g) {
+  constexpr int NST = Smem<BN, KIND>::kStages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  uint64_t* full = (uint64_t*)(smem + STAGES * Smem<BN, KIND>::kStage);
-  uint64_t* empty = full + STAGES;
-  uint64_t* accum_ready = empty + STAGES;
+  uint64_t* full = (uint64_t*)(smem + NST * Smem<BN, KIND>::kStage);
+  uint64_t* empty = full + NST;
+  uint64_t* accum_ready = empty + NST;
   uint32_t* tmem_slot = (uint32_t*)(accum_ready + 1);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
@@ -197,7 +200,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
   constexpr uint32_t kTmemCols = BN < 32 ? 32 : BN;   // power of two >= 32
 
   if (threadIdx.x == 0) {
-    for (int s = 0; s < STAGES; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
+    for (int s = 0; s < NST; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
     mbar_init(accum_ready, 1);
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
@@ -213,8 +216,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
       asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA) : "memory");
       asm volatile("prefetch.tensormap [%0];" ::"l"(&mapB) : "memory");
       for (int i = 0; i < num_k; ++i) {
-        const int s = i % STAGES;
-        const uint32_t ph = (i / STAGES) & 1;
+        const int s = i % NST;
+        const uint32_t ph = (i / NST) & 1;
         mbar_wait(&empty[s], ph ^ 1);
         uint8_t* a_dst = smem + s * Smem<BN, KIND>::kStage;
         uint8_t* b_dst = a_dst + Smem<BN, KIND>::kABytes;
@@ -266,8 +269,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc(BN, KIND);
       for (int i = 0; i < num_k; ++i) {
-        const int s = i % STAGES;
-        const uint32_t ph = (i / STAGES) & 1;
+        const int s = i % NST;
+        const uint32_t ph = (i / NST) & 1;
         mbar_wait(&full[s], ph);
         tc_fence_after();
         const uint32_t a_base = smem_u32(smem + s * Smem<BN, KIND>::kStage);

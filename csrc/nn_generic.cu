@@ -165,17 +165,42 @@ __global__ void __launch_bounds__(256) bn_partial_kernel(const float* __restrict
   }
 }
 
-__global__ void __launch_bounds__(128) bn_finalize_kernel(const float* __restrict__ scratch, int chunks, float* __restrict__ mean,
+// Second pass of the chunked reductions: block = 32 channels x 8 groups of chunks.  Group w adds chunks w, w+8, ... (four
+// independent loads in flight), the eight group sums are combined in group order: the result does not depend on
+// scheduling.  Returns the two per-channel sums to the threads of group 0.
+__device__ __forceinline__ bool chunk_reduce2(const float* __restrict__ scratch, int chunks, int C, int* ch_out, float* a_out,
+                                              float* b_out) {
+  __shared__ float sa[8][32], sb[8][32];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int ch = blockIdx.x * 32 + lane;
+  float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
+  if (ch < C) {
+    int k = w;
+    for (; k + 8 < chunks; k += 16) {
+      const float x0 = scratch[((long long)k * 2 + 0) * C + ch], y0 = scratch[((long long)k * 2 + 1) * C + ch];
+      const float x1 = scratch[((long long)(k + 8) * 2 + 0) * C + ch], y1 = scratch[((long long)(k + 8) * 2 + 1) * C + ch];
+      a0 += x0; b0 += y0; a1 += x1; b1 += y1;
+    }
+    if (k < chunks) { a0 += scratch[((long long)k * 2 + 0) * C + ch]; b0 += scratch[((long long)k * 2 + 1) * C + ch]; }
+  }
+  sa[w][lane] = a0 + a1;
+  sb[w][lane] = b0 + b1;
+  __syncthreads();
+  if (w != 0 || ch >= C) return false;
+  float a = 0.f, b = 0.f;
+#pragma unroll
+  for (int q = 0; q < 8; ++q) { a += sa[q][lane]; b += sb[q][lane]; }
+  *ch_out = ch; *a_out = a; *b_out = b;
+  return true;
+}
+
+__global__ void __launch_bounds__(256) bn_finalize_kernel(const float* __restrict__ scratch, int chunks, float* __restrict__ mean,
                                                          float* __restrict__ invstd, float* __restrict__ run_mean,
                                                          float* __restrict__ run_var, long long rows, int C, float eps,
                                                          float momentum) {
-  const int ch = blockIdx.x * 128 + threadIdx.x;
-  if (ch >= C) return;
-  float sum = 0.f, sq = 0.f;
-  for (int k = 0; k < chunks; ++k) {
-    sum += scratch[((long long)k * 2 + 0) * C + ch];
-    sq += scratch[((long long)k * 2 + 1) * C + ch];
-  }
+  int ch;
+  float sum, sq;
+  if (!chunk_reduce2(scratch, chunks, C, &ch, &sum, &sq)) return;
   const float m = sum / (float)rows;
   float var = sq / (float)rows - m * m;
   var = var < 0.f ? 0.f : var;
@@ -239,15 +264,11 @@ __global__ void __launch_bounds__(256) bn_bwd_partial_kernel(const float* __rest
   }
 }
 
-__global__ void __launch_bounds__(128) bn_bwd_finalize_kernel(const float* __restrict__ scratch, int chunks,
+__global__ void __launch_bounds__(256) bn_bwd_finalize_kernel(const float* __restrict__ scratch, int chunks,
                                                              float* __restrict__ dgamma, float* __restrict__ dbeta, int C) {
-  const int ch = blockIdx.x * 128 + threadIdx.x;
-  if (ch >= C) return;
-  float sa = 0.f, sb = 0.f;
-  for (int k = 0; k < chunks; ++k) {
-    sa += scratch[((long long)k * 2 + 0) * C + ch];
-    sb += scratch[((long long)k * 2 + 1) * C + ch];
-  }
+  int ch;
+  float sa, sb;
+  if (!chunk_reduce2(scratch, chunks, C, &ch, &sa, &sb)) return;
   dbeta[ch] = sa;
   dgamma[ch] = sb;
 }
@@ -508,7 +529,7 @@ extern "C" int fedb_nn_bn_fwd(const float* x, float* y, float* mean, float* invs
     long long rpc = 0;
     const int chunks = bn_chunks(rows, C, scratch_floats, &rpc);
     bn_partial_kernel<<<dim3(fedb_ceil_div(C, 32), chunks), 256, 0, S_>>>(x, scratch, rows, C, rpc);
-    bn_finalize_kernel<<<fedb_ceil_div(C, 128), 128, 0, S_>>>(scratch, chunks, mean, invstd, run_mean, run_var, rows, C, eps, momentum);
+    bn_finalize_kernel<<<fedb_ceil_div(C, 32), 256, 0, S_>>>(scratch, chunks, mean, invstd, run_mean, run_var, rows, C, eps, momentum);
   }
   else bn_eval_prep_kernel<<<fedb_ceil_div(C, 128), 128, 0, S_>>>(run_mean, run_var, mean, invstd, C, eps);
   bn_apply_kernel<<<grid_for(rows * C), 256, 0, S_>>>(x, y, mean, invstd, gamma, beta, rows * C, C, act);
@@ -522,7 +543,7 @@ extern "C" int fedb_nn_bn_bwd(const float* x, const float* dy, float* dx, const 
   long long rpc = 0;
   const int chunks = bn_chunks(rows, C, scratch_floats, &rpc);
   bn_bwd_partial_kernel<<<dim3(fedb_ceil_div(C, 32), chunks), 256, 0, S_>>>(x, dy, mean, invstd, gamma, beta, scratch, rows, C, act, rpc);
-  bn_bwd_finalize_kernel<<<fedb_ceil_div(C, 128), 128, 0, S_>>>(scratch, chunks, dgamma, dbeta, C);
+  bn_bwd_finalize_kernel<<<fedb_ceil_div(C, 32), 256, 0, S_>>>(scratch, chunks, dgamma, dbeta, C);
   bn_bwd_apply_kernel<<<grid_for(rows * C), 256, 0, S_>>>(x, dy, dx, mean, invstd, gamma, beta, dgamma, dbeta, rows * C, C,
                                                          1.f / (float)rows, act, training);
   FEDB_LAUNCH_OK();
