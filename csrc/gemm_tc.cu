@@ -690,6 +690,44 @@ extern "C" int fedb_cast_bf16(const float* src, uint16_t* dst, long long n, void
   return 0;
 }
 
+// Explicit im2col for convolutions whose reduction is tiny (Cin * fs * fs <= 32: the 3-channel stem of every zoo model).
+// Column j = c * fs*fs + r * fs + s, the OIHW flattening of the filter, padded with zeros to 32 (fp32 copy, forward
+// GEMM) and to 64 (bf16 copy, weight-gradient GEMM).  Either output may be null.
+__global__ void __launch_bounds__(256) im2col_small_kernel(const float* __restrict__ x, float* __restrict__ o32,
+                                                          __nv_bfloat16* __restrict__ o16, int N, int H, int W, int C, int fs,
+                                                          int stride, int pad, int P, int Q) {
+  const long long total = (long long)N * P * Q * 32;
+  const int taps = fs * fs, kreal = C * taps;
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+    const int j = (int)(i & 31);
+    const long long pix = i >> 5;
+    float v = 0.f;
+    if (j < kreal) {
+      const int c = j / taps, t = j - c * taps, r = t / fs, sx = t - r * fs;
+      const int q = (int)(pix % Q), p = (int)((pix / Q) % P), n = (int)(pix / ((long long)P * Q));
+      const int ih = p * stride - pad + r, iw = q * stride - pad + sx;
+      if (ih >= 0 && ih < H && iw >= 0 && iw < W) v = x[(((long long)n * H + ih) * W + iw) * C + c];
+    }
+    if (o32 != nullptr) o32[i] = v;
+    if (o16 != nullptr) {
+      o16[pix * 64 + j] = __float2bfloat16(v);
+      o16[pix * 64 + 32 + j] = __float2bfloat16(0.f);
+    }
+  }
+}
+
+extern "C" int fedb_im2col_small(const float* x, float* out_f32, uint16_t* out_bf16, int N, int H, int W, int C, int fs,
+                                 int stride, int pad, void* stream) {
+  FEDB_REQUIRE(C * fs * fs <= 32 && stride >= 1, "fedb_im2col_small: Cin * fs * fs must be <= 32");
+  const int P = (H + 2 * pad - fs) / stride + 1, Q = (W + 2 * pad - fs) / stride + 1;
+  long long blocks = ((long long)N * P * Q * 32 + 255) / 256;
+  if (blocks > fedb_num_sms() * 16) blocks = fedb_num_sms() * 16;
+  im2col_small_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(x, out_f32, (__nv_bfloat16*)out_bf16, N, H, W, C, fs, stride,
+                                                                     pad, P, Q);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+
 extern "C" int fedb_transpose(const float* in, float* out, int rows, int cols, void* stream) {
   dim3 grid(fedb_ceil_div(cols, 32), fedb_ceil_div(rows, 32));
   transpose_kernel<<<grid, 256, 0, (cudaStream_t)stream>>>(in, out, rows, cols);

@@ -35,6 +35,8 @@ def _f(name):
             "fedb_conv_wgrad_bf16": [vp, vp, vp, i, i, i, i, i, i, i, i, i, vp],
             "fedb_pack_filter": [vp, vp, i, i, i, i, vp],
             "fedb_pack_dgrad_s2": [vp, vp, i, i, vp],
+            "fedb_im2col_small": [vp, vp, vp, i, i, i, i, i, i, i, vp],
+            "fedb_nn_channel_copy": [vp, vp, ll, i, i, i, i, i, i, i, vp],
             "fedb_conv_dgrad_s2_tf32": [vp, vp, vp, i, i, i, i, i, i, vp],
         }[name]
         _fns[name] = _lib.bind(name, C.c_int, sig)
@@ -131,7 +133,37 @@ def conv3x3_tf32(x, wk, y, bias, N, H, W, cin, cout, relu=False):
     _lib.count_launch()
 
 
+def _small_reduction(shp) -> bool:
+    """Cin * R * S <= 32 and ungrouped (the 3-channel stem): explicit im2col to a [pixels, 32] matrix, then a GEMM."""
+    N, H, W, Cc, K, R, S, P, Q, sh, sw, ph, pw, groups = shp
+    return groups == 1 and R == S and sh == sw and ph == pw and Cc * R * S <= 32 and K % 4 == 0 and N * P * Q >= MIN_PIXELS
+
+
+def _channel_copy(src, dst, rows, cin, cout, width, accumulate=False):
+    check(_f("fedb_nn_channel_copy")(src.data_ptr(), dst.data_ptr(), rows, cin, cout, 0, 0, width, 1, int(accumulate),
+                                     current_stream()), "fedb_nn_channel_copy")
+    _lib.count_launch()
+
+
+def _im2col(x, shp, f32: bool, bf16: bool):
+    N, H, W, Cc, K, R, S, P, Q, sh, sw, ph, pw, groups = shp
+    pix = N * P * Q
+    o32 = torch.empty(pix * 32, dtype=torch.float32, device=x.device) if f32 else None
+    o16 = torch.empty(pix * 64, dtype=torch.bfloat16, device=x.device) if bf16 else None
+    check(_f("fedb_im2col_small")(x.data_ptr(), 0 if o32 is None else o32.data_ptr(), 0 if o16 is None else o16.data_ptr(),
+                                  N, H, W, Cc, R, sh, ph, current_stream()), "fedb_im2col_small")
+    _lib.count_launch()
+    return o32, o16
+
+
 def conv_forward(x, w, bias, y, shp) -> bool:
+    if _small_reduction(shp):
+        N, H, W, Cc, K, R, S, P, Q = shp[:9]
+        xcol, _ = _im2col(x, shp, True, False)
+        wp = torch.zeros(K * 32, dtype=torch.float32, device=x.device)
+        _channel_copy(w, wp, K, Cc * R * S, 32, Cc * R * S)              # [K][C*R*S] -> [K][32], zero padded
+        gemm_tf32(xcol, wp, y, N * P * Q, K, 32, 32, 32, K, bias=bias)
+        return True
     if _is_3x3(shp, shp[3], shp[4]):
         N, H, W, Cc, K = shp[:5]
         conv3x3_tf32(x, pack3x3(w, 0), y, bias, N, H, W, Cc, K)      # implicit GEMM, shifted TMA boxes per tap
@@ -182,6 +214,18 @@ def conv_dgrad(dy, w, dx, shp) -> bool:
 
 
 def conv_wgrad(x, dy, dw, db, shp) -> bool:
+    if _small_reduction(shp) and shp[4] % 64 == 0:
+        N, H, W, Cc, K, R, S, P, Q = shp[:9]
+        pix = N * P * Q
+        _, xcol16 = _im2col(x, shp, False, True)
+        dy16 = cast_bf16(dy)
+        dwp = torch.zeros(K * 64, dtype=torch.float32, device=x.device)
+        splits = max(1, min(pix // 256, 296))
+        gemm_bf16_tn(dy16, xcol16, dwp, K, 64, pix, K, 64, 64, splits=splits, accumulate=True)   # dWp[K][64] = dY^T Xcol
+        _channel_copy(dwp, dw, K, 64, Cc * R * S, Cc * R * S, accumulate=True)                     # += into OIHW
+        if db is not None:
+            db += dy.sum(dim=(0, 2, 3))
+        return True
     if _is_3x3(shp, shp[3], shp[4]) and shp[3] % 64 == 0 and shp[4] % 64 == 0:
         N, H, W, Cc, K = shp[:5]
         pix = N * H * W

@@ -233,6 +233,10 @@ int fedb_conv3x3_wgrad_bf16(const uint16_t* dY, const uint16_t* X, float* dWk, i
 /* mode 0: OIHW -> [K][tap][C]; mode 1: OIHW -> [C][flipped tap][K] (data gradient); mode 2: [K][tap][C] -> OIHW */
 int fedb_pack_filter(const float* w_oihw, float* out, int K, int C, int mode, int taps, void* stream);
 int fedb_pack3x3(const float* w_oihw, float* out, int K, int C, int mode, void* stream);
+/* im2col for tiny reductions (Cin*fs*fs <= 32, the 3-channel stems): NHWC x -> [pixels][32] fp32 and/or [pixels][64] bf16,
+ * column = OIHW flattening of the filter, zero padded; the convolution and its weight gradient become plain GEMMs */
+int fedb_im2col_small(const float* x, float* out_f32, uint16_t* out_bf16, int N, int H, int W, int C, int fs, int stride,
+                      int pad, void* stream);
 int fedb_cast_bf16(const float* src, uint16_t* dst, long long n, void* stream);          /* n % 4 == 0 */
 int fedb_transpose(const float* in, float* out, int rows, int cols, void* stream);        /* out[cols][rows] */
 

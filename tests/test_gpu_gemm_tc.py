@@ -114,3 +114,27 @@ def test_strided_conv_on_tensor_cores(G, B, C, K, HW, fs):
     # the data gradient runs as four parity-class implicit GEMMs in TF32
     torch.testing.assert_close(xb.grad.cpu(), xa.grad, rtol=3e-3, atol=3e-3 * float(xa.grad.abs().max()))
     torch.testing.assert_close(wb.grad.cpu(), wa.grad, rtol=1e-2, atol=1e-2 * float(wa.grad.abs().max()))
+
+
+@pytest.mark.parametrize("B,K,HW,bias", [(8, 64, 32, False), (4, 32, 32, True), (16, 128, 16, False)])
+def test_stem_conv_through_im2col_gemm(G, B, K, HW, bias):
+    """3-channel stems: Cin*9 = 27 is padded to one 32-wide K tile by an explicit im2col, then the GEMM kernel runs the
+    forward (TF32) and, when Cout is a multiple of 64, the weight gradient (bf16, split over pixels)."""
+    import torch.nn.functional as TF
+    from fedb200.ops import functional as F
+    torch.manual_seed(6)
+    x = torch.randn(B, 3, HW, HW)
+    w = torch.randn(K, 3, 3, 3) * 0.2
+    b = torch.randn(K) if bias else None
+    wa = w.clone().requires_grad_(True)
+    wb = w.clone().to(DEV).requires_grad_(True)
+    ba = b.clone().requires_grad_(True) if bias else None
+    bb = b.clone().to(DEV).requires_grad_(True) if bias else None
+    ya = TF.conv2d(x, wa, ba, 1, 1)
+    yb = F.conv2d(x.to(DEV), wb, bb, 1, 1, 1)
+    torch.testing.assert_close(yb.cpu(), ya.detach(), rtol=3e-3, atol=3e-3 * float(ya.detach().abs().max()))
+    g = torch.randn_like(ya)
+    ya.backward(g), yb.backward(g.to(DEV))
+    torch.testing.assert_close(wb.grad.cpu(), wa.grad, rtol=1e-2, atol=1e-2 * float(wa.grad.abs().max()))
+    if bias:
+        torch.testing.assert_close(bb.grad.cpu(), ba.grad, rtol=1e-3, atol=1e-3 * float(ba.grad.abs().max()))
