@@ -46,9 +46,13 @@ def _bind():
         "fedb_nn_channel_copy": [_vp, _vp, _ll, _i, _i, _i, _i, _i, _i, _i, _vp],
         "fedb_nn_linear_fwd": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
         "fedb_nn_linear_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],
+        "fedb_dw_conv_fwd": [_vp, _vp, _vp, _vp, ip, _vp],
+        "fedb_dw_conv_dgrad": [_vp, _vp, _vp, ip, _vp],
+        "fedb_dw_conv_wgrad": [_vp, _vp, _vp, _vp, ip, _vp],
     }
     for name, args in sigs.items():
         _lib.bind(name, C.c_int, args)
+    _lib.bind("fedb_dw_conv_wgrad_scratch", C.c_longlong, [ip])
     _BOUND = True
 
 
@@ -79,6 +83,17 @@ def _conv_shape(x, w, stride, padding, groups):
     return (N, H, W, Cc, K, R, S, P, Q, stride[0], stride[1], padding[0], padding[1], groups)
 
 
+def _is_depthwise(shp) -> bool:
+    """3x3 depthwise (groups == Cin == Cout), channels a multiple of 4: the streaming kernels of csrc/depthwise.cu."""
+    N, H, W, Cc, K, R, S, P, Q, sh, sw, ph, pw, groups = shp
+    return groups == Cc == K and R == 3 and S == 3 and Cc % 4 == 0
+
+
+def _dw_shape(shp):
+    N, H, W, Cc, K, R, S, P, Q, sh, sw, ph, pw, groups = shp
+    return _ints(N, H, W, Cc, P, Q, sh, sw, ph, pw)
+
+
 class _Conv2d(torch.autograd.Function):
     @staticmethod
     def forward(ctx, x, w, bias, stride, padding, groups):
@@ -87,7 +102,11 @@ class _Conv2d(torch.autograd.Function):
         N, H, W, Cc, K, R, S, P, Q = shp[:9]
         y = torch.empty((N, K, P, Q), dtype=torch.float32, device=x.device, memory_format=CL)
         from . import cuda_tc
-        if cuda_tc.conv_forward(x, w, bias, y, shp):
+        ctx.dw = _is_depthwise(shp)
+        if ctx.dw:
+            ctx.tc = False
+            _call("fedb_dw_conv_fwd", x.data_ptr(), w.data_ptr(), _p(bias), y.data_ptr(), _dw_shape(shp), current_stream())
+        elif cuda_tc.conv_forward(x, w, bias, y, shp):
             ctx.tc = True
         else:
             ctx.tc = False
@@ -107,6 +126,19 @@ class _Conv2d(torch.autograd.Function):
         dy = _cl(dy)
         dx = dw = db = None
         from . import cuda_tc
+        if ctx.dw:
+            if ctx.needs_input_grad[0]:
+                dx = torch.empty_like(x, memory_format=CL)
+                _call("fedb_dw_conv_dgrad", dy.data_ptr(), w.data_ptr(), dx.data_ptr(), _dw_shape(shp), current_stream())
+            if ctx.needs_input_grad[1]:
+                dw = torch.zeros_like(w)
+                ds = _dw_shape(shp)
+                _bind()
+                scratch = torch.empty(int(lib().fedb_dw_conv_wgrad_scratch(ds)), dtype=torch.float32, device=x.device)
+                _call("fedb_dw_conv_wgrad", x.data_ptr(), dy.data_ptr(), dw.data_ptr(), scratch.data_ptr(), ds,
+                      current_stream(), launches=2)
+                db = dy.sum(dim=(0, 2, 3)) if ctx.has_bias else None
+            return dx, dw, db, None, None, None
         if ctx.needs_input_grad[0]:
             dx = torch.empty_like(x, memory_format=CL)
             if not cuda_tc.conv_dgrad(dy, w, dx, shp):

@@ -245,7 +245,7 @@ int fedb_transpose(const float* in, float* out, int rows, int cols, void* stream
  * take: grouped / depthwise / odd-sized convolutions, batch norm, activations, pooling, channel cat/slice/shuffle,
  * squeeze-excite gates, drop-connect masks, the classifier.
  * shape14 = {N,H,W,C,K,R,S,P,Q,stride_h,stride_w,pad_h,pad_w,groups}; shape12 = {N,H,W,C,P,Q,kh,kw,sh,sw,ph,pw}.
- * act: 0 none, 1 relu, 2 sigmoid, 3 swish. */
+ * act: 0 none, 1 relu, 2 swish, 3 sigmoid. */
 int fedb_nn_weight_transpose(const float* w, float* wt, float* wt2, int K, int Cg, int R, int S, void* stream);
 int fedb_nn_conv_fwd(const float* x, const float* wt, const float* bias, float* y, const int* shape14, void* stream);
 int fedb_nn_conv_dgrad(const float* dy, const float* wt2, float* dx, const int* shape14, void* stream);
@@ -273,6 +273,16 @@ int fedb_nn_channel_copy(const float* in, float* out, long long rows, int Cin, i
 int fedb_nn_linear_fwd(const float* x, const float* W, const float* bias, float* y, int B, int K, int J, int act, void* stream);
 int fedb_nn_linear_bwd(const float* dy, const float* x, const float* W, float* dx, float* dW, float* db, int B, int K, int J,
                        void* stream);
+
+/* ------------------------------------------------------------------ depthwise 3x3 convolution (csrc/depthwise.cu)
+ * groups == Cin == Cout, NHWC fp32, any stride / padding, C % 4 == 0; w is OIHW = [C][1][3][3].
+ * shape10 = {N, H, W, C, P, Q, stride_h, stride_w, pad_h, pad_w}.  Streaming kernels: four channels per thread, taps in
+ * registers; the weight gradient is a two-pass deterministic reduction through caller-owned scratch.
+ * reference: src/models/mobilenet.py:14-17, mobilenetv2.py:20-22, efficientnet.py:60-67, shufflenetv2.py:33-36 */
+int fedb_dw_conv_fwd(const float* x, const float* w, const float* bias, float* y, const int* shape10, void* stream);
+int fedb_dw_conv_dgrad(const float* dy, const float* w, float* dx, const int* shape10, void* stream);
+long long fedb_dw_conv_wgrad_scratch(const int* shape10);          /* floats */
+int fedb_dw_conv_wgrad(const float* x, const float* dy, float* dw, float* scratch, const int* shape10, void* stream);
 
 #ifdef __cplusplus
 }

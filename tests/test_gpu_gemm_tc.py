@@ -20,7 +20,7 @@ def _tol(K):
 
 
 @pytest.mark.parametrize("M,N,K", [(128, 128, 32), (256, 64, 96), (1000, 32, 64), (4096, 512, 512), (300, 192, 160),
-                                   (2048, 1024, 512)])
+                                   (2048, 1024, 512), (300, 24, 40), (512, 144, 24), (130, 6, 16)])   # K / N tails
 def test_gemm_nt(G, M, N, K):
     torch.manual_seed(0)
     a, b = torch.randn(M, K, device=DEV), torch.randn(N, K, device=DEV)
@@ -31,7 +31,7 @@ def test_gemm_nt(G, M, N, K):
 
 
 @pytest.mark.parametrize("M,N,K,splits", [(128, 128, 256, 1), (256, 64, 4096, 8), (512, 512, 2048, 4), (64, 64, 8192, 16),
-                                          (1024, 512, 512, 2)])
+                                          (1024, 512, 512, 2), (24, 144, 1000, 3), (96, 16, 520, 1)])     # M / N / K tails
 def test_gemm_bf16_tn_split_k(G, M, N, K, splits):
     """wgrad form: D[M,N] = A^T B with A stored [K][M], B stored [K][N] (bf16), reduction split over CTAs."""
     torch.manual_seed(2)

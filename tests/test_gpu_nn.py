@@ -45,6 +45,8 @@ CONVS = [  # cin, cout, k, stride, pad, groups, bias, hw
     (32, 32, 3, 1, 1, 32, False, 8), (32, 32, 3, 2, 1, 32, False, 8), (48, 48, 5, 1, 2, 48, False, 8),
     (44, 88, 7, 2, 3, 44, False, 16), (64, 64, 3, 1, 1, 8, False, 8), (24, 60, 1, 1, 0, 3, False, 8),
     (16, 24, 3, 1, 1, 1, True, 8), (64, 128, 1, 2, 0, 1, False, 8), (3, 6, 5, 1, 0, 1, True, 32),
+    # depthwise 3x3 (csrc/depthwise.cu): 32 / 16 / 8 channel quads per block row, bias, odd maps, stride 2
+    (128, 128, 3, 1, 1, 128, True, 16), (64, 64, 3, 2, 1, 64, False, 7), (36, 36, 3, 1, 1, 36, False, 11),
 ]
 
 
