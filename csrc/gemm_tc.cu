@@ -410,19 +410,21 @@ int make_map_nhwc(CUtensorMap* map, const void* base, int elem, int N, int H, in
 // mode 0 (forward):  Wk[k][(r*3+s)*C + c] = W[k][c][r][s]
 // mode 1 (dgrad):    Wd[c][(r*3+s)*K + k] = W[k][c][2-r][2-s]     (transposed + spatially flipped filter)
 // mode 2 (unpack):   dW[k][c][r][s] += dWk[k][(r*3+s)*C + c]      (packed weight gradient back to OIHW)
+// Rp = reduction channels rounded up to the K tile (32): the packed matrices of modes 0 / 1 carry zeros in the tail of
+// every tap so that a tap always starts on a K-tile boundary (the activation side gets its zeros from TMA).
 __global__ void __launch_bounds__(256) pack3x3_kernel(const float* __restrict__ w, float* __restrict__ out, int K, int C, int mode,
-                                                     int T /* taps: 9 or 1 */) {
-  const int total = K * C * T;
+                                                     int T /* taps: 9 or 1 */, int Rp) {
+  const int total = mode == 0 ? K * T * Rp : (mode == 1 ? C * 9 * Rp : K * C * T);
   for (int i = blockIdx.x * 256 + threadIdx.x; i < total; i += gridDim.x * 256) {
     if (mode == 0) {
-      const int c = i % C, tap = (i / C) % T, k = i / (T * C);
-      out[i] = w[(k * C + c) * T + tap];
+      const int c = i % Rp, tap = (i / Rp) % T, k = i / (T * Rp);
+      out[i] = c < C ? w[(k * C + c) * T + tap] : 0.f;
     } else if (mode == 2) {
       const int c = i % C, tap = (i / C) % T, k = i / (T * C);
       out[(k * C + c) * T + tap] += w[i];
     } else {
-      const int k = i % K, tap = (i / K) % 9, c = i / (9 * K);
-      out[i] = w[(k * C + c) * 9 + (8 - tap)];
+      const int k = i % Rp, tap = (i / Rp) % 9, c = i / (9 * Rp);
+      out[i] = k < K ? w[(k * C + c) * 9 + (8 - tap)] : 0.f;
     }
   }
 }
@@ -522,7 +524,7 @@ extern "C" int fedb_gemm_bf16_tn(const uint16_t* At, const uint16_t* Bt, float* 
 // roles gives the data gradient).  P = H/stride, Q = W/stride ("same"-style geometry of the CIFAR zoo).
 extern "C" int fedb_conv_tf32(const float* X, const float* Wk, float* Y, const float* bias, int N, int H, int W, int Cin,
                               int Cout, int fs, int stride, int pad, int relu, void* stream) {
-  FEDB_REQUIRE(Cin % 32 == 0 && Cout % 4 == 0, "fedb_conv_tf32: Cin must be a multiple of 32");
+  FEDB_REQUIRE(Cin % 4 == 0, "fedb_conv_tf32: Cin must be a multiple of 4 (16-byte pixel pitch)");
   FEDB_REQUIRE((fs == 3 && pad == 1) || (fs == 1 && pad == 0), "fedb_conv_tf32: 3x3/pad 1 or 1x1/pad 0");
   FEDB_REQUIRE(stride == 1 || stride == 2, "fedb_conv_tf32: stride 1 or 2");
   const int P = H / stride, Q = W / stride;
@@ -533,14 +535,18 @@ extern "C" int fedb_conv_tf32(const float* X, const float* Wk, float* Y, const f
   if (bh > P) bh = P;
   const int bn = 128 / (bw * bh);
   FEDB_REQUIRE(bw * bh * bn == 128 && (bn == 1 || bh == P), "fedb_conv_tf32: unsupported tile geometry");
-  const int M = N * P * Q, K = fs * fs * Cin;
+  // every tap occupies ceil(Cin / 32) K tiles: the activation tail comes back as zeros from TMA (channel index out of
+  // bounds), the packed filter carries explicit zeros (fedb_pack_filter); a 1x1 filter needs no packing at all
+  const int cin_pad = (Cin + 31) / 32 * 32;
+  const int M = N * P * Q, K = fs * fs * cin_pad;
   const int bnt = Cout >= 128 ? 128 : (Cout > 32 ? 64 : 32);
   CUtensorMap ma, mb;
   if (int rc = make_map_nhwc(&ma, X, 4, N, H, W, Cin, bw, bh, bn, stride)) return rc;
-  if (int rc = make_map_2d(&mb, Wk, 4, Cout, K, K, 32, bnt)) return rc;
+  if (fs == 1) { if (int rc = make_map_2d(&mb, Wk, 4, Cout, Cin, Cin, 32, bnt)) return rc; }
+  else if (int rc = make_map_2d(&mb, Wk, 4, Cout, K, K, 32, bnt)) return rc;
   GemmArgs g;
   g.D = Y; g.bias = bias; g.ldd = Cout; g.M = M; g.N = Cout; g.K = K; g.k_per_split = K; g.relu = relu; g.atomic_out = 0;
-  g.conv = 1; g.Cin = Cin; g.H = P; g.W = Q; g.bw = bw; g.bh = bh; g.bn = bn; g.cstride = stride; g.cpad = pad; g.fs = fs;
+  g.conv = 1; g.Cin = cin_pad; g.H = P; g.W = Q; g.bw = bw; g.bh = bh; g.bn = bn; g.cstride = stride; g.cpad = pad; g.fs = fs;
   g.ostride = g.oy = g.ox = 0;
   return dispatch_bn<0>(bnt, ma, mb, g, 1, (cudaStream_t)stream);
 }
@@ -549,7 +555,8 @@ extern "C" int fedb_conv_tf32(const float* X, const float* Wk, float* Y, const f
 //   class (a, b), a = h % 2, b = w % 2 of the dX pixel; rows: a == 0 -> filter row 1 (dY row p'), a == 1 -> filter row 2
 //   (dY row p') then row 0 (dY row p'+1); columns likewise.  out = [class][c][tap][k], classes (0,0),(0,1),(1,0),(1,1)
 //   with 1, 2, 2, 4 taps: class offsets 0, 1, 3, 5 in units of C*K floats.
-__global__ void __launch_bounds__(256) pack_dgrad_s2_kernel(const float* __restrict__ w, float* __restrict__ out, int K, int C) {
+__global__ void __launch_bounds__(256) pack_dgrad_s2_kernel(const float* __restrict__ w, float* __restrict__ out, int Kreal, int C,
+                                                           int K /* Kreal rounded up to 32 */) {
   const int total = 9 * K * C;
   for (int i = blockIdx.x * 256 + threadIdx.x; i < total; i += gridDim.x * 256) {
     const int unit = i / (K * C);                       // 0..8: which (class, tap)
@@ -561,14 +568,15 @@ __global__ void __launch_bounds__(256) pack_dgrad_s2_kernel(const float* __restr
     const int k = j % K, t = (j / K) % T, c = j / (K * T);
     const int rr = t / fc, ss = t % fc;
     const int r = a == 0 ? 1 : (rr == 0 ? 2 : 0), sx = b == 0 ? 1 : (ss == 0 ? 2 : 0);
-    out[i] = w[((k * C + c) * 3 + r) * 3 + sx];
+    out[i] = k < Kreal ? w[((k * C + c) * 3 + r) * 3 + sx] : 0.f;
   }
 }
 
 extern "C" int fedb_pack_dgrad_s2(const float* w_oihw, float* out, int K, int C, void* stream) {
-  int blocks = fedb_ceil_div((long long)K * C * 9, 256);
+  const int Kp = (K + 31) / 32 * 32;                    // out holds 9 * C * Kp floats
+  int blocks = fedb_ceil_div((long long)Kp * C * 9, 256);
   if (blocks > fedb_num_sms() * 8) blocks = fedb_num_sms() * 8;
-  pack_dgrad_s2_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w_oihw, out, K, C);
+  pack_dgrad_s2_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w_oihw, out, K, C, Kp);
   FEDB_LAUNCH_OK();
   return 0;
 }
@@ -579,7 +587,8 @@ extern "C" int fedb_pack_dgrad_s2(const float* w_oihw, float* out, int K, int C,
 // ([Cin][Cout]); only class (0,0) receives gradient, the caller zero-fills dX first.
 extern "C" int fedb_conv_dgrad_s2_tf32(const float* dY, const float* Wcls, float* dX, int N, int P, int Q, int Cout, int Cin,
                                        int fs, void* stream) {
-  FEDB_REQUIRE(Cout % 32 == 0 && Cin % 4 == 0, "fedb_conv_dgrad_s2_tf32: Cout % 32, Cin % 4");
+  FEDB_REQUIRE(Cout % 4 == 0, "fedb_conv_dgrad_s2_tf32: Cout must be a multiple of 4 (16-byte pixel pitch)");
+  const int cout_pad = (Cout + 31) / 32 * 32;
   FEDB_REQUIRE(fs == 1 || fs == 3, "fedb_conv_dgrad_s2_tf32: 1x1 or 3x3");
   FEDB_REQUIRE(Q <= 32 && Q >= 2 && (Q & (Q - 1)) == 0 && (P & (P - 1)) == 0, "fedb_conv_dgrad_s2_tf32: dY maps must be powers of two");
   const int bw = Q;
@@ -595,11 +604,12 @@ extern "C" int fedb_conv_dgrad_s2_tf32(const float* dY, const float* Wcls, float
   for (int cls = 0; cls < ncls; ++cls) {
     const int a = cls >> 1, b = cls & 1;
     const int taps = fs == 3 ? (a + 1) * (b + 1) : 1;
-    const int K = taps * Cout;
-    if (int rc = make_map_2d(&mb, Wcls + (size_t)base[cls] * Cin * Cout, 4, Cin, K, K, 32, bnt)) return rc;
+    const int K = taps * cout_pad;
+    if (fs == 1) { if (int rc = make_map_2d(&mb, Wcls, 4, Cin, Cout, Cout, 32, bnt)) return rc; }
+    else if (int rc = make_map_2d(&mb, Wcls + (size_t)base[cls] * Cin * cout_pad, 4, Cin, K, K, 32, bnt)) return rc;
     GemmArgs g;
     g.D = dX; g.bias = nullptr; g.ldd = Cin; g.M = N * P * Q; g.N = Cin; g.K = K; g.k_per_split = K; g.relu = 0; g.atomic_out = 0;
-    g.conv = 1; g.Cin = Cout; g.H = P; g.W = Q; g.bw = bw; g.bh = bh; g.bn = bn; g.cstride = 1; g.cpad = 0; g.fs = b + 1;
+    g.conv = 1; g.Cin = cout_pad; g.H = P; g.W = Q; g.bw = bw; g.bh = bh; g.bn = bn; g.cstride = 1; g.cpad = 0; g.fs = b + 1;
     g.ostride = 2; g.oy = a; g.ox = b;
     if (int rc = dispatch_bn<0>(bnt, ma, mb, g, 1, (cudaStream_t)stream)) return rc;
   }
@@ -616,7 +626,7 @@ extern "C" int fedb_conv3x3_tf32(const float* X, const float* Wk, float* Y, cons
 // caller).  Strided convolutions read X through a tensor map with element strides.
 extern "C" int fedb_conv_wgrad_bf16(const uint16_t* dY, const uint16_t* X, float* dWk, int N, int H, int W, int Cin, int Cout,
                                     int fs, int stride, int pad, int splits, void* stream) {
-  FEDB_REQUIRE(Cin % 64 == 0 && Cout % 64 == 0, "fedb_conv_wgrad_bf16: channels must be multiples of 64");
+  FEDB_REQUIRE(Cin % 8 == 0 && Cout % 8 == 0, "fedb_conv_wgrad_bf16: channels must be multiples of 8 (16-byte bf16 pitch)");
   FEDB_REQUIRE((fs == 3 && pad == 1) || (fs == 1 && pad == 0), "fedb_conv_wgrad_bf16: 3x3/pad 1 or 1x1/pad 0");
   FEDB_REQUIRE(stride == 1 || stride == 2, "fedb_conv_wgrad_bf16: stride 1 or 2");
   const int P = H / stride, Q = W / stride;
@@ -665,9 +675,11 @@ extern "C" int fedb_conv3x3_wgrad_bf16(const uint16_t* dY, const uint16_t* X, fl
 // filter (un)packing for fs*fs = taps (9 or 1); see pack3x3_kernel for the modes
 extern "C" int fedb_pack_filter(const float* w_oihw, float* out, int K, int C, int mode, int taps, void* stream) {
   FEDB_REQUIRE(taps == 9 || (taps == 1 && mode != 1), "fedb_pack_filter: taps 9, or 1 for modes 0/2");
-  int blocks = fedb_ceil_div((long long)K * C * taps, 256);
+  const int Rp = mode == 0 ? (C + 31) / 32 * 32 : (mode == 1 ? (K + 31) / 32 * 32 : 0);
+  const long long total = mode == 0 ? (long long)K * taps * Rp : (mode == 1 ? (long long)C * 9 * Rp : (long long)K * C * taps);
+  int blocks = fedb_ceil_div(total, 256);
   if (blocks > fedb_num_sms() * 8) blocks = fedb_num_sms() * 8;
-  pack3x3_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w_oihw, out, K, C, mode, taps);
+  pack3x3_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w_oihw, out, K, C, mode, taps, Rp);
   FEDB_LAUNCH_OK();
   return 0;
 }
@@ -675,7 +687,8 @@ extern "C" int fedb_pack_filter(const float* w_oihw, float* out, int K, int C, i
 extern "C" int fedb_pack3x3(const float* w_oihw, float* out, int K, int C, int mode, void* stream) {
   int blocks = fedb_ceil_div((long long)K * C * 9, 256);
   if (blocks > fedb_num_sms() * 8) blocks = fedb_num_sms() * 8;
-  pack3x3_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w_oihw, out, K, C, mode, 9);
+  FEDB_REQUIRE((mode == 0 ? C : (mode == 1 ? K : 32)) % 32 == 0, "fedb_pack3x3: unpadded form, use fedb_pack_filter");
+  pack3x3_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w_oihw, out, K, C, mode, 9, mode == 0 ? C : K);
   FEDB_LAUNCH_OK();
   return 0;
 }

@@ -93,9 +93,11 @@ def _pow2(v: int) -> bool:
 
 
 def _is_3x3(shp, cin, cout) -> bool:
-    """3x3 / stride 1 / pad 1 / ungrouped, `cin` (the GEMM's reduction channels) a multiple of 32, power-of-two maps."""
+    """3x3 / stride 1 / pad 1 / ungrouped, power-of-two maps; `cin` (the GEMM's reduction channels) only needs the 16-byte
+    pixel pitch: every tap is padded to whole 32-channel K tiles (zeros from TMA on the activation side, explicit zeros
+    in the packed filter)."""
     N, H, W, Cc, K, R, S, P, Q, sh, sw, ph, pw, groups = shp
-    return (R == 3 and S == 3 and sh == 1 and sw == 1 and ph == 1 and pw == 1 and groups == 1 and cin % 32 == 0
+    return (R == 3 and S == 3 and sh == 1 and sw == 1 and ph == 1 and pw == 1 and groups == 1 and cin % 4 == 0
             and cout % 4 == 0 and _pow2(H) and _pow2(W) and 2 <= W <= 32 and N * H * W >= MIN_PIXELS
             and (128 // W <= H or (128 // (W * H)) >= 1))
 
@@ -113,20 +115,22 @@ def _strided(shp):
     return R, 2, ph
 
 
+def _pad32(v: int) -> int:
+    return (v + 31) // 32 * 32
+
+
 def pack_filter(w, mode: int, taps: int) -> torch.Tensor:
+    """mode 0: OIHW -> [K][tap][C padded to 32] (forward); mode 1: -> [C][flipped tap][K padded to 32] (data gradient)."""
     K, Cc = w.shape[0], w.shape[1]
-    out = torch.empty(K * Cc * taps, dtype=torch.float32, device=w.device)
+    n = K * taps * _pad32(Cc) if mode == 0 else Cc * 9 * _pad32(K)
+    out = torch.empty(n, dtype=torch.float32, device=w.device)
     check(_f("fedb_pack_filter")(w.data_ptr(), out.data_ptr(), K, Cc, mode, taps, current_stream()), "fedb_pack_filter")
     _lib.count_launch()
     return out
 
 
 def pack3x3(w, mode: int) -> torch.Tensor:
-    K, Cc = w.shape[0], w.shape[1]
-    out = torch.empty(K * Cc * 9, dtype=torch.float32, device=w.device)
-    check(_f("fedb_pack3x3")(w.data_ptr(), out.data_ptr(), K, Cc, mode, current_stream()), "fedb_pack3x3")
-    _lib.count_launch()
-    return out
+    return pack_filter(w, mode, 9)
 
 
 def conv3x3_tf32(x, wk, y, bias, N, H, W, cin, cout, relu=False):
@@ -171,7 +175,7 @@ def conv_forward(x, w, bias, y, shp) -> bool:
         conv3x3_tf32(x, pack3x3(w, 0), y, bias, N, H, W, Cc, K)      # implicit GEMM, shifted TMA boxes per tap
         return True
     st = _strided(shp)
-    if st is not None and shp[3] % 32 == 0 and shp[4] % 4 == 0:
+    if st is not None and shp[3] % 4 == 0 and shp[4] % 4 == 0:
         N, H, W, Cc, K = shp[:5]
         fs, stride, pad = st
         wk = pack_filter(w, 0, 9) if fs == 3 else w                  # a 1x1 filter already is [Cout][Cin]
@@ -192,12 +196,12 @@ def conv_dgrad(dy, w, dx, shp) -> bool:
         conv3x3_tf32(dy, pack3x3(w, 1), dx, None, N, H, W, K, Cc)    # dX = conv3x3(dY, flipped + transposed filter)
         return True
     st = _strided(shp)
-    if st is not None and shp[4] % 32 == 0 and shp[3] % 4 == 0:
+    if st is not None and shp[4] % 4 == 0 and shp[3] % 4 == 0:
         # stride 2: four parity classes of dX, each a dense stride-1 implicit GEMM over dY, scattered by the epilogue
         N, H, W, Cc, K, _, _, P, Q = shp[:9]
         fs = st[0]
         if fs == 3:
-            wc = torch.empty(9 * K * Cc, dtype=torch.float32, device=w.device)
+            wc = torch.empty(9 * _pad32(K) * Cc, dtype=torch.float32, device=w.device)
             check(_f("fedb_pack_dgrad_s2")(w.data_ptr(), wc.data_ptr(), K, Cc, current_stream()), "fedb_pack_dgrad_s2")
             _lib.count_launch()
         else:
@@ -228,7 +232,7 @@ def conv_wgrad(x, dy, dw, db, shp) -> bool:
         if db is not None:
             db += dy.sum(dim=(0, 2, 3))
         return True
-    if _is_3x3(shp, shp[3], shp[4]) and shp[3] % 64 == 0 and shp[4] % 64 == 0:
+    if _is_3x3(shp, shp[3], shp[4]) and shp[3] % 8 == 0 and shp[4] % 8 == 0:
         N, H, W, Cc, K = shp[:5]
         pix = N * H * W
         tiles = ((K + 127) // 128) * ((Cc + 127) // 128) * 9
@@ -244,7 +248,7 @@ def conv_wgrad(x, dy, dw, db, shp) -> bool:
             db += dy.sum(dim=(0, 2, 3))
         return True
     st = _strided(shp)
-    if st is not None and shp[3] % 64 == 0 and shp[4] % 64 == 0:
+    if st is not None and shp[3] % 8 == 0 and shp[4] % 8 == 0:
         N, H, W, Cc, K = shp[:5]
         fs, stride, pad = st
         taps, pix = fs * fs, N * shp[7] * shp[8]

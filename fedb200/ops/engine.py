@@ -15,6 +15,8 @@ graph (one graph launch = upload + every step of the pass).  Loss / accuracy cou
 """
 from __future__ import annotations
 
+import contextlib
+import gc
 from typing import Dict, List, Optional, Tuple
 
 import torch
@@ -22,6 +24,21 @@ import torch
 from ..utils import data as D
 from . import _lib
 from . import cuda as K
+
+
+@contextlib.contextmanager
+def _quiet_gc():
+    """No cyclic garbage collection while a stream capture is open: the collector may finalise objects of an EARLIER
+    engine (captured graphs with their private pools, pinned buffers), and the CUDA calls of those finalisers
+    (cudaFree, cudaFreeHost, cudaGraphExecDestroy) are illegal during a global-mode capture and invalidate it."""
+    gc.collect()
+    was = gc.isenabled()
+    gc.disable()
+    try:
+        yield
+    finally:
+        if was:
+            gc.enable()
 
 
 class CudaEngine:
@@ -191,7 +208,7 @@ class CudaEngine:
                     g = torch.cuda.CUDAGraph()
                     # the warm-up already trained one pass; that is a real pass, so count it and
                     # capture the graph (with or without the H2D branch) for the following rounds
-                    with torch.cuda.graph(g, stream=torch.cuda.Stream(device=self.dev)):
+                    with _quiet_gc(), torch.cuda.graph(g, stream=torch.cuda.Stream(device=self.dev)):
                         self._issue_steps(sh, upload, with_test)
                     graphs[key] = g
                 else:
@@ -289,7 +306,7 @@ class CudaEngine:
                     if self.cfg.use_cuda_graph:
                         torch.cuda.synchronize(self.dev)
                         g = torch.cuda.CUDAGraph()
-                        with torch.cuda.graph(g, stream=torch.cuda.Stream(device=self.dev)):
+                        with _quiet_gc(), torch.cuda.graph(g, stream=torch.cuda.Stream(device=self.dev)):
                             self._streamed(pairs, bounds, work, copy)
                         graphs[copy] = g
             else:

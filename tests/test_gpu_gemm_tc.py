@@ -70,7 +70,7 @@ def test_pointwise_conv_uses_tensor_cores_and_matches(G):
 
 
 @pytest.mark.parametrize("B,C,K,HW", [(4, 64, 64, 32), (8, 64, 128, 16), (16, 128, 256, 8), (32, 256, 512, 4), (64, 512, 512, 2),
-                                      (5, 32, 32, 8)])
+                                      (5, 32, 32, 8), (4, 48, 24, 16), (8, 96, 208, 8), (4, 16, 40, 32), (8, 128, 32, 16)])
 def test_conv3x3_implicit_gemm_fwd_and_dgrad(G, B, C, K, HW):
     """3x3 / stride 1 / pad 1 convolution as an implicit GEMM: every filter tap is a shifted 4-D TMA box of the NHWC
     activation (the zero padding comes from TMA's out-of-bounds fill)."""
@@ -93,7 +93,7 @@ def test_conv3x3_implicit_gemm_fwd_and_dgrad(G, B, C, K, HW):
 
 
 @pytest.mark.parametrize("B,C,K,HW,fs", [(4, 64, 128, 32, 3), (8, 128, 256, 16, 3), (16, 256, 512, 8, 3), (4, 64, 128, 32, 1),
-                                         (16, 256, 512, 8, 1), (64, 64, 64, 4, 3)])
+                                         (16, 256, 512, 8, 1), (64, 64, 64, 4, 3), (8, 48, 88, 16, 3), (8, 24, 56, 32, 1)])
 def test_strided_conv_on_tensor_cores(G, B, C, K, HW, fs):
     """Stride-2 3x3 / 1x1 convolutions: the TMA tensor map skips every other input pixel (element strides), so the
     forward and the weight gradient reuse the implicit-GEMM kernel; the data gradient is decomposed by the parity of the

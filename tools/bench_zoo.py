@@ -29,4 +29,6 @@ for name in names:
     print(json.dumps({"model": name, "steps": st.steps, "ms_per_step": ms / st.steps, "samples_per_s": st.samples / ms * 1e3,
                       "loss": st.mean_loss, "launches_per_step": (_lib.launches - l0) / max(st.steps, 1)}), flush=True)
     del t
+    import gc
+    gc.collect()
     torch.cuda.empty_cache()

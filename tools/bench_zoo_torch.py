@@ -21,7 +21,12 @@ dev = torch.device("cuda:0")
 def run(name, channels_last):
     torch.manual_seed(0)
     fmt = torch.channels_last if channels_last else torch.contiguous_format
-    ctor = (lambda: models.VGG(name)) if name.startswith("VGG") else getattr(models, name)
+    if name.startswith("VGG"):
+        ctor = lambda: models.VGG(name)                                            # noqa: E731
+    elif name.startswith("ShuffleNetV2_"):
+        ctor = lambda: models.ShuffleNetV2(net_size=float(name.split("_")[1]))     # noqa: E731
+    else:
+        ctor = getattr(models, name)
     net = ctor().to(dev).to(memory_format=fmt)
     opt = torch.optim.SGD(net.parameters(), lr=0.1, momentum=0.9, weight_decay=5e-4)
     crit = torch.nn.CrossEntropyLoss()
@@ -69,7 +74,11 @@ def run(name, channels_last):
 
 for name in names:
     try:
-        run(name, True)
-    except RuntimeError:          # some reference models call .view() on the activations: NCHW only
-        run(name, False)
+        try:
+            run(name, True)
+        except RuntimeError:      # some reference models call .view() on the activations: NCHW only
+            run(name, False)
+    except Exception as e:        # noqa: BLE001 - e.g. the reference's ShuffleNetG constructors raise TypeError (SURVEY B-list)
+        print(json.dumps({"model": name, "impl": "torch+cudnn (reference model code)", "error": f"{type(e).__name__}: {e}"[:160]}),
+              flush=True)
     torch.cuda.empty_cache()
