@@ -392,12 +392,13 @@ int make_map_2d(CUtensorMap* map, const void* base, int elem, long long rows, lo
 // 4-D NHWC activation [N][H][W][C] (fp32: elem 4, bf16: elem 2); box = [128 bytes of channels x bw x bh x bn],
 // 128B swizzle, zero fill outside
 int make_map_nhwc(CUtensorMap* map, const void* base, int elem, int N, int H, int W, int C, int bw, int bh, int bn,
-                  int estride = 1) {
+                  int estride = 1, long long pitch = 0 /* elements between pixels; 0 = C (dense) */) {
+  if (pitch <= 0) pitch = C;
   EncodeTiledFn enc;
   if (int rc = get_encode(&enc)) return rc;
-  FEDB_REQUIRE(((uintptr_t)base & 15) == 0 && (C * elem) % 16 == 0, "conv_tc: activation base/pitch must be 16-byte aligned");
+  FEDB_REQUIRE(((uintptr_t)base & 15) == 0 && (pitch * elem) % 16 == 0, "conv_tc: activation base/pitch must be 16-byte aligned");
   cuuint64_t dims[4] = {(cuuint64_t)C, (cuuint64_t)W, (cuuint64_t)H, (cuuint64_t)N};
-  cuuint64_t strides[3] = {(cuuint64_t)C * elem, (cuuint64_t)W * C * elem, (cuuint64_t)H * W * C * elem};
+  cuuint64_t strides[3] = {(cuuint64_t)pitch * elem, (cuuint64_t)W * pitch * elem, (cuuint64_t)H * W * pitch * elem};
   // with a traversal stride the box SPANS bw*stride input pixels and picks every stride-th one
   cuuint32_t box[4] = {(cuuint32_t)(128 / elem), (cuuint32_t)(bw * estride), (cuuint32_t)(bh * estride), (cuuint32_t)bn};
   cuuint32_t estr[4] = {1, (cuuint32_t)estride, (cuuint32_t)estride, 1};
@@ -522,8 +523,10 @@ extern "C" int fedb_gemm_bf16_tn(const uint16_t* At, const uint16_t* Bt, float* 
 // Y[N,P,Q,Cout] = conv(X[N,H,W,Cin]; fs x fs filter, stride 1|2, padding) as an implicit GEMM on the tensor cores.
 // Wk is the packed filter [Cout][fs*fs*Cin] (fedb_pack_filter mode 0; for 3x3/stride 1, mode 1 + swapped channel
 // roles gives the data gradient).  P = H/stride, Q = W/stride ("same"-style geometry of the CIFAR zoo).
-extern "C" int fedb_conv_tf32(const float* X, const float* Wk, float* Y, const float* bias, int N, int H, int W, int Cin,
-                              int Cout, int fs, int stride, int pad, int relu, void* stream) {
+// Grouped convolutions run one group per call: X / Y point at the group's first channel and xpitch / ypitch are the
+// channel counts of the WHOLE tensors (elements between consecutive pixels).
+extern "C" int fedb_conv_tf32_g(const float* X, const float* Wk, float* Y, const float* bias, int N, int H, int W, int Cin,
+                                int Cout, int fs, int stride, int pad, int relu, long long xpitch, long long ypitch, void* stream) {
   FEDB_REQUIRE(Cin % 4 == 0, "fedb_conv_tf32: Cin must be a multiple of 4 (16-byte pixel pitch)");
   FEDB_REQUIRE((fs == 3 && pad == 1) || (fs == 1 && pad == 0), "fedb_conv_tf32: 3x3/pad 1 or 1x1/pad 0");
   FEDB_REQUIRE(stride == 1 || stride == 2, "fedb_conv_tf32: stride 1 or 2");
@@ -541,11 +544,12 @@ extern "C" int fedb_conv_tf32(const float* X, const float* Wk, float* Y, const f
   const int M = N * P * Q, K = fs * fs * cin_pad;
   const int bnt = Cout >= 128 ? 128 : (Cout > 32 ? 64 : 32);
   CUtensorMap ma, mb;
-  if (int rc = make_map_nhwc(&ma, X, 4, N, H, W, Cin, bw, bh, bn, stride)) return rc;
+  if (int rc = make_map_nhwc(&ma, X, 4, N, H, W, Cin, bw, bh, bn, stride, xpitch)) return rc;
   if (fs == 1) { if (int rc = make_map_2d(&mb, Wk, 4, Cout, Cin, Cin, 32, bnt)) return rc; }
   else if (int rc = make_map_2d(&mb, Wk, 4, Cout, K, K, 32, bnt)) return rc;
   GemmArgs g;
-  g.D = Y; g.bias = bias; g.ldd = Cout; g.M = M; g.N = Cout; g.K = K; g.k_per_split = K; g.relu = relu; g.atomic_out = 0;
+  g.D = Y; g.bias = bias; g.ldd = ypitch > 0 ? ypitch : Cout; g.M = M; g.N = Cout; g.K = K; g.k_per_split = K; g.relu = relu;
+  g.atomic_out = 0;
   g.conv = 1; g.Cin = cin_pad; g.H = P; g.W = Q; g.bw = bw; g.bh = bh; g.bn = bn; g.cstride = stride; g.cpad = pad; g.fs = fs;
   g.ostride = g.oy = g.ox = 0;
   return dispatch_bn<0>(bnt, ma, mb, g, 1, (cudaStream_t)stream);
@@ -585,8 +589,8 @@ extern "C" int fedb_pack_dgrad_s2(const float* w_oihw, float* out, int K, int C,
 // sees a dense 1x1 / 1x2 / 2x1 / 2x2 filter over dY), written straight into the interleaved positions of dX by the
 // epilogue.  dY [N,P,Q,Cout], dX [N,2P,2Q,Cin].  fs == 3: Wcls from fedb_pack_dgrad_s2.  fs == 1: Wcls = W^T
 // ([Cin][Cout]); only class (0,0) receives gradient, the caller zero-fills dX first.
-extern "C" int fedb_conv_dgrad_s2_tf32(const float* dY, const float* Wcls, float* dX, int N, int P, int Q, int Cout, int Cin,
-                                       int fs, void* stream) {
+extern "C" int fedb_conv_dgrad_s2_tf32_g(const float* dY, const float* Wcls, float* dX, int N, int P, int Q, int Cout, int Cin,
+                                         int fs, long long dypitch, long long dxpitch, void* stream) {
   FEDB_REQUIRE(Cout % 4 == 0, "fedb_conv_dgrad_s2_tf32: Cout must be a multiple of 4 (16-byte pixel pitch)");
   const int cout_pad = (Cout + 31) / 32 * 32;
   FEDB_REQUIRE(fs == 1 || fs == 3, "fedb_conv_dgrad_s2_tf32: 1x1 or 3x3");
@@ -598,7 +602,7 @@ extern "C" int fedb_conv_dgrad_s2_tf32(const float* dY, const float* Wcls, float
   FEDB_REQUIRE(bw * bh * bn == 128 && (bn == 1 || bh == P), "fedb_conv_dgrad_s2_tf32: unsupported tile geometry");
   const int bnt = Cin >= 128 ? 128 : (Cin > 32 ? 64 : 32);
   CUtensorMap ma, mb;
-  if (int rc = make_map_nhwc(&ma, dY, 4, N, P, Q, Cout, bw, bh, bn, 1)) return rc;
+  if (int rc = make_map_nhwc(&ma, dY, 4, N, P, Q, Cout, bw, bh, bn, 1, dypitch)) return rc;
   const int ncls = fs == 3 ? 4 : 1;
   const int base[4] = {0, 1, 3, 5};
   for (int cls = 0; cls < ncls; ++cls) {
@@ -608,12 +612,22 @@ extern "C" int fedb_conv_dgrad_s2_tf32(const float* dY, const float* Wcls, float
     if (fs == 1) { if (int rc = make_map_2d(&mb, Wcls, 4, Cin, Cout, Cout, 32, bnt)) return rc; }
     else if (int rc = make_map_2d(&mb, Wcls + (size_t)base[cls] * Cin * cout_pad, 4, Cin, K, K, 32, bnt)) return rc;
     GemmArgs g;
-    g.D = dX; g.bias = nullptr; g.ldd = Cin; g.M = N * P * Q; g.N = Cin; g.K = K; g.k_per_split = K; g.relu = 0; g.atomic_out = 0;
+    g.D = dX; g.bias = nullptr; g.ldd = dxpitch > 0 ? dxpitch : Cin; g.M = N * P * Q; g.N = Cin; g.K = K; g.k_per_split = K; g.relu = 0; g.atomic_out = 0;
     g.conv = 1; g.Cin = cout_pad; g.H = P; g.W = Q; g.bw = bw; g.bh = bh; g.bn = bn; g.cstride = 1; g.cpad = 0; g.fs = b + 1;
     g.ostride = 2; g.oy = a; g.ox = b;
     if (int rc = dispatch_bn<0>(bnt, ma, mb, g, 1, (cudaStream_t)stream)) return rc;
   }
   return 0;
+}
+
+extern "C" int fedb_conv_dgrad_s2_tf32(const float* dY, const float* Wcls, float* dX, int N, int P, int Q, int Cout, int Cin,
+                                       int fs, void* stream) {
+  return fedb_conv_dgrad_s2_tf32_g(dY, Wcls, dX, N, P, Q, Cout, Cin, fs, 0, 0, stream);
+}
+
+extern "C" int fedb_conv_tf32(const float* X, const float* Wk, float* Y, const float* bias, int N, int H, int W, int Cin,
+                              int Cout, int fs, int stride, int pad, int relu, void* stream) {
+  return fedb_conv_tf32_g(X, Wk, Y, bias, N, H, W, Cin, Cout, fs, stride, pad, relu, 0, 0, stream);
 }
 
 extern "C" int fedb_conv3x3_tf32(const float* X, const float* Wk, float* Y, const float* bias, int N, int H, int W, int Cin,
@@ -624,8 +638,8 @@ extern "C" int fedb_conv3x3_tf32(const float* X, const float* Wk, float* Y, cons
 // dWk[Cout][fs*fs*Cin] (+)= sum over output pixels of dY[pix][Cout]^T * shift_tap(X)[pix][Cin]: bf16 copies of dY and X
 // (NHWC), reduction over the pixels split across CTAs, partial tiles combined with red.global.add (dWk zeroed by the
 // caller).  Strided convolutions read X through a tensor map with element strides.
-extern "C" int fedb_conv_wgrad_bf16(const uint16_t* dY, const uint16_t* X, float* dWk, int N, int H, int W, int Cin, int Cout,
-                                    int fs, int stride, int pad, int splits, void* stream) {
+extern "C" int fedb_conv_wgrad_bf16_g(const uint16_t* dY, const uint16_t* X, float* dWk, int N, int H, int W, int Cin, int Cout,
+                                      int fs, int stride, int pad, int splits, long long dypitch, long long xpitch, void* stream) {
   FEDB_REQUIRE(Cin % 8 == 0 && Cout % 8 == 0, "fedb_conv_wgrad_bf16: channels must be multiples of 8 (16-byte bf16 pitch)");
   FEDB_REQUIRE((fs == 3 && pad == 1) || (fs == 1 && pad == 0), "fedb_conv_wgrad_bf16: 3x3/pad 1 or 1x1/pad 0");
   FEDB_REQUIRE(stride == 1 || stride == 2, "fedb_conv_wgrad_bf16: stride 1 or 2");
@@ -640,8 +654,8 @@ extern "C" int fedb_conv_wgrad_bf16(const uint16_t* dY, const uint16_t* X, float
   const int pix = N * P * Q, taps = fs * fs;
   const int bnt = Cin >= 128 ? 128 : 64;
   CUtensorMap ma, mb;
-  if (int rc = make_map_2d(&ma, dY, 2, pix, Cout, Cout, 64, 64)) return rc;                  // A^T: [K=pix][M=Cout]
-  if (int rc = make_map_nhwc(&mb, X, 2, N, H, W, Cin, bw, bh, bn, stride)) return rc;        // B^T: shifted [pix][Cin]
+  if (int rc = make_map_2d(&ma, dY, 2, pix, Cout, dypitch > 0 ? dypitch : Cout, 64, 64)) return rc;   // A^T: [K=pix][M=Cout]
+  if (int rc = make_map_nhwc(&mb, X, 2, N, H, W, Cin, bw, bh, bn, stride, xpitch)) return rc;         // B^T: shifted [pix][Cin]
   GemmArgs g;
   g.D = dWk; g.bias = nullptr; g.ldd = (long long)taps * Cin; g.M = Cout; g.N = Cin;
   const int ktiles = (pix + 63) / 64;
@@ -665,6 +679,11 @@ extern "C" int fedb_conv_wgrad_bf16(const uint16_t* dY, const uint16_t* X, float
   }
   FEDB_LAUNCH_OK();
   return 0;
+}
+
+extern "C" int fedb_conv_wgrad_bf16(const uint16_t* dY, const uint16_t* X, float* dWk, int N, int H, int W, int Cin, int Cout,
+                                    int fs, int stride, int pad, int splits, void* stream) {
+  return fedb_conv_wgrad_bf16_g(dY, X, dWk, N, H, W, Cin, Cout, fs, stride, pad, splits, 0, 0, stream);
 }
 
 extern "C" int fedb_conv3x3_wgrad_bf16(const uint16_t* dY, const uint16_t* X, float* dWk, int N, int H, int W, int Cin, int Cout,

@@ -36,6 +36,9 @@ def _f(name):
             "fedb_pack_filter": [vp, vp, i, i, i, i, vp],
             "fedb_pack_dgrad_s2": [vp, vp, i, i, vp],
             "fedb_im2col_small": [vp, vp, vp, i, i, i, i, i, i, i, vp],
+            "fedb_conv_tf32_g": [vp, vp, vp, vp, i, i, i, i, i, i, i, i, i, ll, ll, vp],
+            "fedb_conv_wgrad_bf16_g": [vp, vp, vp, i, i, i, i, i, i, i, i, i, ll, ll, vp],
+            "fedb_conv_dgrad_s2_tf32_g": [vp, vp, vp, i, i, i, i, i, i, ll, ll, vp],
             "fedb_nn_channel_copy": [vp, vp, ll, i, i, i, i, i, i, i, vp],
             "fedb_conv_dgrad_s2_tf32": [vp, vp, vp, i, i, i, i, i, i, vp],
         }[name]
@@ -162,7 +165,85 @@ def _im2col(x, shp, f32: bool, bf16: bool):
     return o32, o16
 
 
+MAX_TC_GROUPS = 8         # grouped convolutions run group by group on the tensor-core kernels up to this many groups
+
+
+def _group_geometry(shp):
+    """(Cg, Kg) when a grouped 3x3 / 1x1 convolution (stride 1 or 2) can run one group per launch on the implicit-GEMM
+    kernels (pointer offset + whole-tensor pixel pitch), else None.  ResNeXt-29 (2/4/8 x 64d) is the zoo's user."""
+    N, H, W, Cc, K, R, S, P, Q, sh, sw, ph, pw, groups = shp
+    if groups < 2 or groups > MAX_TC_GROUPS or Cc % groups or K % groups:
+        return None
+    Cg, Kg = Cc // groups, K // groups
+    if Cg % 8 or Kg % 8 or R != S or R not in (1, 3) or sh != sw or sh not in (1, 2) or ph != (R - 1) // 2 or pw != ph:
+        return None
+    if not (_pow2(P) and _pow2(Q) and 2 <= Q <= 32 and P * sh == H and Q * sw == W and N * P * Q >= MIN_PIXELS):
+        return None
+    return Cg, Kg
+
+
+def _grouped_forward(x, w, bias, y, shp, Cg, Kg) -> bool:
+    N, H, W, Cc, K, R, S, P, Q, sh, sw, ph, pw, groups = shp
+    fn = _f("fedb_conv_tf32_g")
+    for g in range(groups):
+        wg = w[g * Kg:(g + 1) * Kg]                                      # contiguous OIHW slice of the group
+        wk = pack_filter(wg, 0, 9) if R == 3 else wg
+        check(fn(x.data_ptr() + 4 * g * Cg, wk.data_ptr(), y.data_ptr() + 4 * g * Kg,
+                 0 if bias is None else bias.data_ptr() + 4 * g * Kg, N, H, W, Cg, Kg, R, sh, ph, 0, Cc, K,
+                 current_stream()), "fedb_conv_tf32_g")
+        _lib.count_launch()
+    return True
+
+
+def _grouped_dgrad(dy, w, dx, shp, Cg, Kg) -> bool:
+    N, H, W, Cc, K, R, S, P, Q, sh, sw, ph, pw, groups = shp
+    if sh == 2 and R == 1:
+        dx.zero_()
+    for g in range(groups):
+        wg = w[g * Kg:(g + 1) * Kg]
+        dyp, dxp = dy.data_ptr() + 4 * g * Kg, dx.data_ptr() + 4 * g * Cg
+        if sh == 1:
+            wk = pack_filter(wg, 1, 9) if R == 3 else transpose(wg, Kg, Cg)
+            check(_f("fedb_conv_tf32_g")(dyp, wk.data_ptr(), dxp, 0, N, H, W, Kg, Cg, R, 1, ph, 0, K, Cc, current_stream()),
+                  "fedb_conv_tf32_g")
+            _lib.count_launch()
+        else:
+            if R == 3:
+                wk = torch.empty(9 * _pad32(Kg) * Cg, dtype=torch.float32, device=w.device)
+                check(_f("fedb_pack_dgrad_s2")(wg.data_ptr(), wk.data_ptr(), Kg, Cg, current_stream()), "fedb_pack_dgrad_s2")
+                _lib.count_launch()
+            else:
+                wk = transpose(wg, Kg, Cg)
+            check(_f("fedb_conv_dgrad_s2_tf32_g")(dyp, wk.data_ptr(), dxp, N, P, Q, Kg, Cg, R, K, Cc, current_stream()),
+                  "fedb_conv_dgrad_s2_tf32_g")
+            _lib.count_launch(4 if R == 3 else 1)
+    return True
+
+
+def _grouped_wgrad(x, dy, dw, db, shp, Cg, Kg) -> bool:
+    N, H, W, Cc, K, R, S, P, Q, sh, sw, ph, pw, groups = shp
+    taps, pix = R * R, N * P * Q
+    tiles = ((Kg + 127) // 128) * ((Cg + 127) // 128) * taps
+    splits = max(1, min(pix // 256, 444 // max(tiles * groups, 1)))
+    dy16, x16 = cast_bf16(dy), cast_bf16(x)
+    for g in range(groups):
+        dwg = dw[g * Kg:(g + 1) * Kg]
+        dwk = torch.zeros(Kg * taps * Cg, dtype=torch.float32, device=x.device) if taps > 1 else dwg
+        check(_f("fedb_conv_wgrad_bf16_g")(dy16.data_ptr() + 2 * g * Kg, x16.data_ptr() + 2 * g * Cg, dwk.data_ptr(), N, H, W,
+                                           Cg, Kg, R, sh, ph, splits, K, Cc, current_stream()), "fedb_conv_wgrad_bf16_g")
+        _lib.count_launch()
+        if taps > 1:
+            check(_f("fedb_pack_filter")(dwk.data_ptr(), dwg.data_ptr(), Kg, Cg, 2, taps, current_stream()), "fedb_pack_filter")
+            _lib.count_launch()
+    if db is not None:
+        db += dy.sum(dim=(0, 2, 3))
+    return True
+
+
 def conv_forward(x, w, bias, y, shp) -> bool:
+    gg = _group_geometry(shp)
+    if gg is not None:
+        return _grouped_forward(x, w, bias, y, shp, *gg)
     if _small_reduction(shp):
         N, H, W, Cc, K, R, S, P, Q = shp[:9]
         xcol, _ = _im2col(x, shp, True, False)
@@ -191,6 +272,9 @@ def conv_forward(x, w, bias, y, shp) -> bool:
 
 
 def conv_dgrad(dy, w, dx, shp) -> bool:
+    gg = _group_geometry(shp)
+    if gg is not None:
+        return _grouped_dgrad(dy, w, dx, shp, *gg)
     if _is_3x3(shp, shp[4], shp[3]):
         N, H, W, Cc, K = shp[:5]
         conv3x3_tf32(dy, pack3x3(w, 1), dx, None, N, H, W, K, Cc)    # dX = conv3x3(dY, flipped + transposed filter)
@@ -220,6 +304,9 @@ def conv_dgrad(dy, w, dx, shp) -> bool:
 
 
 def conv_wgrad(x, dy, dw, db, shp) -> bool:
+    gg = _group_geometry(shp)
+    if gg is not None:
+        return _grouped_wgrad(x, dy, dw, db, shp, *gg)
     if _small_reduction(shp) and shp[4] % 64 == 0:
         N, H, W, Cc, K, R, S, P, Q = shp[:9]
         pix = N * P * Q

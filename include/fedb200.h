@@ -228,6 +228,14 @@ int fedb_conv_wgrad_bf16(const uint16_t* dY, const uint16_t* X, float* dWk, int 
 int fedb_pack_dgrad_s2(const float* w_oihw, float* out, int K, int C, void* stream);
 int fedb_conv_dgrad_s2_tf32(const float* dY, const float* Wcls, float* dX, int N, int P, int Q, int Cout, int Cin, int fs,
                             void* stream);
+/* One group of a grouped convolution per call: pointers address the group's first channel, the pitches are the channel
+ * counts of the whole NHWC tensors (0 = dense).  Same kernels, same constraints on the per-group channel counts. */
+int fedb_conv_tf32_g(const float* X, const float* Wk, float* Y, const float* bias, int N, int H, int W, int Cin, int Cout, int fs,
+                     int stride, int pad, int relu, long long xpitch, long long ypitch, void* stream);
+int fedb_conv_wgrad_bf16_g(const uint16_t* dY, const uint16_t* X, float* dWk, int N, int H, int W, int Cin, int Cout, int fs,
+                           int stride, int pad, int splits, long long dypitch, long long xpitch, void* stream);
+int fedb_conv_dgrad_s2_tf32_g(const float* dY, const float* Wcls, float* dX, int N, int P, int Q, int Cout, int Cin, int fs,
+                              long long dypitch, long long dxpitch, void* stream);
 int fedb_conv3x3_wgrad_bf16(const uint16_t* dY, const uint16_t* X, float* dWk, int N, int H, int W, int Cin, int Cout,
                             int splits, void* stream);
 /* mode 0: OIHW -> [K][tap][C]; mode 1: OIHW -> [C][flipped tap][K] (data gradient); mode 2: [K][tap][C] -> OIHW */
