@@ -1,7 +1,7 @@
 """GPU step engine behind ``LocalTrainer`` (SURVEY C12 on the device).
 
 Two paths, both hand-written kernels end to end:
-* LeNet - the fused four-kernel step of csrc/lenet.cu.  A whole local pass (every step of the
+* LeNet - the fused two-kernel step of csrc/lenet.cu.  A whole local pass (every step of the
   shard) is captured ONCE into a CUDA graph per (shard shape) and replayed each round: one graph
   launch per round, no host syncs inside (K13), uint8 images normalised on the fly (K14).
 * any other zoo model - the model's own ``forward`` (which dispatches every op to
