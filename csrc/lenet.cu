@@ -31,6 +31,10 @@ constexpr int OFF_B1 = 450, OFF_W2 = 456, OFF_B2 = 2856;
 // gradient of conv1 reads img[ci][y+r][x+s] with lanes spread over (r, ci): banks 6r + 2ci are all distinct, whereas
 // the natural 32/1024 strides put every (r, ci) of a tap column into the same bank (measured: 35 % of the kernel).
 constexpr int IW = 38, IPLANE = 32 * IW + 2;
+// The pooled conv1 maps (conv2's input) are padded likewise: row stride 22, plane stride 334.  Both the 6x6 patch loads
+// of conv2's forward (lanes = pooled positions) and the filter-row loads of its weight gradient (lanes = (r, ci)) then
+// cost two wavefronts instead of three with the dense 14 / 196 strides.
+constexpr int P1S = 22, P1PLANE = 334;
 constexpr int kThreads = 512;          // sample kernel: 16 warps per sample keep the issue slots fed
 constexpr int kWarps = kThreads / 32;
 
@@ -77,8 +81,8 @@ struct Sm {
   static constexpr int b1 = w1 + 18 * 28;             // 8
   static constexpr int w2 = b1 + 8;                   // 96 filters x 28
   static constexpr int b2 = w2 + 96 * 28;             // 16
-  static constexpr int p1 = b2 + 16;                  // 1176
-  static constexpr int flat = p1 + NP1;               // 400
+  static constexpr int p1 = b2 + 16;                  // 6 padded planes
+  static constexpr int flat = p1 + C1 * P1PLANE;      // 400
   static constexpr int h1 = flat + NFLAT;             // 120
   static constexpr int h2 = h1 + H1;                  // 84
   static constexpr int lg = h2 + H2;                  // 16
@@ -92,8 +96,9 @@ struct Sm {
   static constexpr int g1 = g2 + NFLAT;               // 1176
   static constexpr int dp1 = g1 + NP1;                // 8 x 1176 (also the 8 x 400 partials of d(flat), and 2 x 120 of dh1)
   static constexpr int half = dp1 + 8 * NP1;          // 5 x 450
-  static constexpr int pos2 = half + 5 * NW1 + 2;     // 400 ints
-  static constexpr int pos1 = pos2 + NFLAT;           // 1176 ints
+  static constexpr int pos2 = half + 5 * NW1 + 2;     // 400 ints: arg-max offsets in a dense 14x14 plane (data gradient)
+  static constexpr int pos2p = pos2 + NFLAT;          // 400 ints: the same offsets in the padded p1 planes (weight gradient)
+  static constexpr int pos1 = pos2p + NFLAT;          // 1176 ints
   static constexpr int idx1 = pos1 + NP1;             // 1176 bytes = 294 words
   static constexpr int idx2 = idx1 + 296;             // 400 bytes = 100 words
   static constexpr int total = idx2 + 100;
@@ -304,7 +309,7 @@ __global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* _
     conv5_relu_pool<3, 3, IW, IPLANE>(s_img, s_w1, s_b1, 3 * hf, py, px, o, a);
 #pragma unroll
     for (int c = 0; c < 3; ++c) {
-      s_p1[(3 * hf + c) * 196 + pos] = o[c];
+      s_p1[(3 * hf + c) * P1PLANE + py * P1S + px] = o[c];
       s_idx1[(3 * hf + c) * 196 + pos] = a[c];
     }
   }
@@ -317,7 +322,7 @@ __global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* _
     const int py = pos / P2, px = pos % P2;
     float o[2];
     uint8_t a[2];
-    conv5_relu_pool<C1, 2, P1>(s_p1, s_w2, s_b2, 2 * cg, py, px, o, a);
+    conv5_relu_pool<C1, 2, P1S, P1PLANE>(s_p1, s_w2, s_b2, 2 * cg, py, px, o, a);
 #pragma unroll
     for (int c = 0; c < 2; ++c) {
       s_flat[(2 * cg + c) * 25 + pos] = o[c];  // co * 25 + pos: NCHW flatten order == fc1's input order
@@ -371,6 +376,7 @@ __global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* _
   float* s_dp1 = sm + Sm::dp1;
   float* s_half = sm + Sm::half;
   int* s_pos2 = reinterpret_cast<int*>(sm + Sm::pos2);
+  int* s_pos2p = reinterpret_cast<int*>(sm + Sm::pos2p);
   int* s_pos1 = reinterpret_cast<int*>(sm + Sm::pos1);
 
   FEDB_PHASE_MARK(5);
@@ -461,6 +467,7 @@ __global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* _
     const int pos = e % 25, py = pos / 5, px = pos % 5;
     s_g2[e] = s_flat[e] > 0.f ? s_dflat[e] : 0.f;
     s_pos2[e] = (2 * py + (k >> 1)) * 14 + (2 * px + (k & 1));       // offset of the arg-max inside a 14x14 p1 plane
+    s_pos2p[e] = (2 * py + (k >> 1)) * P1S + (2 * px + (k & 1));     // ... and inside the padded plane
   }
   __syncthreads();
 
@@ -470,12 +477,12 @@ __global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* _
   // one thread per (co, ci, filter row): the five taps of the row share the loads of g2 and of the arg-max offset
   if (tid < NW2 / 5) {
     const int r = tid % 5, ci = (tid / 5) % C1, co = tid / 30;
-    const float* src = s_p1 + ci * 196 + r * 14;
+    const float* src = s_p1 + ci * P1PLANE + r * P1S;
     float acc[5] = {0.f, 0.f, 0.f, 0.f, 0.f};
 #pragma unroll 5
     for (int pos = 0; pos < 25; ++pos) {
       const float g = s_g2[co * 25 + pos];
-      const float* q = src + s_pos2[co * 25 + pos];
+      const float* q = src + s_pos2p[co * 25 + pos];
 #pragma unroll
       for (int t = 0; t < 5; ++t) acc[t] = fmaf(g, q[t], acc[t]);
     }
@@ -517,7 +524,7 @@ __global__ void __launch_bounds__(kThreads, 1) lenet_sample_kernel(const void* _
     for (int w = 0; w < 8; ++w) d += s_dp1[w * NP1 + e];
     const int k = s_idx1[e];
     const int pos = e % 196, py = pos / 14, px = pos % 14;
-    s_g1[e] = s_p1[e] > 0.f ? d : 0.f;
+    s_g1[e] = s_p1[(e / 196) * P1PLANE + py * P1S + px] > 0.f ? d : 0.f;
     s_pos1[e] = (2 * py + (k >> 1)) * IW + (2 * px + (k & 1));       // offset of the arg-max inside a padded image plane
   }
   __syncthreads();
