@@ -622,26 +622,31 @@ __global__ void __launch_bounds__(256) update_kernel(UpdateArgs U, Workspace W) 
     if (b < 60)      { J = H1; K = NFLAT; jt = b / 4; kt = b % 4; dout = W.dh1; in = W.flat; off = U.off[4]; }
     else if (b < 71) { J = H2; K = H1; jt = b - 60; kt = 0; dout = W.dh2; in = W.h1; off = U.off[6]; }
     else             { J = NCLS; K = H2; jt = b - 71; kt = 0; dout = W.dlogits; in = W.h2; off = U.off[8]; }
-    // compute roles: warp = (row pair rp, sample half sh); a thread owns rows 2rp, 2rp+1 x columns k..k+3 and sums the
-    // samples of its half.  Two rows per loaded x halve the shared-memory wavefronts of the FMA loop (the loop is bound
-    // by them); the two sample halves are added in a fixed order at the end.
+    // compute roles: warp = (row quad rq, sample quarter sq); a thread owns rows 4rq..4rq+3 x columns k..k+3 and sums the
+    // samples of its quarter.  Four rows per loaded x quarter the shared-memory wavefronts of the FMA loop (the loop is
+    // bound by them); the four sample quarters are added in a fixed order at the end.
     const int wp = tid >> 5, lane = tid & 31;
-    const int rp = wp & 3, sh = wp >> 2;
-    const int j0 = jt * 8 + 2 * rp, k = kt * 128 + lane * 4;
+    const int rq = wp & 1, sq = wp >> 1;
+    const int j0 = jt * 8 + 4 * rq, k = kt * 128 + lane * 4;
     const bool col_ok = k < K;
     const long long dst0 = off + (long long)j0 * K + k;         // multiple of 4 floats: segments are 32-float aligned
-    const long long dst1 = dst0 + K;
-    float4 p0 = make_float4(0.f, 0.f, 0.f, 0.f), m0 = p0, p1 = p0, m1 = p0;
-    if (kApply && sh == 0 && col_ok) {
-      if (j0 < J) { p0 = *reinterpret_cast<const float4*>(U.param + dst0); m0 = *reinterpret_cast<const float4*>(U.momentum + dst0); }
-      if (j0 + 1 < J) { p1 = *reinterpret_cast<const float4*>(U.param + dst1); m1 = *reinterpret_cast<const float4*>(U.momentum + dst1); }
+    float4 pw[4], mw[4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) {
+      pw[r] = mw[r] = make_float4(0.f, 0.f, 0.f, 0.f);
+      if (kApply && sq == 0 && col_ok && j0 + r < J) {
+        pw[r] = *reinterpret_cast<const float4*>(U.param + dst0 + (long long)r * K);
+        mw[r] = *reinterpret_cast<const float4*>(U.momentum + dst0 + (long long)r * K);
+      }
     }
     // loader roles: float4 column lk4 of sample rows ls, ls+8, ...; dout element (ds, dj)
     const int lk4 = tid & 31, ls = tid >> 5;
     const int dj = tid & 7, ds = tid >> 3;
     const bool lk_ok = kt * 128 + lk4 * 4 < K;                  // K is a multiple of 4
     const bool dj_ok = jt * 8 + dj < J;
-    float4 a0 = make_float4(0.f, 0.f, 0.f, 0.f), a1 = a0;
+    float4 acc[4];
+#pragma unroll
+    for (int r = 0; r < 4; ++r) acc[r] = make_float4(0.f, 0.f, 0.f, 0.f);
     for (int s0 = 0; s0 < B; s0 += kUChunk) {
       float4 vin[16];
       float vd[4];
@@ -663,35 +668,43 @@ __global__ void __launch_bounds__(256) update_kernel(UpdateArgs U, Workspace W) 
       for (int r = 0; r < 4; ++r) s_dout[(ds + 32 * r) * 8 + dj] = vd[r];
       __syncthreads();
       const int ns = min(kUChunk, B - s0);
-      const int sb = sh * (kUChunk / 2), se = min(sb + kUChunk / 2, ns);
+      const int sb = sq * (kUChunk / 4), se = min(sb + kUChunk / 4, ns);
 #pragma unroll 8
       for (int sidx = sb; sidx < se; ++sidx) {
-        const float2 d = *reinterpret_cast<const float2*>(s_dout + sidx * 8 + 2 * rp);
+        const float4 d = *reinterpret_cast<const float4*>(s_dout + sidx * 8 + 4 * rq);
         const float4 x = reinterpret_cast<const float4*>(s_in)[sidx * 32 + lane];
-        a0.x = fmaf(d.x, x.x, a0.x); a0.y = fmaf(d.x, x.y, a0.y); a0.z = fmaf(d.x, x.z, a0.z); a0.w = fmaf(d.x, x.w, a0.w);
-        a1.x = fmaf(d.y, x.x, a1.x); a1.y = fmaf(d.y, x.y, a1.y); a1.z = fmaf(d.y, x.z, a1.z); a1.w = fmaf(d.y, x.w, a1.w);
+        const float dv[4] = {d.x, d.y, d.z, d.w};
+#pragma unroll
+        for (int r = 0; r < 4; ++r) {
+          acc[r].x = fmaf(dv[r], x.x, acc[r].x);
+          acc[r].y = fmaf(dv[r], x.y, acc[r].y);
+          acc[r].z = fmaf(dv[r], x.z, acc[r].z);
+          acc[r].w = fmaf(dv[r], x.w, acc[r].w);
+        }
       }
     }
     __syncthreads();                                            // every warp is done with the staged tile
-    float4* s_half4 = reinterpret_cast<float4*>(s_in);
-    if (sh == 1) {
-      s_half4[(2 * rp) * 32 + lane] = a0;
-      s_half4[(2 * rp + 1) * 32 + lane] = a1;
+    float4* s_part4 = reinterpret_cast<float4*>(s_in);           // [3 quarters][8 rows][32 lanes]
+    if (sq > 0) {
+#pragma unroll
+      for (int r = 0; r < 4; ++r) s_part4[((sq - 1) * 8 + 4 * rq + r) * 32 + lane] = acc[r];
     }
     __syncthreads();
-    if (sh == 0 && col_ok) {
-      const float4 h0 = s_half4[(2 * rp) * 32 + lane], h1 = s_half4[(2 * rp + 1) * 32 + lane];
-      if (j0 < J) {
-        apply_update<kApply>(U, dst0 + 0, a0.x + h0.x, p0.x, m0.x);
-        apply_update<kApply>(U, dst0 + 1, a0.y + h0.y, p0.y, m0.y);
-        apply_update<kApply>(U, dst0 + 2, a0.z + h0.z, p0.z, m0.z);
-        apply_update<kApply>(U, dst0 + 3, a0.w + h0.w, p0.w, m0.w);
-      }
-      if (j0 + 1 < J) {
-        apply_update<kApply>(U, dst1 + 0, a1.x + h1.x, p1.x, m1.x);
-        apply_update<kApply>(U, dst1 + 1, a1.y + h1.y, p1.y, m1.y);
-        apply_update<kApply>(U, dst1 + 2, a1.z + h1.z, p1.z, m1.z);
-        apply_update<kApply>(U, dst1 + 3, a1.w + h1.w, p1.w, m1.w);
+    if (sq == 0 && col_ok) {
+#pragma unroll
+      for (int r = 0; r < 4; ++r) {
+        if (j0 + r >= J) break;
+        float4 g = acc[r];
+#pragma unroll
+        for (int q = 0; q < 3; ++q) {
+          const float4 h = s_part4[(q * 8 + 4 * rq + r) * 32 + lane];
+          g.x += h.x; g.y += h.y; g.z += h.z; g.w += h.w;
+        }
+        const long long dst = dst0 + (long long)r * K;
+        apply_update<kApply>(U, dst + 0, g.x, pw[r].x, mw[r].x);
+        apply_update<kApply>(U, dst + 1, g.y, pw[r].y, mw[r].y);
+        apply_update<kApply>(U, dst + 2, g.z, pw[r].z, mw[r].z);
+        apply_update<kApply>(U, dst + 3, g.w, pw[r].w, mw[r].w);
       }
     }
     return;
