@@ -49,6 +49,7 @@ def parse():
     ap.add_argument("--no-multicast", action="store_true")
     ap.add_argument("--repl", choices=("overlap", "fused"), default="overlap")
     ap.add_argument("--ref-gpu-workers", action="store_true", help="reference arm: R-gpu variant (DP shim)")
+    ap.add_argument("--no-l2-flush", action="store_true", help="diagnostic: skip the L2 flush between device-timed rounds")
     return ap.parse_args()
 
 
@@ -150,9 +151,12 @@ def run_ours(a) -> dict:
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")      # > 126 MB L2
 
     # ---------------------------------------------------------------- warm-up (uploads + graph capture)
+    # both flavours of the round graph are captured here, never inside a timed region: the first W-1 rounds stream their
+    # inputs from pinned memory (the e2e flavour), the last one reuses the resident copy (the device-timed flavour)
     last = None
-    for _ in range(max(a.warmup, 3)):
-        last = fed.run_round(upload=True, sync=True)
+    W = max(a.warmup, 3)
+    for i in range(W):
+        last = fed.run_round(upload=i < W - 1, sync=True)
     barrier()
 
     # ---------------------------------------------------------------- device-timed rounds
@@ -163,7 +167,8 @@ def run_ours(a) -> dict:
     launches0 = _lib.launches
     barrier()
     for s, e in ev:
-        flush.zero_()                       # L2 flush between timed iterations, outside the events
+        if not a.no_l2_flush:
+            flush.zero_()                   # L2 flush between timed iterations, outside the events
         s.record()
         fed.run_round(upload=False, sync=False)
         e.record()
