@@ -156,6 +156,13 @@ struct GemmArgs {
   // output scatter of the parity-decomposed data gradient of a stride-2 convolution: tile row (n, p, q) of the
   // [N, H, W] sub-grid is written to pixel (n, p*ostride + oy, q*ostride + ox) of the [N, H*ostride, W*ostride] map
   int ostride, oy, ox;     // ostride <= 1: rows are written in place
+  // grouped convolution in ONE launch: the tensor maps cover the whole tensors, the group index (blockIdx.z for the
+  // forward / data-gradient form, folded into blockIdx.y for the weight gradient) shifts the channel coordinate of the
+  // activation by a_goff, the row coordinate of the other operand by b_goff and the output by d_goff elements.  Tile
+  // rows / columns that spill into the next group are multiplied by explicit zeros of the packed filter (forward) or
+  // masked by the M / N guards of the epilogue.
+  int groups, a_goff, b_goff;
+  long long d_goff;
 };
 
 __device__ __forceinline__ long long out_row(const GemmArgs& g, int row) {
@@ -190,9 +197,13 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
   // conv wgrad (g.conv == 2): blockIdx.y enumerates (filter tap, N tile); the tap selects the spatial shift of the
   // X operand and the column block [tap*Cin, (tap+1)*Cin) of the packed gradient dWk[Cout][9*Cin]
   const int n_tiles = (g.N + BN - 1) / BN;
-  const int tap = g.conv == 2 ? blockIdx.y / n_tiles : 0;
+  const bool grouped = g.groups > 1;
+  const int ytap = g.conv == 2 ? blockIdx.y / n_tiles : 0;                       // (group, tap) of a weight-gradient tile
+  const int ntaps = g.fs * g.fs;
+  const int tap = grouped ? ytap % ntaps : ytap;
+  const int grp = !grouped ? 0 : (g.conv == 2 ? ytap / ntaps : blockIdx.z);
   const int m0 = blockIdx.x * BM, n0 = (g.conv == 2 ? blockIdx.y % n_tiles : blockIdx.y) * BN;
-  const int k_begin = blockIdx.z * g.k_per_split;
+  const int k_begin = (grouped && g.conv == 1) ? 0 : blockIdx.z * g.k_per_split;
   const int k_end = min(g.K, k_begin + g.k_per_split);
   constexpr int BK = Kind<KIND>::kBK;
   constexpr int kChunkBytes = BK * 128;          // one MN-major chunk: BK K-rows of 128 bytes
@@ -235,8 +246,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             else           { n_img = blockIdx.x * g.bn; h0 = 0; }
             // box [32 ch x bw x bh x bn] output pixels; with stride 2 the tensor map itself skips every other input
             // pixel (elementStrides), so the same 128 x 32 tile lands in shared memory
-            tma_load_4d(a_dst, &mapA, &full[s], c0, sx - g.cpad, h0 * g.cstride + r - g.cpad, n_img);
-            tma_load_2d(b_dst, &mapB, &full[s], k0, n0);
+            tma_load_4d(a_dst, &mapA, &full[s], c0 + grp * g.a_goff, sx - g.cpad, h0 * g.cstride + r - g.cpad, n_img);
+            tma_load_2d(b_dst, &mapB, &full[s], k0, n0 + grp * g.b_goff);
           } else {
             tma_load_2d(a_dst, &mapA, &full[s], k0, m0);                   // box [32 fp32 (K) x BM rows]
             tma_load_2d(b_dst, &mapB, &full[s], k0, n0);                   // box [32 fp32 (K) x BN rows]
@@ -244,7 +255,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
         } else {
 #pragma unroll
           for (int c = 0; c < BM / 64; ++c)                                // box [64 bf16 (M) x BK K-rows] per chunk
-            tma_load_2d(a_dst + c * kChunkBytes, &mapA, &full[s], m0 + c * 64, k0);
+            tma_load_2d(a_dst + c * kChunkBytes, &mapA, &full[s], m0 + c * 64 + grp * g.b_goff, k0);
           if (g.conv == 2) {
             // K runs over output pixels in tiles of 64 = one [bw x bh x bn] box of the bf16 NHWC activation, shifted
             // by the filter tap (zero fill outside the image = the padding)
@@ -254,7 +265,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
             else           { n_img = pt * g.bn; h0 = 0; }
 #pragma unroll
             for (int c = 0; c < Smem<BN, KIND>::kBN / 64; ++c)
-              tma_load_4d(b_dst + c * kChunkBytes, &mapB, &full[s], n0 + c * 64, tap % g.fs - g.cpad,
+              tma_load_4d(b_dst + c * kChunkBytes, &mapB, &full[s], n0 + c * 64 + grp * g.a_goff, tap % g.fs - g.cpad,
                           h0 * g.cstride + tap / g.fs - g.cpad, n_img);
           } else {
 #pragma unroll
@@ -302,7 +313,8 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     // store is 32 scattered 64-byte pieces; staging through smem turns the write-out into whole 512-byte rows.
     constexpr int PITCH = BN + 4;                            // floats; +4 keeps 128-bit smem accesses conflict-free
     float* stage = reinterpret_cast<float*>(smem) + (size_t)(q * 32) * PITCH;
-    const bool vec_ok = !g.atomic_out && (g.ldd % 4 == 0) && (g.N % 4 == 0) && ((reinterpret_cast<uintptr_t>(g.D) & 15) == 0);
+    const bool vec_ok = !g.atomic_out && (g.ldd % 4 == 0) && (g.N % 4 == 0) && (g.d_goff % 4 == 0) &&
+                        ((reinterpret_cast<uintptr_t>(g.D) & 15) == 0);
     if (num_k > 0) {
 #pragma unroll 1
       for (int c0 = 0; c0 < BN; c0 += 16) {
@@ -311,7 +323,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
           const int col = n0 + c0 + j;
-          if (g.bias != nullptr && blockIdx.z == 0 && col < g.N) v[j] += g.bias[col];
+          if (g.bias != nullptr && (grouped || blockIdx.z == 0) && col < g.N) v[j] += g.bias[grp * g.N + col];
           if (g.relu) v[j] = fmaxf(v[j], 0.f);
         }
         if (vec_ok) {
@@ -319,7 +331,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
           for (int j = 0; j < 16; j += 4)
             *reinterpret_cast<float4*>(stage + lane * PITCH + c0 + j) = make_float4(v[j], v[j + 1], v[j + 2], v[j + 3]);
         } else if (row < g.M) {
-          float* drow = g.D + out_row(g, row) * g.ldd + (long long)tap * g.Cin + n0 + c0;
+          float* drow = g.D + grp * g.d_goff + out_row(g, row) * g.ldd + (long long)tap * g.Cin + n0 + c0;
 #pragma unroll
           for (int j = 0; j < 16; ++j) {
             if (n0 + c0 + j < g.N) {
@@ -338,7 +350,7 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
           for (int c4 = lane; c4 < BN / 4; c4 += 32) {
             const int col = n0 + 4 * c4;
             if (col < g.N)
-              *reinterpret_cast<float4*>(g.D + orow * g.ldd + col) =
+              *reinterpret_cast<float4*>(g.D + grp * g.d_goff + orow * g.ldd + col) =
                   *reinterpret_cast<const float4*>(stage + r * PITCH + 4 * c4);
           }
         }
@@ -413,9 +425,12 @@ int make_map_nhwc(CUtensorMap* map, const void* base, int elem, int N, int H, in
 // mode 2 (unpack):   dW[k][c][r][s] += dWk[k][(r*3+s)*C + c]      (packed weight gradient back to OIHW)
 // Rp = reduction channels rounded up to the K tile (32): the packed matrices of modes 0 / 1 carry zeros in the tail of
 // every tap so that a tap always starts on a K-tile boundary (the activation side gets its zeros from TMA).
+// Grouped filters (OIHW with I = C channels per group, K output channels over all groups): modes 0 and 2 are unchanged
+// (every output row only knows its own group's inputs); mode 1 emits one row per INPUT channel of the whole tensor,
+// [groups * C][flipped tap][K/groups padded], with the output channels of that input channel's group.
 __global__ void __launch_bounds__(256) pack3x3_kernel(const float* __restrict__ w, float* __restrict__ out, int K, int C, int mode,
-                                                     int T /* taps: 9 or 1 */, int Rp) {
-  const int total = mode == 0 ? K * T * Rp : (mode == 1 ? C * 9 * Rp : K * C * T);
+                                                     int T /* taps: 9 or 1 */, int Rp, int groups = 1) {
+  const int total = mode == 0 ? K * T * Rp : (mode == 1 ? groups * C * T * Rp : K * C * T);
   for (int i = blockIdx.x * 256 + threadIdx.x; i < total; i += gridDim.x * 256) {
     if (mode == 0) {
       const int c = i % Rp, tap = (i / Rp) % T, k = i / (T * Rp);
@@ -424,8 +439,9 @@ __global__ void __launch_bounds__(256) pack3x3_kernel(const float* __restrict__ 
       const int c = i % C, tap = (i / C) % T, k = i / (T * C);
       out[(k * C + c) * T + tap] += w[i];
     } else {
-      const int k = i % Rp, tap = (i / Rp) % 9, c = i / (9 * Rp);
-      out[i] = k < K ? w[(k * C + c) * 9 + (8 - tap)] : 0.f;
+      const int k = i % Rp, tap = (i / Rp) % T, cg = i / (T * Rp);       // cg: input channel of the whole tensor
+      const int Kg = K / groups, grp = cg / C, c = cg - grp * C;
+      out[i] = k < Kg ? w[((grp * Kg + k) * C + c) * T + (T - 1 - tap)] : 0.f;
     }
   }
 }
@@ -479,6 +495,7 @@ int run_gemm(int kind, const void* A, const void* B, float* D, const float* bias
   g.atomic_out = (splits > 1 || accumulate) ? 1 : 0;
   g.conv = 0; g.Cin = g.H = g.W = g.bw = g.bh = g.bn = 0; g.cstride = 1; g.cpad = 0; g.fs = 1;
   g.ostride = g.oy = g.ox = 0;
+  g.groups = 1; g.a_goff = g.b_goff = 0; g.d_goff = 0;
   return kind == 0 ? dispatch_bn<0>(bn, ma, mb, g, splits, s) : dispatch_bn<1>(bn, ma, mb, g, splits, s);
 }
 
@@ -525,8 +542,10 @@ extern "C" int fedb_gemm_bf16_tn(const uint16_t* At, const uint16_t* Bt, float* 
 // roles gives the data gradient).  P = H/stride, Q = W/stride ("same"-style geometry of the CIFAR zoo).
 // Grouped convolutions run one group per call: X / Y point at the group's first channel and xpitch / ypitch are the
 // channel counts of the WHOLE tensors (elements between consecutive pixels).
-extern "C" int fedb_conv_tf32_g(const float* X, const float* Wk, float* Y, const float* bias, int N, int H, int W, int Cin,
-                                int Cout, int fs, int stride, int pad, int relu, long long xpitch, long long ypitch, void* stream) {
+// groups > 1: X / Y are the WHOLE tensors (xpitch / ypitch their channel counts), Cin / Cout are per group, Wk holds the
+// filters of all groups ([groups * Cout][taps][Cin padded to 32]); one launch, blockIdx.z = group.
+static int conv_tf32_impl(const float* X, const float* Wk, float* Y, const float* bias, int N, int H, int W, int Cin, int Cout,
+                          int fs, int stride, int pad, int relu, long long xpitch, long long ypitch, int groups, void* stream) {
   FEDB_REQUIRE(Cin % 4 == 0, "fedb_conv_tf32: Cin must be a multiple of 4 (16-byte pixel pitch)");
   FEDB_REQUIRE((fs == 3 && pad == 1) || (fs == 1 && pad == 0), "fedb_conv_tf32: 3x3/pad 1 or 1x1/pad 0");
   FEDB_REQUIRE(stride == 1 || stride == 2, "fedb_conv_tf32: stride 1 or 2");
@@ -544,23 +563,38 @@ extern "C" int fedb_conv_tf32_g(const float* X, const float* Wk, float* Y, const
   const int M = N * P * Q, K = fs * fs * cin_pad;
   const int bnt = Cout >= 128 ? 128 : (Cout > 32 ? 64 : 32);
   CUtensorMap ma, mb;
-  if (int rc = make_map_nhwc(&ma, X, 4, N, H, W, Cin, bw, bh, bn, stride, xpitch)) return rc;
-  if (fs == 1) { if (int rc = make_map_2d(&mb, Wk, 4, Cout, Cin, Cin, 32, bnt)) return rc; }
-  else if (int rc = make_map_2d(&mb, Wk, 4, Cout, K, K, 32, bnt)) return rc;
+  if (int rc = make_map_nhwc(&ma, X, 4, N, H, W, groups > 1 ? (int)xpitch : Cin, bw, bh, bn, stride, xpitch)) return rc;
+  if (fs == 1) { if (int rc = make_map_2d(&mb, Wk, 4, (long long)Cout * groups, Cin, Cin, 32, bnt)) return rc; }
+  else if (int rc = make_map_2d(&mb, Wk, 4, (long long)Cout * groups, K, K, 32, bnt)) return rc;
   GemmArgs g;
   g.D = Y; g.bias = bias; g.ldd = ypitch > 0 ? ypitch : Cout; g.M = M; g.N = Cout; g.K = K; g.k_per_split = K; g.relu = relu;
   g.atomic_out = 0;
   g.conv = 1; g.Cin = cin_pad; g.H = P; g.W = Q; g.bw = bw; g.bh = bh; g.bn = bn; g.cstride = stride; g.cpad = pad; g.fs = fs;
   g.ostride = g.oy = g.ox = 0;
-  return dispatch_bn<0>(bnt, ma, mb, g, 1, (cudaStream_t)stream);
+  g.groups = groups; g.a_goff = groups > 1 ? Cin : 0; g.b_goff = groups > 1 ? Cout : 0; g.d_goff = groups > 1 ? Cout : 0;
+  return dispatch_bn<0>(bnt, ma, mb, g, groups, (cudaStream_t)stream);
+}
+
+extern "C" int fedb_conv_tf32_g(const float* X, const float* Wk, float* Y, const float* bias, int N, int H, int W, int Cin,
+                                int Cout, int fs, int stride, int pad, int relu, long long xpitch, long long ypitch, void* stream) {
+  return conv_tf32_impl(X, Wk, Y, bias, N, H, W, Cin, Cout, fs, stride, pad, relu, xpitch, ypitch, 1, stream);
+}
+
+// All groups of a grouped convolution in one launch.  C, K: channel counts of the whole tensors.
+extern "C" int fedb_conv_tf32_grouped(const float* X, const float* Wk, float* Y, const float* bias, int N, int H, int W, int C,
+                                      int K, int groups, int fs, int stride, int pad, int relu, void* stream) {
+  FEDB_REQUIRE(groups >= 1 && C % groups == 0 && K % groups == 0, "fedb_conv_tf32_grouped: channels must divide into the groups");
+  return conv_tf32_impl(X, Wk, Y, bias, N, H, W, C / groups, K / groups, fs, stride, pad, relu, C, K, groups, stream);
 }
 
 // Filters of the four output-parity classes of a stride-2 3x3/pad-1 data gradient, K-major for the GEMM:
 //   class (a, b), a = h % 2, b = w % 2 of the dX pixel; rows: a == 0 -> filter row 1 (dY row p'), a == 1 -> filter row 2
 //   (dY row p') then row 0 (dY row p'+1); columns likewise.  out = [class][c][tap][k], classes (0,0),(0,1),(1,0),(1,1)
 //   with 1, 2, 2, 4 taps: class offsets 0, 1, 3, 5 in units of C*K floats.
-__global__ void __launch_bounds__(256) pack_dgrad_s2_kernel(const float* __restrict__ w, float* __restrict__ out, int Kreal, int C,
-                                                           int K /* Kreal rounded up to 32 */) {
+__global__ void __launch_bounds__(256) pack_dgrad_s2_kernel(const float* __restrict__ w, float* __restrict__ out, int Kreal, int Cg,
+                                                           int K /* Kreal rounded up to 32 */, int groups) {
+  // Kreal: output channels PER GROUP, Cg: input channels per group, C: input channels of the whole tensor (rows)
+  const int C = Cg * groups;
   const int total = 9 * K * C;
   for (int i = blockIdx.x * 256 + threadIdx.x; i < total; i += gridDim.x * 256) {
     const int unit = i / (K * C);                       // 0..8: which (class, tap)
@@ -572,15 +606,23 @@ __global__ void __launch_bounds__(256) pack_dgrad_s2_kernel(const float* __restr
     const int k = j % K, t = (j / K) % T, c = j / (K * T);
     const int rr = t / fc, ss = t % fc;
     const int r = a == 0 ? 1 : (rr == 0 ? 2 : 0), sx = b == 0 ? 1 : (ss == 0 ? 2 : 0);
-    out[i] = k < Kreal ? w[((k * C + c) * 3 + r) * 3 + sx] : 0.f;
+    const int grp = c / Cg, cl = c - grp * Cg;
+    out[i] = k < Kreal ? w[(((grp * Kreal + k) * Cg + cl) * 3 + r) * 3 + sx] : 0.f;
   }
 }
 
+extern "C" int fedb_pack_dgrad_s2_grouped(const float* w_oihw, float* out, int K, int C, int groups, void* stream);
 extern "C" int fedb_pack_dgrad_s2(const float* w_oihw, float* out, int K, int C, void* stream) {
-  const int Kp = (K + 31) / 32 * 32;                    // out holds 9 * C * Kp floats
-  int blocks = fedb_ceil_div((long long)Kp * C * 9, 256);
+  return fedb_pack_dgrad_s2_grouped(w_oihw, out, K, C, 1, stream);
+}
+
+// K: output channels over all groups, C: input channels per group; out holds 9 * groups * C * pad32(K / groups) floats
+extern "C" int fedb_pack_dgrad_s2_grouped(const float* w_oihw, float* out, int K, int C, int groups, void* stream) {
+  FEDB_REQUIRE(groups >= 1 && K % groups == 0, "fedb_pack_dgrad_s2: K must divide into the groups");
+  const int Kg = K / groups, Kp = (Kg + 31) / 32 * 32;
+  int blocks = fedb_ceil_div((long long)Kp * C * groups * 9, 256);
   if (blocks > fedb_num_sms() * 8) blocks = fedb_num_sms() * 8;
-  pack_dgrad_s2_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w_oihw, out, K, C, Kp);
+  pack_dgrad_s2_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w_oihw, out, Kg, C, Kp, groups);
   FEDB_LAUNCH_OK();
   return 0;
 }
@@ -589,8 +631,8 @@ extern "C" int fedb_pack_dgrad_s2(const float* w_oihw, float* out, int K, int C,
 // sees a dense 1x1 / 1x2 / 2x1 / 2x2 filter over dY), written straight into the interleaved positions of dX by the
 // epilogue.  dY [N,P,Q,Cout], dX [N,2P,2Q,Cin].  fs == 3: Wcls from fedb_pack_dgrad_s2.  fs == 1: Wcls = W^T
 // ([Cin][Cout]); only class (0,0) receives gradient, the caller zero-fills dX first.
-extern "C" int fedb_conv_dgrad_s2_tf32_g(const float* dY, const float* Wcls, float* dX, int N, int P, int Q, int Cout, int Cin,
-                                         int fs, long long dypitch, long long dxpitch, void* stream) {
+static int conv_dgrad_s2_impl(const float* dY, const float* Wcls, float* dX, int N, int P, int Q, int Cout, int Cin, int fs,
+                              long long dypitch, long long dxpitch, int groups, void* stream) {
   FEDB_REQUIRE(Cout % 4 == 0, "fedb_conv_dgrad_s2_tf32: Cout must be a multiple of 4 (16-byte pixel pitch)");
   const int cout_pad = (Cout + 31) / 32 * 32;
   FEDB_REQUIRE(fs == 1 || fs == 3, "fedb_conv_dgrad_s2_tf32: 1x1 or 3x3");
@@ -602,27 +644,42 @@ extern "C" int fedb_conv_dgrad_s2_tf32_g(const float* dY, const float* Wcls, flo
   FEDB_REQUIRE(bw * bh * bn == 128 && (bn == 1 || bh == P), "fedb_conv_dgrad_s2_tf32: unsupported tile geometry");
   const int bnt = Cin >= 128 ? 128 : (Cin > 32 ? 64 : 32);
   CUtensorMap ma, mb;
-  if (int rc = make_map_nhwc(&ma, dY, 4, N, P, Q, Cout, bw, bh, bn, 1, dypitch)) return rc;
+  if (int rc = make_map_nhwc(&ma, dY, 4, N, P, Q, groups > 1 ? (int)dypitch : Cout, bw, bh, bn, 1, dypitch)) return rc;
   const int ncls = fs == 3 ? 4 : 1;
   const int base[4] = {0, 1, 3, 5};
   for (int cls = 0; cls < ncls; ++cls) {
     const int a = cls >> 1, b = cls & 1;
     const int taps = fs == 3 ? (a + 1) * (b + 1) : 1;
     const int K = taps * cout_pad;
-    if (fs == 1) { if (int rc = make_map_2d(&mb, Wcls, 4, Cin, Cout, Cout, 32, bnt)) return rc; }
-    else if (int rc = make_map_2d(&mb, Wcls + (size_t)base[cls] * Cin * cout_pad, 4, Cin, K, K, 32, bnt)) return rc;
+    // filters of all groups: [class][groups * Cin rows][taps][Cout padded]
+    if (fs == 1) { if (int rc = make_map_2d(&mb, Wcls, 4, (long long)Cin * groups, Cout, Cout, 32, bnt)) return rc; }
+    else if (int rc = make_map_2d(&mb, Wcls + (size_t)base[cls] * Cin * groups * cout_pad, 4, (long long)Cin * groups, K, K, 32, bnt)) return rc;
     GemmArgs g;
     g.D = dX; g.bias = nullptr; g.ldd = dxpitch > 0 ? dxpitch : Cin; g.M = N * P * Q; g.N = Cin; g.K = K; g.k_per_split = K; g.relu = 0; g.atomic_out = 0;
     g.conv = 1; g.Cin = cout_pad; g.H = P; g.W = Q; g.bw = bw; g.bh = bh; g.bn = bn; g.cstride = 1; g.cpad = 0; g.fs = b + 1;
     g.ostride = 2; g.oy = a; g.ox = b;
-    if (int rc = dispatch_bn<0>(bnt, ma, mb, g, 1, (cudaStream_t)stream)) return rc;
+    g.groups = groups; g.a_goff = groups > 1 ? Cout : 0; g.b_goff = groups > 1 ? Cin : 0; g.d_goff = groups > 1 ? Cin : 0;
+    if (int rc = dispatch_bn<0>(bnt, ma, mb, g, groups, (cudaStream_t)stream)) return rc;
   }
   return 0;
 }
 
+extern "C" int fedb_conv_dgrad_s2_tf32_g(const float* dY, const float* Wcls, float* dX, int N, int P, int Q, int Cout, int Cin,
+                                         int fs, long long dypitch, long long dxpitch, void* stream) {
+  return conv_dgrad_s2_impl(dY, Wcls, dX, N, P, Q, Cout, Cin, fs, dypitch, dxpitch, 1, stream);
+}
+
 extern "C" int fedb_conv_dgrad_s2_tf32(const float* dY, const float* Wcls, float* dX, int N, int P, int Q, int Cout, int Cin,
                                        int fs, void* stream) {
-  return fedb_conv_dgrad_s2_tf32_g(dY, Wcls, dX, N, P, Q, Cout, Cin, fs, 0, 0, stream);
+  return conv_dgrad_s2_impl(dY, Wcls, dX, N, P, Q, Cout, Cin, fs, 0, 0, 1, stream);
+}
+
+// K, C: channel counts of the whole dY / dX tensors; Wcls from fedb_pack_dgrad_s2_grouped (fs == 3) or the per-group
+// transposes [groups * Cg][Kg] (fs == 1, dX zero-filled by the caller).
+extern "C" int fedb_conv_dgrad_s2_tf32_grouped(const float* dY, const float* Wcls, float* dX, int N, int P, int Q, int K, int C,
+                                               int groups, int fs, void* stream) {
+  FEDB_REQUIRE(groups >= 1 && C % groups == 0 && K % groups == 0, "fedb_conv_dgrad_s2_tf32_grouped: channels must divide into the groups");
+  return conv_dgrad_s2_impl(dY, Wcls, dX, N, P, Q, K / groups, C / groups, fs, K, C, groups, stream);
 }
 
 extern "C" int fedb_conv_tf32(const float* X, const float* Wk, float* Y, const float* bias, int N, int H, int W, int Cin,
@@ -638,8 +695,8 @@ extern "C" int fedb_conv3x3_tf32(const float* X, const float* Wk, float* Y, cons
 // dWk[Cout][fs*fs*Cin] (+)= sum over output pixels of dY[pix][Cout]^T * shift_tap(X)[pix][Cin]: bf16 copies of dY and X
 // (NHWC), reduction over the pixels split across CTAs, partial tiles combined with red.global.add (dWk zeroed by the
 // caller).  Strided convolutions read X through a tensor map with element strides.
-extern "C" int fedb_conv_wgrad_bf16_g(const uint16_t* dY, const uint16_t* X, float* dWk, int N, int H, int W, int Cin, int Cout,
-                                      int fs, int stride, int pad, int splits, long long dypitch, long long xpitch, void* stream) {
+static int conv_wgrad_impl(const uint16_t* dY, const uint16_t* X, float* dWk, int N, int H, int W, int Cin, int Cout, int fs,
+                           int stride, int pad, int splits, long long dypitch, long long xpitch, int groups, void* stream) {
   FEDB_REQUIRE(Cin % 8 == 0 && Cout % 8 == 0, "fedb_conv_wgrad_bf16: channels must be multiples of 8 (16-byte bf16 pitch)");
   FEDB_REQUIRE((fs == 3 && pad == 1) || (fs == 1 && pad == 0), "fedb_conv_wgrad_bf16: 3x3/pad 1 or 1x1/pad 0");
   FEDB_REQUIRE(stride == 1 || stride == 2, "fedb_conv_wgrad_bf16: stride 1 or 2");
@@ -654,8 +711,8 @@ extern "C" int fedb_conv_wgrad_bf16_g(const uint16_t* dY, const uint16_t* X, flo
   const int pix = N * P * Q, taps = fs * fs;
   const int bnt = Cin >= 128 ? 128 : 64;
   CUtensorMap ma, mb;
-  if (int rc = make_map_2d(&ma, dY, 2, pix, Cout, dypitch > 0 ? dypitch : Cout, 64, 64)) return rc;   // A^T: [K=pix][M=Cout]
-  if (int rc = make_map_nhwc(&mb, X, 2, N, H, W, Cin, bw, bh, bn, stride, xpitch)) return rc;         // B^T: shifted [pix][Cin]
+  if (int rc = make_map_2d(&ma, dY, 2, pix, groups > 1 ? dypitch : Cout, dypitch > 0 ? dypitch : Cout, 64, 64)) return rc;
+  if (int rc = make_map_nhwc(&mb, X, 2, N, H, W, groups > 1 ? (int)xpitch : Cin, bw, bh, bn, stride, xpitch)) return rc;
   GemmArgs g;
   g.D = dWk; g.bias = nullptr; g.ldd = (long long)taps * Cin; g.M = Cout; g.N = Cin;
   const int ktiles = (pix + 63) / 64;
@@ -667,9 +724,11 @@ extern "C" int fedb_conv_wgrad_bf16_g(const uint16_t* dY, const uint16_t* X, flo
   g.relu = 0; g.atomic_out = 1;
   g.conv = 2; g.Cin = Cin; g.H = P; g.W = Q; g.bw = bw; g.bh = bh; g.bn = bn; g.cstride = stride; g.cpad = pad; g.fs = fs;
   g.ostride = g.oy = g.ox = 0;
+  g.groups = groups; g.a_goff = groups > 1 ? Cin : 0; g.b_goff = groups > 1 ? Cout : 0;
+  g.d_goff = groups > 1 ? (long long)Cout * taps * Cin : 0;        // dWk of group g: [Cout][taps][Cin] after g such blocks
   static bool attr128 = false, attr64 = false;
   cudaStream_t s = (cudaStream_t)stream;
-  dim3 grid(fedb_ceil_div(Cout, BM), fedb_ceil_div(Cin, bnt) * taps, splits);
+  dim3 grid(fedb_ceil_div(Cout, BM), fedb_ceil_div(Cin, bnt) * taps * groups, splits);
   if (bnt == 128) {
     if (!attr128) { FEDB_CHECK(cudaFuncSetAttribute(gemm_tc_kernel<128, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem<128, 1>::kTotal)); attr128 = true; }
     gemm_tc_kernel<128, 1><<<grid, kThreads, Smem<128, 1>::kTotal, s>>>(ma, mb, g);
@@ -681,9 +740,22 @@ extern "C" int fedb_conv_wgrad_bf16_g(const uint16_t* dY, const uint16_t* X, flo
   return 0;
 }
 
+extern "C" int fedb_conv_wgrad_bf16_g(const uint16_t* dY, const uint16_t* X, float* dWk, int N, int H, int W, int Cin, int Cout,
+                                      int fs, int stride, int pad, int splits, long long dypitch, long long xpitch, void* stream) {
+  return conv_wgrad_impl(dY, X, dWk, N, H, W, Cin, Cout, fs, stride, pad, splits, dypitch, xpitch, 1, stream);
+}
+
 extern "C" int fedb_conv_wgrad_bf16(const uint16_t* dY, const uint16_t* X, float* dWk, int N, int H, int W, int Cin, int Cout,
                                     int fs, int stride, int pad, int splits, void* stream) {
-  return fedb_conv_wgrad_bf16_g(dY, X, dWk, N, H, W, Cin, Cout, fs, stride, pad, splits, 0, 0, stream);
+  return conv_wgrad_impl(dY, X, dWk, N, H, W, Cin, Cout, fs, stride, pad, splits, 0, 0, 1, stream);
+}
+
+// C, K: channel counts of the whole tensors; dWk = [K][taps][C / groups] (the packed OIHW of a grouped filter), zeroed
+// by the caller
+extern "C" int fedb_conv_wgrad_bf16_grouped(const uint16_t* dY, const uint16_t* X, float* dWk, int N, int H, int W, int C, int K,
+                                            int groups, int fs, int stride, int pad, int splits, void* stream) {
+  FEDB_REQUIRE(groups >= 1 && C % groups == 0 && K % groups == 0, "fedb_conv_wgrad_bf16_grouped: channels must divide into the groups");
+  return conv_wgrad_impl(dY, X, dWk, N, H, W, C / groups, K / groups, fs, stride, pad, splits, K, C, groups, stream);
 }
 
 extern "C" int fedb_conv3x3_wgrad_bf16(const uint16_t* dY, const uint16_t* X, float* dWk, int N, int H, int W, int Cin, int Cout,
@@ -692,15 +764,23 @@ extern "C" int fedb_conv3x3_wgrad_bf16(const uint16_t* dY, const uint16_t* X, fl
 }
 
 // filter (un)packing for fs*fs = taps (9 or 1); see pack3x3_kernel for the modes
-extern "C" int fedb_pack_filter(const float* w_oihw, float* out, int K, int C, int mode, int taps, void* stream) {
-  FEDB_REQUIRE(taps == 9 || (taps == 1 && mode != 1), "fedb_pack_filter: taps 9, or 1 for modes 0/2");
-  const int Rp = mode == 0 ? (C + 31) / 32 * 32 : (mode == 1 ? (K + 31) / 32 * 32 : 0);
-  const long long total = mode == 0 ? (long long)K * taps * Rp : (mode == 1 ? (long long)C * 9 * Rp : (long long)K * C * taps);
+// K: output channels over all groups, C: input channels PER GROUP (groups == 1: the plain filter)
+extern "C" int fedb_pack_filter_grouped(const float* w_oihw, float* out, int K, int C, int groups, int mode, int taps, void* stream) {
+  FEDB_REQUIRE(taps == 9 || taps == 1, "fedb_pack_filter: 9 taps or 1");
+  FEDB_REQUIRE(groups >= 1 && K % groups == 0, "fedb_pack_filter: K must divide into the groups");
+  // a 1x1 filter is its own K-major matrix: mode 1 with one tap is the plain per-group transpose, unpadded
+  const int Rp = mode == 0 ? (C + 31) / 32 * 32 : (mode == 1 ? (taps == 1 ? K / groups : (K / groups + 31) / 32 * 32) : 0);
+  const long long total = mode == 0 ? (long long)K * taps * Rp
+                                    : (mode == 1 ? (long long)groups * C * taps * Rp : (long long)K * C * taps);
   int blocks = fedb_ceil_div(total, 256);
   if (blocks > fedb_num_sms() * 8) blocks = fedb_num_sms() * 8;
-  pack3x3_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w_oihw, out, K, C, mode, taps, Rp);
+  pack3x3_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w_oihw, out, K, C, mode, taps, Rp, groups);
   FEDB_LAUNCH_OK();
   return 0;
+}
+
+extern "C" int fedb_pack_filter(const float* w_oihw, float* out, int K, int C, int mode, int taps, void* stream) {
+  return fedb_pack_filter_grouped(w_oihw, out, K, C, 1, mode, taps, stream);
 }
 
 extern "C" int fedb_pack3x3(const float* w_oihw, float* out, int K, int C, int mode, void* stream) {

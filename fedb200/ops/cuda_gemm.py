@@ -37,6 +37,11 @@ def _f(name):
             "fedb_pack_dgrad_s2": [vp, vp, i, i, vp],
             "fedb_im2col_small": [vp, vp, vp, i, i, i, i, i, i, i, vp],
             "fedb_conv_tf32_g": [vp, vp, vp, vp, i, i, i, i, i, i, i, i, i, ll, ll, vp],
+            "fedb_conv_tf32_grouped": [vp, vp, vp, vp, i, i, i, i, i, i, i, i, i, i, vp],
+            "fedb_conv_dgrad_s2_tf32_grouped": [vp, vp, vp, i, i, i, i, i, i, i, vp],
+            "fedb_conv_wgrad_bf16_grouped": [vp, vp, vp, i, i, i, i, i, i, i, i, i, i, vp],
+            "fedb_pack_filter_grouped": [vp, vp, i, i, i, i, i, vp],
+            "fedb_pack_dgrad_s2_grouped": [vp, vp, i, i, i, vp],
             "fedb_conv_wgrad_bf16_g": [vp, vp, vp, i, i, i, i, i, i, i, i, i, ll, ll, vp],
             "fedb_conv_dgrad_s2_tf32_g": [vp, vp, vp, i, i, i, i, i, i, ll, ll, vp],
             "fedb_nn_channel_copy": [vp, vp, ll, i, i, i, i, i, i, i, vp],
@@ -165,76 +170,77 @@ def _im2col(x, shp, f32: bool, bf16: bool):
     return o32, o16
 
 
-MAX_TC_GROUPS = 8         # grouped convolutions run group by group on the tensor-core kernels up to this many groups
-
-
 def _group_geometry(shp):
-    """(Cg, Kg) when a grouped 3x3 / 1x1 convolution (stride 1 or 2) can run one group per launch on the implicit-GEMM
-    kernels (pointer offset + whole-tensor pixel pitch), else None.  ResNeXt-29 (2/4/8 x 64d) is the zoo's user."""
+    """(Cg, Kg) when a grouped 3x3 / 1x1 convolution (stride 1 or 2) can run on the implicit-GEMM kernels: ALL groups in
+    one launch, the group index shifts the channel coordinates of the TMA boxes (ResNeXt, RegNet, DPN)."""
     N, H, W, Cc, K, R, S, P, Q, sh, sw, ph, pw, groups = shp
-    if groups < 2 or groups > MAX_TC_GROUPS or Cc % groups or K % groups:
+    if groups < 2 or Cc % groups or K % groups:
         return None
     Cg, Kg = Cc // groups, K // groups
-    if Cg % 8 or Kg % 8 or R != S or R not in (1, 3) or sh != sw or sh not in (1, 2) or ph != (R - 1) // 2 or pw != ph:
+    if Cg % 4 or Kg % 4 or R != S or R not in (1, 3) or sh != sw or sh not in (1, 2) or ph != (R - 1) // 2 or pw != ph:
         return None
     if not (_pow2(P) and _pow2(Q) and 2 <= Q <= 32 and P * sh == H and Q * sw == W and N * P * Q >= MIN_PIXELS):
         return None
     return Cg, Kg
 
 
+def _pack_grouped(w, mode: int, taps: int, groups: int) -> torch.Tensor:
+    K, Cg = w.shape[0], w.shape[1]
+    Kg = K // groups
+    n = K * taps * _pad32(Cg) if mode == 0 else groups * Cg * taps * (Kg if taps == 1 else _pad32(Kg))
+    out = torch.empty(n, dtype=torch.float32, device=w.device)
+    check(_f("fedb_pack_filter_grouped")(w.data_ptr(), out.data_ptr(), K, Cg, groups, mode, taps, current_stream()),
+          "fedb_pack_filter_grouped")
+    _lib.count_launch()
+    return out
+
+
 def _grouped_forward(x, w, bias, y, shp, Cg, Kg) -> bool:
     N, H, W, Cc, K, R, S, P, Q, sh, sw, ph, pw, groups = shp
-    fn = _f("fedb_conv_tf32_g")
-    for g in range(groups):
-        wg = w[g * Kg:(g + 1) * Kg]                                      # contiguous OIHW slice of the group
-        wk = pack_filter(wg, 0, 9) if R == 3 else wg
-        check(fn(x.data_ptr() + 4 * g * Cg, wk.data_ptr(), y.data_ptr() + 4 * g * Kg,
-                 0 if bias is None else bias.data_ptr() + 4 * g * Kg, N, H, W, Cg, Kg, R, sh, ph, 0, Cc, K,
-                 current_stream()), "fedb_conv_tf32_g")
-        _lib.count_launch()
+    wk = pack_filter(w, 0, 9) if R == 3 else w          # rows only know their own group's inputs: the plain packing
+    check(_f("fedb_conv_tf32_grouped")(x.data_ptr(), wk.data_ptr(), y.data_ptr(), 0 if bias is None else bias.data_ptr(),
+                                       N, H, W, Cc, K, groups, R, sh, ph, 0, current_stream()), "fedb_conv_tf32_grouped")
+    _lib.count_launch()
     return True
 
 
 def _grouped_dgrad(dy, w, dx, shp, Cg, Kg) -> bool:
     N, H, W, Cc, K, R, S, P, Q, sh, sw, ph, pw, groups = shp
-    if sh == 2 and R == 1:
+    if sh == 1:
+        wk = _pack_grouped(w, 1, R * R, groups)         # [C][flipped tap][Kg padded] (1x1: the per-group transposes)
+        check(_f("fedb_conv_tf32_grouped")(dy.data_ptr(), wk.data_ptr(), dx.data_ptr(), 0, N, H, W, K, Cc, groups, R, 1, ph, 0,
+                                           current_stream()), "fedb_conv_tf32_grouped")
+        _lib.count_launch()
+        return True
+    if R == 3:
+        wk = torch.empty(9 * Cc * _pad32(Kg), dtype=torch.float32, device=w.device)
+        check(_f("fedb_pack_dgrad_s2_grouped")(w.data_ptr(), wk.data_ptr(), K, Cg, groups, current_stream()),
+              "fedb_pack_dgrad_s2_grouped")
+        _lib.count_launch()
+    else:
+        wk = _pack_grouped(w, 1, 1, groups)
         dx.zero_()
-    for g in range(groups):
-        wg = w[g * Kg:(g + 1) * Kg]
-        dyp, dxp = dy.data_ptr() + 4 * g * Kg, dx.data_ptr() + 4 * g * Cg
-        if sh == 1:
-            wk = pack_filter(wg, 1, 9) if R == 3 else transpose(wg, Kg, Cg)
-            check(_f("fedb_conv_tf32_g")(dyp, wk.data_ptr(), dxp, 0, N, H, W, Kg, Cg, R, 1, ph, 0, K, Cc, current_stream()),
-                  "fedb_conv_tf32_g")
-            _lib.count_launch()
-        else:
-            if R == 3:
-                wk = torch.empty(9 * _pad32(Kg) * Cg, dtype=torch.float32, device=w.device)
-                check(_f("fedb_pack_dgrad_s2")(wg.data_ptr(), wk.data_ptr(), Kg, Cg, current_stream()), "fedb_pack_dgrad_s2")
-                _lib.count_launch()
-            else:
-                wk = transpose(wg, Kg, Cg)
-            check(_f("fedb_conv_dgrad_s2_tf32_g")(dyp, wk.data_ptr(), dxp, N, P, Q, Kg, Cg, R, K, Cc, current_stream()),
-                  "fedb_conv_dgrad_s2_tf32_g")
-            _lib.count_launch(4 if R == 3 else 1)
+    check(_f("fedb_conv_dgrad_s2_tf32_grouped")(dy.data_ptr(), wk.data_ptr(), dx.data_ptr(), N, P, Q, K, Cc, groups, R,
+                                                current_stream()), "fedb_conv_dgrad_s2_tf32_grouped")
+    _lib.count_launch(4 if R == 3 else 1)
     return True
 
 
 def _grouped_wgrad(x, dy, dw, db, shp, Cg, Kg) -> bool:
     N, H, W, Cc, K, R, S, P, Q, sh, sw, ph, pw, groups = shp
+    if Cg % 8 or Kg % 8:
+        return False                                     # bf16 operands need a 16-byte channel pitch per group
     taps, pix = R * R, N * P * Q
-    tiles = ((Kg + 127) // 128) * ((Cg + 127) // 128) * taps
-    splits = max(1, min(pix // 256, 444 // max(tiles * groups, 1)))
+    tiles = ((Kg + 127) // 128) * ((Cg + 127) // 128) * taps * groups
+    splits = max(1, min(pix // 256, 444 // max(tiles, 1)))
     dy16, x16 = cast_bf16(dy), cast_bf16(x)
-    for g in range(groups):
-        dwg = dw[g * Kg:(g + 1) * Kg]
-        dwk = torch.zeros(Kg * taps * Cg, dtype=torch.float32, device=x.device) if taps > 1 else dwg
-        check(_f("fedb_conv_wgrad_bf16_g")(dy16.data_ptr() + 2 * g * Kg, x16.data_ptr() + 2 * g * Cg, dwk.data_ptr(), N, H, W,
-                                           Cg, Kg, R, sh, ph, splits, K, Cc, current_stream()), "fedb_conv_wgrad_bf16_g")
+    dwk = torch.zeros(K * taps * Cg, dtype=torch.float32, device=x.device) if taps > 1 else dw
+    check(_f("fedb_conv_wgrad_bf16_grouped")(dy16.data_ptr(), x16.data_ptr(), dwk.data_ptr(), N, H, W, Cc, K, groups, R, sh, ph,
+                                             splits, current_stream()), "fedb_conv_wgrad_bf16_grouped")
+    _lib.count_launch()
+    if taps > 1:
+        check(_f("fedb_pack_filter")(dwk.data_ptr(), dw.data_ptr(), K, Cg, 2, taps, current_stream()), "fedb_pack_filter")
         _lib.count_launch()
-        if taps > 1:
-            check(_f("fedb_pack_filter")(dwk.data_ptr(), dwg.data_ptr(), Kg, Cg, 2, taps, current_stream()), "fedb_pack_filter")
-            _lib.count_launch()
     if db is not None:
         db += dy.sum(dim=(0, 2, 3))
     return True

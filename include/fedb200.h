@@ -236,6 +236,19 @@ int fedb_conv_wgrad_bf16_g(const uint16_t* dY, const uint16_t* X, float* dWk, in
                            int stride, int pad, int splits, long long dypitch, long long xpitch, void* stream);
 int fedb_conv_dgrad_s2_tf32_g(const float* dY, const float* Wcls, float* dX, int N, int P, int Q, int Cout, int Cin, int fs,
                               long long dypitch, long long dxpitch, void* stream);
+/* All groups of a grouped convolution in ONE launch (blockIdx.z / blockIdx.y carries the group): C and K are the channel
+ * counts of the whole tensors, the filter is the grouped OIHW tensor [K][C/groups][fs][fs].  Packing: forward = plain
+ * fedb_pack_filter mode 0 with C/groups input channels; stride-1 data gradient = fedb_pack_filter_grouped mode 1 (one row
+ * per input channel of the whole tensor; a 1x1 filter gives the unpadded per-group transposes); stride-2 data gradient =
+ * fedb_pack_dgrad_s2_grouped.  Per-group channel counts: % 4 (forward / data gradient), % 8 (weight gradient). */
+int fedb_conv_tf32_grouped(const float* X, const float* Wk, float* Y, const float* bias, int N, int H, int W, int C, int K,
+                           int groups, int fs, int stride, int pad, int relu, void* stream);
+int fedb_conv_dgrad_s2_tf32_grouped(const float* dY, const float* Wcls, float* dX, int N, int P, int Q, int K, int C, int groups,
+                                    int fs, void* stream);
+int fedb_conv_wgrad_bf16_grouped(const uint16_t* dY, const uint16_t* X, float* dWk, int N, int H, int W, int C, int K, int groups,
+                                 int fs, int stride, int pad, int splits, void* stream);
+int fedb_pack_filter_grouped(const float* w_oihw, float* out, int K, int C_per_group, int groups, int mode, int taps, void* stream);
+int fedb_pack_dgrad_s2_grouped(const float* w_oihw, float* out, int K, int C_per_group, int groups, void* stream);
 int fedb_conv3x3_wgrad_bf16(const uint16_t* dY, const uint16_t* X, float* dWk, int N, int H, int W, int Cin, int Cout,
                             int splits, void* stream);
 /* mode 0: OIHW -> [K][tap][C]; mode 1: OIHW -> [C][flipped tap][K] (data gradient); mode 2: [K][tap][C] -> OIHW */
