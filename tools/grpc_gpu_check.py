@@ -1,4 +1,4 @@
-"""gRPC control plane + GPU data plane, end to end on one box with >= 2 GPUs:
+"""gRPC control plane + GPU data plane, end to end on one box with >= 2 GPUs (FEDB200_CHECK_WORLD=8 for eight):
 
   coordinator (this process, no GPU context) --StartTrain/SendModel descriptors--> 2 worker processes
   (``python -m fedb200.client --plane peer``), one per GPU, whose arenas are peer-mapped; FedAvg, broadcast and
@@ -38,9 +38,12 @@ def wait_port(port, timeout=240):
     return False
 
 
+WORLD = int(os.environ.get("FEDB200_CHECK_WORLD", "2"))     # workers = GPUs (config 4 of BASELINE.json uses 8)
+
+
 def spawn_worker(rank, port, tag, work, rejoin=False):
     cmd = [sys.executable, "-m", "fedb200.client", "-a", f"127.0.0.1:{port}", "--plane", "peer", "--model", "LeNet",
-           "--device", f"cuda:{rank}", "--peer-rank", str(rank), "--peer-world", "2", "--peer-tag", tag,
+           "--device", f"cuda:{rank}", "--peer-rank", str(rank), "--peer-world", str(WORLD), "--peer-tag", tag,
            "--dataset-size", "2048", "--test-size", "500", "--seed", str(10 + rank), "--agg-timeout", "4"]
     if rejoin:
         cmd.append("--rejoin")
@@ -52,8 +55,8 @@ def spawn_worker(rank, port, tag, work, rejoin=False):
 def main():
     work = tempfile.mkdtemp(prefix="fedb200-grpcgpu-")
     tag = f"g{os.getpid()}"
-    ports = [free_port(), free_port()]
-    procs = [spawn_worker(r, ports[r], tag, work) for r in range(2)]
+    ports = [free_port() for _ in range(WORLD)]
+    procs = [spawn_worker(r, ports[r], tag, work) for r in range(WORLD)]
     try:
         assert all(wait_port(p) for p in ports), "workers did not come up"
         bport = free_port()
@@ -67,7 +70,7 @@ def main():
         c = Coordinator(ccfg, term=1)
         assert c.run() == 3
         rounds = [r for r in c.sink.records if r["event"] == "round"]
-        assert all(r["uploads"] == 2 and r["plane"] == "peer" for r in rounds), rounds
+        assert all(r["uploads"] == WORLD and r["plane"] == "peer" for r in rounds), rounds
         assert all(r["bytes_up"] == 0 for r in rounds)                       # no weights in the RPC payloads
         glob = ckpt.load_checkpoint(os.path.join(work, "Primary", "optimizedModel.pth"))
         assert list(glob["net"].keys())[0] == "conv1.weight" and glob["acc"] == 1
@@ -80,7 +83,7 @@ def main():
         c.cfg.rounds = 6
         done = c.run()
         rounds = [r for r in c.sink.records if r["event"] == "round"]
-        assert done == 3 and rounds[-1]["uploads"] == 1, (done, rounds[-3:])
+        assert done == 3 and rounds[-1]["uploads"] == WORLD - 1, (done, rounds[-3:])
         assert c.members.snapshot()[ccfg.workers[1]] is False
         print("phase 2 ok: worker 1 killed, rounds continue with the survivor:", [r["uploads"] for r in rounds])
 
@@ -94,7 +97,7 @@ def main():
         c.cfg.rounds = c.round + 2
         done = c.run()
         rounds = [r for r in c.sink.records if r["event"] == "round"]
-        assert done == 2 and rounds[-1]["uploads"] == 2, (done, rounds[-2:])
+        assert done == 2 and rounds[-1]["uploads"] == WORLD, (done, rounds[-2:])
         print("phase 3 ok: worker 1 re-admitted, uploads per round:", [r["uploads"] for r in rounds])
         last_round = c.round
         c.close()
