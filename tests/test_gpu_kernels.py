@@ -276,6 +276,21 @@ def test_gpu_trainer_pass_matches_cpu_trainer(K):
     assert eb2.correct == eb.correct
 
 
+def test_gpu_trainer_generic_model_eval_graph(K):
+    """A zoo model other than LeNet through the trainer: the evaluation pass (batches of 500, one CUDA graph) gives the
+    CPU trainer's loss / accuracy, and its replay gives the same numbers again."""
+    from fedb200.control.trainer import LocalTrainer, TrainerConfig
+    ds = D.synthetic_cifar(128, 1100, seed=6)
+    cpu = LocalTrainer(TrainerConfig(model="MobileNet", device="cpu", seed=3), ds)
+    gpu = LocalTrainer(TrainerConfig(model="MobileNet", device=DEV, seed=3), ds)
+    gpu.load_state_dict(cpu.state_dict())
+    ea, eb = cpu.test(), gpu.test()
+    assert ea.samples == eb.samples == 1100
+    assert abs(ea.mean_loss - eb.mean_loss) < 5e-2 * max(1.0, abs(ea.mean_loss)) and abs(ea.correct - eb.correct) <= 30
+    eb2 = gpu.test()
+    assert eb2.correct == eb.correct and eb2.loss_sum == eb.loss_sum
+
+
 def test_mem_manager_roundtrip_single_process(K):
     import ctypes as C
     from fedb200.ops import _lib
