@@ -288,3 +288,47 @@ extern "C" int fedb_flag_barrier(fedb_ctrl_t* local, fedb_ctrl_t* const* peers, 
   FEDB_LAUNCH_OK();
   return 0;
 }
+
+// ---------------------------------------------------------------------------------------------- K-PUSH
+// Bit-exact fan-out of a byte range into peer memory: dst[k][i] = src[i] for every destination, or ONE multimem.st per
+// 16 bytes through the NVLS multicast alias (the switch replicates it, the bytes cross this GPU's links once).  No
+// arithmetic touches the data, so it carries uint8 images as well as floats.  Used to all-gather the evaluation set:
+// every rank uploads 1/N of it from its host and pushes that slice to everybody over NVLink, instead of N ranks
+// pulling the whole set through their own PCIe links every round.  The caller orders the reads of the peers (K-AGG's
+// arrive / done flags of the same round do that in the federation round).
+struct PushArgs {
+  const float4* src;
+  float4* dst[FEDB_MAX_DST];
+  float4* mc_dst;
+  int n_dst;
+  long long n4;
+};
+
+__global__ void __launch_bounds__(256) push_copy_kernel(PushArgs a) {
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < a.n4; i += (long long)gridDim.x * 256) {
+    const float4 v = a.src[i];
+    if (a.mc_dst != nullptr) {
+      mc_st_f4(reinterpret_cast<float*>(a.mc_dst), i, v);
+    } else {
+      for (int k = 0; k < a.n_dst; ++k) a.dst[k][i] = v;
+    }
+  }
+}
+
+extern "C" int fedb_push_copy(const void* src, void* const* dst, int n_dst, void* mc_dst, uint64_t bytes, void* stream) {
+  FEDB_REQUIRE(src != nullptr && bytes % 16 == 0, "fedb_push_copy: bytes must be a multiple of 16");
+  FEDB_REQUIRE(mc_dst != nullptr || (n_dst >= 1 && n_dst <= FEDB_MAX_DST), "fedb_push_copy: 1..FEDB_MAX_DST destinations");
+  FEDB_REQUIRE((((uintptr_t)src | (uintptr_t)mc_dst) & 15) == 0, "fedb_push_copy: pointers must be 16-byte aligned");
+  if (bytes == 0) return 0;
+  PushArgs a;
+  a.src = (const float4*)src; a.mc_dst = (float4*)mc_dst; a.n_dst = mc_dst ? 0 : n_dst; a.n4 = (long long)(bytes / 16);
+  for (int k = 0; k < FEDB_MAX_DST; ++k) {
+    a.dst[k] = (!mc_dst && k < n_dst) ? (float4*)dst[k] : nullptr;
+    FEDB_REQUIRE(((uintptr_t)a.dst[k] & 15) == 0, "fedb_push_copy: destinations must be 16-byte aligned");
+  }
+  long long blocks = (a.n4 + 255) / 256;
+  if (blocks > fedb_num_sms() * 4) blocks = fedb_num_sms() * 4;
+  push_copy_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(a);
+  FEDB_LAUNCH_OK();
+  return 0;
+}

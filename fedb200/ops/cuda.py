@@ -115,6 +115,14 @@ def replicate(dst, src, dst_ctrl: torch.Tensor, version: int, stream: Optional[i
     _lib.count_launch()
 
 
+def push_copy(src_ptr: int, dst_ptrs: Sequence[int], nbytes: int, mc_dst: int = 0, stream: Optional[int] = None) -> None:
+    """K-PUSH: bit-exact copy of ``nbytes`` at ``src_ptr`` into every peer pointer (or through the multicast alias)."""
+    arr = (C.c_void_p * max(len(dst_ptrs), 1))(*dst_ptrs)
+    check(lib().fedb_push_copy(src_ptr, arr, len(dst_ptrs), mc_dst or None, nbytes,
+                               current_stream() if stream is None else stream), "fedb_push_copy")
+    _lib.count_launch()
+
+
 # ------------------------------------------------------------------------------------ K-CODEC
 def codec_encode(cur: torch.Tensor, base: torch.Tensor, residual: torch.Tensor, q: torch.Tensor,
                  scale: torch.Tensor) -> None:

@@ -54,6 +54,9 @@ class CudaEngine:
         self._shards: Dict[Tuple[int, ...], dict] = {}
         self._test_dev = None
         self._test_resident = False
+        self._tex = None                  # evaluation-set exchange over NVLink (multi-GPU sessions)
+        self._slot = 0                    # half of the exchange double buffer that holds / receives the current round's set
+        self._tex_on = False
         self._eval_graph = None
         self.h2d_bytes_last = 0
         self.d2h_bytes_last = 0
@@ -142,7 +145,21 @@ class CudaEngine:
                 hx, hy = hx.pin_memory(), hy.pin_memory()
             self._test_host = (hx, hy)
             self._test_dev = (torch.empty_like(hx, device=self.dev), torch.empty_like(hy, device=self.dev))
+        if self._tex is not None:          # images live in the peer-mapped double buffer, labels stay local
+            return [(self._tex.images(self._slot), self._test_host[0]), (self._test_dev[1], self._test_host[1])]
         return list(zip(self._test_dev, self._test_host))
+
+    def set_test_exchange(self, ex) -> None:
+        """``ex`` (fedb200.parallel.session.TestExchange): the evaluation images are all-gathered over NVLink - every rank
+        uploads 1/N of them and pushes that slice into every peer's double buffer - instead of N full PCIe uploads."""
+        self._tex = ex
+        self._eval_graph = None
+        for sh in self._shards.values():
+            sh["graph"] = None
+
+    def _test_images(self) -> torch.Tensor:
+        self._test_buffers()
+        return self._tex.images(self._slot) if self._tex is not None else self._test_dev[0]
 
     def _test_bytes(self) -> int:
         return self._test_host[0].numel() + self._test_host[1].numel() * 8
@@ -168,8 +185,17 @@ class CudaEngine:
                     self._generic_step(x, y, i + 1)
 
         def tail(side):                                              # the round's test set rides behind the shard
-            for d, h in self._test_buffers():
-                self._h2d(d, h, 0, h.shape[0], side)
+            pairs = self._test_buffers()
+            if self._tex is not None and self._tex_on:
+                # all-gather: my 1/N of the images comes up from my host, K-PUSH sends it to every peer over NVLink
+                # (their slices arrive the same way; this round's K-AGG flags order them before anybody's evaluation)
+                lo, hi = self._tex.rows(self._tex.rank)
+                self._h2d(pairs[0][0], pairs[0][1], lo, hi, side)
+                self._h2d(pairs[1][0], pairs[1][1], 0, pairs[1][1].shape[0], side)
+                self._tex.push(self._slot, side.cuda_stream)
+            else:
+                for d, h in pairs:
+                    self._h2d(d, h, 0, h.shape[0], side)
 
         self._streamed([(sh["dx"], sh["hx"]), (sh["dy"], sh["hy"])], bounds, work, upload,
                        tail if (upload and with_test) else None)
@@ -196,7 +222,10 @@ class CudaEngine:
                 return self.TrainStats()
             upload = bool(upload)
             with_test = bool(with_test) and upload
-            key = (upload, with_test)
+            if with_test and self._tex is not None:
+                self._slot ^= 1                               # this round's set goes into the other half
+                self._tex_on = self._tex.enabled()
+            key = (upload, with_test, self._slot if with_test else -1, self._tex_on if with_test else False)
             self.stats.zero_()
             self.seed_dev += 1
             if self.cfg.use_cuda_graph:
@@ -219,7 +248,8 @@ class CudaEngine:
             if upload:
                 self.h2d_bytes_last = sh["hx"].numel() + sh["hy"].numel() * 8
                 if with_test:
-                    self.h2d_bytes_last += self._test_bytes()
+                    self.h2d_bytes_last += self._test_bytes() if not (self._tex is not None and self._tex_on) \
+                        else self._tex.slice_bytes() + self._test_host[1].numel() * 8
             self._test_resident = with_test
             self.arena.sgd_steps += len(sh["sizes"])
             return self.read_stats() if sync else None
@@ -292,14 +322,17 @@ class CudaEngine:
                 step = chunk if copy else n
                 bounds = list(range(0, n, step)) + [n]
 
+                imgs = self._test_images()
+
                 def work(c):
                     lo, hi = bounds[c], bounds[c + 1]
-                    self.plan.eval_batch(self._test_dev[0][lo:hi], self._test_dev[1][lo:hi], self.eval_stats)
+                    self.plan.eval_batch(imgs[lo:hi], self._test_dev[1][lo:hi], self.eval_stats)
 
                 graphs = self._eval_graph if self._eval_graph is not None else {}
                 self._eval_graph = graphs
-                if self.cfg.use_cuda_graph and copy in graphs:
-                    graphs[copy].replay()
+                gkey = (copy, self._slot)
+                if self.cfg.use_cuda_graph and gkey in graphs:
+                    graphs[gkey].replay()
                     _lib.count_launch(2 * (len(bounds) - 1))
                 else:
                     self._streamed(pairs, bounds, work, copy)
@@ -308,24 +341,27 @@ class CudaEngine:
                         g = torch.cuda.CUDAGraph()
                         with _quiet_gc(), torch.cuda.graph(g, stream=torch.cuda.Stream(device=self.dev)):
                             self._streamed(pairs, bounds, work, copy)
-                        graphs[copy] = g
+                        graphs[gkey] = g
             else:
                 # eval-mode results do not depend on the batch size (BN uses running statistics): evaluate in batches of
                 # at least 500 instead of the reference's 100 (src/main.py:54-55) and replay the pass as one CUDA graph
                 bs = max(self.cfg.test_batch_size, 500)
                 bounds = list(range(0, n, bs)) + [n]
 
+                imgs = self._test_images()
+
                 def work(c):
                     lo, hi = bounds[c], bounds[c + 1]
-                    x = K.prepare_batch(self._test_dev[0][lo:hi], nhwc=True)
+                    x = K.prepare_batch(imgs[lo:hi], nhwc=True)
                     out = self.t.model(x)
                     K.cross_entropy_raw(out.contiguous(), self._test_dev[1][lo:hi], None, None, self.eval_stats)
 
                 graphs = self._eval_graph if self._eval_graph is not None else {}
                 self._eval_graph = graphs
+                gkey = (copy, self._slot)                    # graph key: which half of the double buffer is read
                 with torch.no_grad():
-                    if self.cfg.use_cuda_graph and copy in graphs:
-                        graphs[copy].replay()
+                    if self.cfg.use_cuda_graph and gkey in graphs:
+                        graphs[gkey].replay()
                     else:
                         self._streamed(pairs, bounds, work, copy)
                         if self.cfg.use_cuda_graph:
@@ -333,5 +369,5 @@ class CudaEngine:
                             g = torch.cuda.CUDAGraph()
                             with _quiet_gc(), torch.cuda.graph(g, stream=torch.cuda.Stream(device=self.dev)):
                                 self._streamed(pairs, bounds, work, copy)
-                            graphs[copy] = g
+                            graphs[gkey] = g
             return self.read_stats("eval") if sync else None

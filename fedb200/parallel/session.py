@@ -21,7 +21,9 @@ import torch
 from ..control.trainer import LocalTrainer, TrainerConfig
 from ..ops import _lib
 from ..utils import data as D
+from ..ops import cuda as K
 from .group import FedGroup
+from .mem import PeerGroup, PeerLayout, tensor_from_ptr
 
 
 def dist_min_barrier():
@@ -35,11 +37,69 @@ def dist_min_barrier():
     return fn
 
 
+class TestExchange:
+    """All-gather of the evaluation images over NVLink (K-PUSH, csrc/fedavg.cu).
+
+    Every client evaluates the global model on the SAME test set every round (N8).  Instead of N processes each
+    pulling all of it through their own PCIe link, rank r uploads rows ``rows(r)`` from its pinned copy and pushes
+    them into every peer's buffer - one ``multimem.st`` stream through the NVLS multicast alias, or unicast peer
+    stores.  The buffer is double (one half per round parity): a rank can run at most one K-AGG ahead of its peers, so
+    round r+2's pushes never land in a half that somebody still evaluates.  Ordering of the pushes before the peers'
+    evaluation comes from the round's K-AGG flags: a rank raises its "arrived" flag after its own pushes (same stream
+    order), and nobody leaves the aggregation before everybody has arrived.
+    """
+    __test__ = False
+
+    def __init__(self, group: FedGroup, n_rows: int, row_bytes: int, tag: str, dist_barrier=None, use_multicast: bool = True):
+        self.group, self.rank, self.world = group, group.rank, group.world
+        self.n_rows, self.row_bytes = n_rows, row_bytes
+        self.half_bytes = (n_rows * row_bytes + 255) // 256 * 256
+        layout = PeerLayout(n_f32=2 * self.half_bytes // 4, n_i64=0, with_codec=False)
+        self.peers = PeerGroup(self.rank, self.world, group.device, layout, tag, use_multicast=use_multicast,
+                               barrier=dist_barrier)
+        me = self.peers.me
+        self._views = [tensor_from_ptr(me.client_f32_ptr() + h * self.half_bytes, n_rows * row_bytes, torch.uint8,
+                                       group.device) for h in (0, 1)]
+
+    def enabled(self) -> bool:
+        """Only while every rank takes part: a dead rank's slice would never arrive (then each rank uploads all rows)."""
+        return len(self.group.live) == self.world
+
+    def rows(self, r: int):
+        return r * self.n_rows // self.world, (r + 1) * self.n_rows // self.world
+
+    def slice_bytes(self) -> int:
+        lo, hi = self.rows(self.rank)
+        return (hi - lo) * self.row_bytes
+
+    def images(self, half: int) -> torch.Tensor:
+        return self._views[half].view(self.n_rows, *self._shape)
+
+    def set_shape(self, shape) -> None:
+        self._shape = tuple(shape)
+
+    def push(self, half: int, stream: int) -> None:
+        lo, hi = self.rows(self.rank)
+        off = half * self.half_bytes + lo * self.row_bytes
+        nbytes = (hi - lo) * self.row_bytes
+        bufs = self.peers.buffers
+        mc = self.peers.mc_client_f32_ptr()
+        if mc:
+            # the multicast store also lands in my own copy, which already holds the bytes: harmless
+            K.push_copy(bufs[self.rank].client_f32_ptr() + off, [], nbytes, mc_dst=mc + off, stream=stream)
+        else:
+            K.push_copy(bufs[self.rank].client_f32_ptr() + off,
+                        [bufs[r].client_f32_ptr() + off for r in range(self.world) if r != self.rank], nbytes, stream=stream)
+
+    def close(self):
+        self.peers.close()
+
+
 class GpuFederation:
     def __init__(self, model: str = "LeNet", rank: int = 0, world: int = 1, device: Optional[int] = None,
                  dataset: Optional[D.ImageDataset] = None, seed: Optional[int] = None, tag: Optional[str] = None,
                  lr: float = 0.1, batch_size: int = 128, augment: bool = False, evaluate: bool = True,
-                 **group_kw):
+                 test_allgather: Optional[bool] = None, **group_kw):
         device = rank if device is None else device
         torch.cuda.set_device(device)
         self.rank, self.world, self.evaluate = rank, world, evaluate
@@ -51,6 +111,19 @@ class GpuFederation:
         tag = tag or os.environ.get("MASTER_PORT", "solo") + f"-{os.getppid()}"
         self.group = FedGroup(self.trainer, rank, world, tag, dist_barrier=dist_min_barrier(), **group_kw)
         self.rounds = 0
+        # evaluation-set all-gather over NVLink: on by default for rank-symmetric multi-GPU sessions (torchrun); workers
+        # that may be restarted one by one (gRPC plane: persistent_server / rejoin) keep the plain per-rank upload
+        if test_allgather is None:
+            test_allgather = world > 1 and evaluate and not (group_kw.get("persistent_server") or group_kw.get("rejoin"))
+        self.exchange = None
+        if test_allgather and world > 1:
+            tx = ds.test_x
+            row = int(tx[0].numel()) * tx.element_size()
+            if row % 16 == 0:
+                self.exchange = TestExchange(self.group, int(tx.shape[0]), row, tag + "-tst", dist_barrier=dist_min_barrier(),
+                                             use_multicast=group_kw.get("use_multicast", True))
+                self.exchange.set_shape(tx.shape[1:])
+                self.engine.set_test_exchange(self.exchange)
 
     def run_round(self, upload: bool = True, sync: bool = True):
         """One federated round.  Returns (train_stats, eval_stats) when ``sync``; with ``sync=False``
@@ -85,6 +158,9 @@ class GpuFederation:
         return 32 + 4
 
     def close(self):
+        if self.exchange is not None:
+            torch.cuda.synchronize()
+            self.exchange.close()
         self.group.close()
 
 

@@ -88,6 +88,12 @@ int fedb_fedavg(const fedb_agg_desc_t* desc, int max_blocks, void* stream);
 int fedb_replicate(float* dst, const float* src, int64_t n_f32, int64_t* dst_i64, const int64_t* src_i64,
                    int64_t n_i64, fedb_ctrl_t* dst_ctrl, uint32_t version, void* stream);
 
+/* K-PUSH: bit-exact fan-out of `bytes` (multiple of 16) from local memory into n_dst peer buffers, or through the NVLS
+ * multicast alias mc_dst when it is non-NULL (one multimem.st per 16 bytes).  No arithmetic: carries any data type.
+ * Used to all-gather per-round inputs that every client needs (the evaluation set) over NVLink instead of N PCIe
+ * uploads.  No counterpart in the reference (every worker loads its own copy of CIFAR-10, src/main.py:43-56). */
+int fedb_push_copy(const void* src, void* const* dst, int n_dst, void* mc_dst, uint64_t bytes, void* stream);
+
 /* Barrier on device flags only (bounded spin). */
 int fedb_flag_barrier(fedb_ctrl_t* local, fedb_ctrl_t* const* peers, int rank, int world,
                       uint64_t timeout_ns, void* stream);

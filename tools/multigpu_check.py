@@ -104,6 +104,30 @@ def main():
         dist.barrier()
         fed.close()
         dist.barrier()
+    # ---- evaluation-set all-gather over NVLink (K-PUSH): every rank uploads 1/N of the test images and pushes its slice
+    # to all peers; the evaluation must give, on every rank, exactly what a full local upload gives
+    for mc in (True, False):
+        fed = GpuFederation(model="LeNet", rank=rank, world=world, device=local, dataset=ds, seed=100 + rank,
+                            tag=f"mg-tex{int(mc)}-{os.environ['MASTER_PORT']}", evaluate=True, use_multicast=mc)
+        assert fed.exchange is not None and fed.exchange.enabled()
+        for r in range(4):                                   # both halves of the double buffer, live and as graph replays
+            tr, ev = fed.run_round(upload=True)
+            assert ev.samples == 500
+        torch.cuda.synchronize()
+        dist.barrier()
+        h2d = fed.h2d_bytes_per_round()
+        ev_local = fed.engine.eval_pass(upload=True, sync=True)      # full local upload into the current half
+        assert (ev.correct, ev.loss_sum) == (ev_local.correct, ev_local.loss_sum), (ev, ev_local)
+        allc = gather(torch.tensor([float(ev.correct), ev.loss_sum], device="cuda"))
+        assert all(torch.equal(allc[0], c) for c in allc), "ranks disagree on the evaluation of the same global model"
+        shard = fed.trainer.shard(rank, world)
+        n_shard = sum(min(128, ds.train_x.shape[0] - b * 128) for b in shard)
+        lo, hi = fed.exchange.rows(rank)
+        assert h2d == n_shard * (3072 + 8) + (hi - lo) * 3072 + 500 * 8, (h2d, n_shard, lo, hi)
+        report[f"exchange-mc{int(mc)}"] = {"multicast": bool(fed.exchange.peers.mc_base)}
+        dist.barrier()
+        fed.close()
+        dist.barrier()
     if rank == 0:
         print("MULTIGPU_CHECK_OK", world, report)
     dist.destroy_process_group()
