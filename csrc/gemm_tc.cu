@@ -12,13 +12,19 @@
 // (TF32 operands in MN-major order need the 32-byte-atom swizzle variant; the weight gradient instead reads
 //  bf16 copies of dY and X, which is also what mixed-precision training stores for the backward pass.)
 //
-// Structure (one CTA per 128 x BN output tile, 6 warps):
-//   warp 0      TMA producer: cp.async.bulk.tensor.2d (128B swizzle) into a 4-stage smem ring, mbarrier tx-count
-//   warp 1      TMEM allocation + MMA issue: one elected lane issues tcgen05.mma.cta_group::1.kind::tf32,
+// The same kernel runs convolutions as IMPLICIT GEMMs (no im2col buffer): every filter tap is a shifted 4-D TMA box of
+// the NHWC activation (TMA's out-of-bounds zero fill is the padding and the channel-tail padding, TMA element strides
+// are the stride-2 sampling), the stride-2 data gradient is four parity-class GEMMs with a scattering epilogue, the
+// weight gradient is the bf16 MN-major form over shifted boxes, and grouped convolutions run all groups in one launch
+// (the group index shifts the channel coordinates).  See the host entry points at the end of the file.
+//
+// Structure (one CTA per 128 x BN output tile, 6 warps, two CTAs per SM):
+//   warp 0      TMA producer: cp.async.bulk.tensor.2d/4d (128B swizzle) into a 3-4 stage smem ring, mbarrier tx-count
+//   warp 1      TMEM allocation + MMA issue: one elected lane issues tcgen05.mma.cta_group::1.kind::tf32 / kind::f16,
 //               tcgen05.commit releases smem stages and finally signals the epilogue
-//   warps 2..5  epilogue: tcgen05.ld (32 lanes x 32 bit) -> registers -> bias / ReLU -> global stores
-//               (red.global.add for split-K partial tiles)
-// SASS evidence expected: UTCHMMA/UTCQMMA-family for the MMA, LDTM for tcgen05.ld, UTMALDG for TMA.
+//   warps 2..5  epilogue: tcgen05.ld (32 lanes x 32 bit) -> registers -> bias / ReLU -> staging through the (now idle)
+//               pipeline smem -> whole 512-byte rows to global memory (red.global.add for split-K partial tiles)
+// SASS evidence (profiles/sass_evidence.md): UTCHMMA for the MMA, LDTM for tcgen05.ld, UTMALDG.2D/4D for TMA.
 #include "common.cuh"
 #include "../include/fedb200.h"
 #include <cuda.h>

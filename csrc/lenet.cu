@@ -5,8 +5,9 @@
 //                      softmax-CE -> backward through the three linears (data path) -> un-pool -> conv2 wgrad +
 //                      sparse dgrad -> conv1 wgrad.  Leaves per-sample rows in scratch: conv partial gradients,
 //                      (flat, h1, h2) and (dh1, dh2, dlogits).  No cross-sample dependency, no atomics.
-//   U  update kernel   one thread per parameter: fc weight gradients as fixed-order batch reductions
-//                      dW = sum_s dout[s] (x) in[s], conv partial reduction, then the SGD update (K10) in place.
+//   U  update kernel   fc weight gradients as fixed-order batch reductions dW = sum_s dout[s] (x) in[s] (8 x 128 tiles,
+//                      4 rows per thread), conv / bias partial reductions, then the SGD update (K10) in place.
+//   E  eval kernel     forward + loss / correct of five samples per CTA, two CTAs per SM (the per-round evaluation).
 //
 // fp32 on CUDA cores on purpose: N_out is 6/16/10 and K is 75/150/400, far below a tcgen05 tile, and fp32 keeps
 // the step comparable bit-for-tolerance with the reference's CPU run (src/models/lenet.py:5-23,
