@@ -1,4 +1,4 @@
-// Depthwise 3x3 convolution (groups == Cin == Cout), forward / data gradient / weight gradient, NHWC fp32.
+// Depthwise RxR convolution, R in {3, 5, 7} (groups == Cin == Cout), forward / data gradient / weight gradient, NHWC fp32.
 // MobileNet, MobileNetV2, EfficientNet, ShuffleNet(V2) spend most of their layers here (reference:
 // src/models/mobilenet.py:14-17, mobilenetv2.py:20-22, efficientnet.py:60-67, shufflenetv2.py:33-36 - nn.Conv2d with
 // groups=planes).  There is no reduction over channels, so this is a streaming op: the arithmetic intensity is 9 FMA
@@ -18,6 +18,34 @@ struct DwShape {
   int N, H, W, C, P, Q, sh, sw, ph, pw;
 };
 
+// Filter taps of four channels.  3x3 and 5x5 filters live in registers for the whole pixel run; a 7x7 filter (49 x 4
+// values) would not fit, so its taps are re-read through L1 at every use (the filter is a few KB and stays cached).
+template <int R, bool kInRegs = (R <= 5)>
+struct Taps;
+
+template <int R>
+struct Taps<R, true> {
+  float4 t[R * R];
+  __device__ __forceinline__ void load(const float* __restrict__ w, int c) {
+#pragma unroll
+    for (int k = 0; k < R * R; ++k)
+      t[k] = make_float4(__ldg(w + (c + 0) * R * R + k), __ldg(w + (c + 1) * R * R + k), __ldg(w + (c + 2) * R * R + k),
+                         __ldg(w + (c + 3) * R * R + k));
+  }
+  __device__ __forceinline__ float4 get(int k) const { return t[k]; }
+};
+
+template <int R>
+struct Taps<R, false> {
+  const float* w_;
+  int c_;
+  __device__ __forceinline__ void load(const float* __restrict__ w, int c) { w_ = w; c_ = c; }
+  __device__ __forceinline__ float4 get(int k) const {
+    return make_float4(__ldg(w_ + (c_ + 0) * R * R + k), __ldg(w_ + (c_ + 1) * R * R + k), __ldg(w_ + (c_ + 2) * R * R + k),
+                       __ldg(w_ + (c_ + 3) * R * R + k));
+  }
+};
+
 __device__ __forceinline__ float4 ld4(const float* p) { return *reinterpret_cast<const float4*>(p); }
 __device__ __forceinline__ void fma4(float4& a, const float4& x, const float4& w) {
   a.x = fmaf(x.x, w.x, a.x);
@@ -26,17 +54,10 @@ __device__ __forceinline__ void fma4(float4& a, const float4& x, const float4& w
   a.w = fmaf(x.w, w.w, a.w);
 }
 
-// taps of four channels: w is OIHW with one input channel per group, i.e. [C][3][3]
-__device__ __forceinline__ void load_taps(const float* __restrict__ w, int c, float4 (&t)[9]) {
-#pragma unroll
-  for (int k = 0; k < 9; ++k)
-    t[k] = make_float4(__ldg(w + (c + 0) * 9 + k), __ldg(w + (c + 1) * 9 + k), __ldg(w + (c + 2) * 9 + k),
-                       __ldg(w + (c + 3) * 9 + k));
-}
-
 constexpr int kRun = 8;      // output pixels per thread along the row
 
 // y[n,p,q,c] = bias[c] + sum_{r,s} x[n, p*sh - ph + r, q*sw - pw + s, c] * w[c][r][s]
+template <int R>
 __global__ void __launch_bounds__(256) dw_fwd_kernel(const float* __restrict__ x, const float* __restrict__ w,
                                                     const float* __restrict__ bias, float* __restrict__ y, DwShape d) {
   const int C4 = d.C >> 2, runs = (d.Q + kRun - 1) / kRun;
@@ -47,21 +68,21 @@ __global__ void __launch_bounds__(256) dw_fwd_kernel(const float* __restrict__ x
     const int q0 = (int)(t % runs) * kRun;
     t /= runs;
     const int p = (int)(t % d.P), n = (int)(t / d.P);
-    float4 tap[9];
-    load_taps(w, c, tap);
+    Taps<R> tap;
+    tap.load(w, c);
     const float4 b = bias != nullptr ? ld4(bias + c) : make_float4(0.f, 0.f, 0.f, 0.f);
     const int qe = min(q0 + kRun, d.Q);
     for (int q = q0; q < qe; ++q) {
       float4 acc = b;
 #pragma unroll
-      for (int r = 0; r < 3; ++r) {
+      for (int r = 0; r < R; ++r) {
         const int ih = p * d.sh - d.ph + r;
         if (ih < 0 || ih >= d.H) continue;
 #pragma unroll
-        for (int s = 0; s < 3; ++s) {
+        for (int s = 0; s < R; ++s) {
           const int iw = q * d.sw - d.pw + s;
           if (iw < 0 || iw >= d.W) continue;
-          fma4(acc, ld4(x + (((long long)n * d.H + ih) * d.W + iw) * d.C + c), tap[r * 3 + s]);
+          fma4(acc, ld4(x + (((long long)n * d.H + ih) * d.W + iw) * d.C + c), tap.get(r * R + s));
         }
       }
       *reinterpret_cast<float4*>(y + (((long long)n * d.P + p) * d.Q + q) * d.C + c) = acc;
@@ -70,6 +91,7 @@ __global__ void __launch_bounds__(256) dw_fwd_kernel(const float* __restrict__ x
 }
 
 // dx[n,h,w,c] = sum_{r,s : (h+ph-r) % sh == 0, (w+pw-s) % sw == 0} dy[n,(h+ph-r)/sh,(w+pw-s)/sw,c] * w[c][r][s]
+template <int R>
 __global__ void __launch_bounds__(256) dw_dgrad_kernel(const float* __restrict__ dy, const float* __restrict__ w,
                                                       float* __restrict__ dx, DwShape d) {
   const int C4 = d.C >> 2, runs = (d.W + kRun - 1) / kRun;
@@ -80,24 +102,24 @@ __global__ void __launch_bounds__(256) dw_dgrad_kernel(const float* __restrict__
     const int w0 = (int)(t % runs) * kRun;
     t /= runs;
     const int h = (int)(t % d.H), n = (int)(t / d.H);
-    float4 tap[9];
-    load_taps(w, c, tap);
+    Taps<R> tap;
+    tap.load(w, c);
     const int we = min(w0 + kRun, d.W);
     for (int wx = w0; wx < we; ++wx) {
       float4 acc = make_float4(0.f, 0.f, 0.f, 0.f);
 #pragma unroll
-      for (int r = 0; r < 3; ++r) {
+      for (int r = 0; r < R; ++r) {
         const int hp = h + d.ph - r;
         if (hp < 0 || hp % d.sh != 0) continue;
         const int p = hp / d.sh;
         if (p >= d.P) continue;
 #pragma unroll
-        for (int s = 0; s < 3; ++s) {
+        for (int s = 0; s < R; ++s) {
           const int wq = wx + d.pw - s;
           if (wq < 0 || wq % d.sw != 0) continue;
           const int q = wq / d.sw;
           if (q >= d.Q) continue;
-          fma4(acc, ld4(dy + (((long long)n * d.P + p) * d.Q + q) * d.C + c), tap[r * 3 + s]);
+          fma4(acc, ld4(dy + (((long long)n * d.P + p) * d.Q + q) * d.C + c), tap.get(r * R + s));
         }
       }
       *reinterpret_cast<float4*>(dx + (((long long)n * d.H + h) * d.W + wx) * d.C + c) = acc;
@@ -106,52 +128,57 @@ __global__ void __launch_bounds__(256) dw_dgrad_kernel(const float* __restrict__
 }
 
 // dw[c][r][s] = sum_{n,p,q} dy[n,p,q,c] * x[n, p*sh - ph + r, q*sw - pw + s, c]
-// grid = (channel tiles, pixel chunks); block = TX channel quads x TY pixel lanes (TX * TY == 256).
+// grid = (channel tiles, pixel chunks, filter-row strips); block = TX channel quads x TY pixel lanes (TX * TY == 256).
+// A block accumulates RB filter rows (RB * R taps x 4 channels in registers: 3x3 and 5x5 in one strip, 7x7 in two).
 // part[chunk][tap][C]
-template <int TX>
+template <int TX, int R, int RB>
 __global__ void __launch_bounds__(256) dw_wgrad_partial_kernel(const float* __restrict__ x, const float* __restrict__ dy,
                                                               float* __restrict__ part, DwShape d, long long pix_per_chunk) {
   constexpr int TY = 256 / TX;
+  constexpr int T = R * R;
   __shared__ float4 red[TY][TX + 1];
   const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
   const int c4 = blockIdx.x * TX + tx;
   const bool live = c4 < (d.C >> 2);
   const int c = c4 << 2;
+  const int r0 = blockIdx.z * RB;                                   // first filter row of this strip
   const long long npix = (long long)d.N * d.P * d.Q;
   const long long p0 = (long long)blockIdx.y * pix_per_chunk;
   const long long p1 = min(p0 + pix_per_chunk, npix);
-  float4 acc[9];
+  float4 acc[RB * R];
 #pragma unroll
-  for (int k = 0; k < 9; ++k) acc[k] = make_float4(0.f, 0.f, 0.f, 0.f);
+  for (int k = 0; k < RB * R; ++k) acc[k] = make_float4(0.f, 0.f, 0.f, 0.f);
   if (live) {
     for (long long pix = p0 + ty; pix < p1; pix += TY) {
       const int q = (int)(pix % d.Q), p = (int)((pix / d.Q) % d.P), n = (int)(pix / ((long long)d.Q * d.P));
       const float4 g = ld4(dy + pix * d.C + c);
 #pragma unroll
-      for (int r = 0; r < 3; ++r) {
+      for (int rr = 0; rr < RB; ++rr) {
+        const int r = r0 + rr;
         const int ih = p * d.sh - d.ph + r;
-        if (ih < 0 || ih >= d.H) continue;
+        if (r >= R || ih < 0 || ih >= d.H) continue;
 #pragma unroll
-        for (int s = 0; s < 3; ++s) {
+        for (int s = 0; s < R; ++s) {
           const int iw = q * d.sw - d.pw + s;
           if (iw < 0 || iw >= d.W) continue;
-          fma4(acc[r * 3 + s], ld4(x + (((long long)n * d.H + ih) * d.W + iw) * d.C + c), g);
+          fma4(acc[rr * R + s], ld4(x + (((long long)n * d.H + ih) * d.W + iw) * d.C + c), g);
         }
       }
     }
   }
   // fixed-order reduction over the TY pixel lanes, one tap at a time
 #pragma unroll
-  for (int k = 0; k < 9; ++k) {
+  for (int k = 0; k < RB * R; ++k) {
+    const int tap = r0 * R + k;
     red[ty][tx] = acc[k];
     __syncthreads();
-    if (ty == 0 && live) {
+    if (ty == 0 && live && tap < T) {
       float4 sum = red[0][tx];
       for (int j = 1; j < TY; ++j) {
         const float4 v = red[j][tx];
         sum.x += v.x; sum.y += v.y; sum.z += v.z; sum.w += v.w;
       }
-      *reinterpret_cast<float4*>(part + ((long long)blockIdx.y * 9 + k) * d.C + c) = sum;
+      *reinterpret_cast<float4*>(part + ((long long)blockIdx.y * T + tap) * d.C + c) = sum;
     }
     __syncthreads();
   }
@@ -159,20 +186,34 @@ __global__ void __launch_bounds__(256) dw_wgrad_partial_kernel(const float* __re
 
 // dw[c][tap] += sum_chunk part[chunk][tap][c]   (chunks added in order; four independent partial sums in flight)
 __global__ void __launch_bounds__(256) dw_wgrad_final_kernel(const float* __restrict__ part, float* __restrict__ dw, int chunks,
-                                                            int C) {
+                                                            int C, int T) {
   const int i = blockIdx.x * 256 + threadIdx.x;      // i = tap * C + c
-  if (i >= 9 * C) return;
+  if (i >= T * C) return;
   float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
   int k = 0;
   for (; k + 3 < chunks; k += 4) {
-    a0 += part[(long long)(k + 0) * 9 * C + i];
-    a1 += part[(long long)(k + 1) * 9 * C + i];
-    a2 += part[(long long)(k + 2) * 9 * C + i];
-    a3 += part[(long long)(k + 3) * 9 * C + i];
+    a0 += part[(long long)(k + 0) * T * C + i];
+    a1 += part[(long long)(k + 1) * T * C + i];
+    a2 += part[(long long)(k + 2) * T * C + i];
+    a3 += part[(long long)(k + 3) * T * C + i];
   }
-  for (; k < chunks; ++k) a0 += part[(long long)k * 9 * C + i];
+  for (; k < chunks; ++k) a0 += part[(long long)k * T * C + i];
   const int tap = i / C, c = i - tap * C;
-  dw[c * 9 + tap] += (a0 + a1) + (a2 + a3);
+  dw[c * T + tap] += (a0 + a1) + (a2 + a3);
+}
+
+template <int TX, int R, int RB>
+void launch_wgrad(const float* x, const float* dy, float* scratch, const DwShape& d, long long ppc, dim3 grid, cudaStream_t s) {
+  grid.z = (R + RB - 1) / RB;
+  dw_wgrad_partial_kernel<TX, R, RB><<<grid, 256, 0, s>>>(x, dy, scratch, d, ppc);
+}
+
+template <int R, int RB>
+void launch_wgrad_tx(int TX, const float* x, const float* dy, float* scratch, const DwShape& d, long long ppc, dim3 grid,
+                     cudaStream_t s) {
+  if (TX == 32) launch_wgrad<32, R, RB>(x, dy, scratch, d, ppc, grid, s);
+  else if (TX == 16) launch_wgrad<16, R, RB>(x, dy, scratch, d, ppc, grid, s);
+  else launch_wgrad<8, R, RB>(x, dy, scratch, d, ppc, grid, s);
 }
 
 DwShape mk(const int* s) {
@@ -189,34 +230,46 @@ int grid_for(long long n) {
 
 }  // namespace
 
-// shape10 = {N, H, W, C, P, Q, stride_h, stride_w, pad_h, pad_w}; 3x3 taps; C % 4 == 0; w is [C][1][3][3]
-extern "C" int fedb_dw_conv_fwd(const float* x, const float* w, const float* bias, float* y, const int* shape10, void* stream) {
+// shape10 = {N, H, W, C, P, Q, stride_h, stride_w, pad_h, pad_w}; fs x fs taps, fs in {3, 5, 7}; C % 4 == 0;
+// w is [C][1][fs][fs]
+extern "C" int fedb_dw_conv_fwd_k(const float* x, const float* w, const float* bias, float* y, const int* shape10, int fs,
+                                  void* stream) {
   const DwShape d = mk(shape10);
   FEDB_REQUIRE(d.C % 4 == 0, "fedb_dw_conv: C must be a multiple of 4");
+  FEDB_REQUIRE(fs == 3 || fs == 5 || fs == 7, "fedb_dw_conv: 3x3, 5x5 or 7x7");
   const long long items = (long long)d.N * d.P * ((d.Q + kRun - 1) / kRun) * (d.C / 4);
-  dw_fwd_kernel<<<grid_for(items), 256, 0, (cudaStream_t)stream>>>(x, w, bias, y, d);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (fs == 3) dw_fwd_kernel<3><<<grid_for(items), 256, 0, s>>>(x, w, bias, y, d);
+  else if (fs == 5) dw_fwd_kernel<5><<<grid_for(items), 256, 0, s>>>(x, w, bias, y, d);
+  else dw_fwd_kernel<7><<<grid_for(items), 256, 0, s>>>(x, w, bias, y, d);
   FEDB_LAUNCH_OK();
   return 0;
 }
 
-extern "C" int fedb_dw_conv_dgrad(const float* dy, const float* w, float* dx, const int* shape10, void* stream) {
+extern "C" int fedb_dw_conv_dgrad_k(const float* dy, const float* w, float* dx, const int* shape10, int fs, void* stream) {
   const DwShape d = mk(shape10);
   FEDB_REQUIRE(d.C % 4 == 0, "fedb_dw_conv: C must be a multiple of 4");
+  FEDB_REQUIRE(fs == 3 || fs == 5 || fs == 7, "fedb_dw_conv: 3x3, 5x5 or 7x7");
   const long long items = (long long)d.N * d.H * ((d.W + kRun - 1) / kRun) * (d.C / 4);
-  dw_dgrad_kernel<<<grid_for(items), 256, 0, (cudaStream_t)stream>>>(dy, w, dx, d);
+  cudaStream_t s = (cudaStream_t)stream;
+  if (fs == 3) dw_dgrad_kernel<3><<<grid_for(items), 256, 0, s>>>(dy, w, dx, d);
+  else if (fs == 5) dw_dgrad_kernel<5><<<grid_for(items), 256, 0, s>>>(dy, w, dx, d);
+  else dw_dgrad_kernel<7><<<grid_for(items), 256, 0, s>>>(dy, w, dx, d);
   FEDB_LAUNCH_OK();
   return 0;
 }
 
-extern "C" long long fedb_dw_conv_wgrad_scratch(const int* shape10) {
+extern "C" long long fedb_dw_conv_wgrad_scratch_k(const int* shape10, int fs) {
   const DwShape d = mk(shape10);
-  return (long long)fedb_num_sms() * 4 * 9 * d.C;       // upper bound on chunks * 9 * C floats
+  return (long long)fedb_num_sms() * 4 * fs * fs * d.C;       // upper bound on chunks * taps * C floats
 }
 
-// dw (+)= the weight gradient; scratch: fedb_dw_conv_wgrad_scratch(shape) floats owned by the caller
-extern "C" int fedb_dw_conv_wgrad(const float* x, const float* dy, float* dw, float* scratch, const int* shape10, void* stream) {
+// dw (+)= the weight gradient; scratch: fedb_dw_conv_wgrad_scratch_k(shape, fs) floats owned by the caller
+extern "C" int fedb_dw_conv_wgrad_k(const float* x, const float* dy, float* dw, float* scratch, const int* shape10, int fs,
+                                    void* stream) {
   const DwShape d = mk(shape10);
   FEDB_REQUIRE(d.C % 4 == 0 && scratch != nullptr, "fedb_dw_conv_wgrad: C % 4 and a scratch buffer are required");
+  FEDB_REQUIRE(fs == 3 || fs == 5 || fs == 7, "fedb_dw_conv: 3x3, 5x5 or 7x7");
   const int C4 = d.C / 4;
   const int TX = C4 >= 32 ? 32 : (C4 >= 16 ? 16 : 8);
   const int ctiles = (C4 + TX - 1) / TX;
@@ -227,12 +280,24 @@ extern "C" int fedb_dw_conv_wgrad(const float* x, const float* dy, float* dw, fl
   long long ppc = (npix + chunks - 1) / chunks;
   if (ppc < 4 * TY) ppc = 4 * TY;                          // at least four pixels per thread
   chunks = (int)((npix + ppc - 1) / ppc);
-  dim3 grid(ctiles, chunks);
+  dim3 grid(ctiles, chunks, 1);
   cudaStream_t s = (cudaStream_t)stream;
-  if (TX == 32) dw_wgrad_partial_kernel<32><<<grid, 256, 0, s>>>(x, dy, scratch, d, ppc);
-  else if (TX == 16) dw_wgrad_partial_kernel<16><<<grid, 256, 0, s>>>(x, dy, scratch, d, ppc);
-  else dw_wgrad_partial_kernel<8><<<grid, 256, 0, s>>>(x, dy, scratch, d, ppc);
-  dw_wgrad_final_kernel<<<fedb_ceil_div(9 * d.C, 256), 256, 0, s>>>(scratch, dw, chunks, d.C);
+  if (fs == 3) launch_wgrad_tx<3, 3>(TX, x, dy, scratch, d, ppc, grid, s);
+  else if (fs == 5) launch_wgrad_tx<5, 5>(TX, x, dy, scratch, d, ppc, grid, s);
+  else launch_wgrad_tx<7, 4>(TX, x, dy, scratch, d, ppc, grid, s);
+  dw_wgrad_final_kernel<<<fedb_ceil_div(fs * fs * d.C, 256), 256, 0, s>>>(scratch, dw, chunks, d.C, fs * fs);
   FEDB_LAUNCH_OK();
   return 0;
+}
+
+// 3x3 forms of the four entry points above
+extern "C" int fedb_dw_conv_fwd(const float* x, const float* w, const float* bias, float* y, const int* shape10, void* stream) {
+  return fedb_dw_conv_fwd_k(x, w, bias, y, shape10, 3, stream);
+}
+extern "C" int fedb_dw_conv_dgrad(const float* dy, const float* w, float* dx, const int* shape10, void* stream) {
+  return fedb_dw_conv_dgrad_k(dy, w, dx, shape10, 3, stream);
+}
+extern "C" long long fedb_dw_conv_wgrad_scratch(const int* shape10) { return fedb_dw_conv_wgrad_scratch_k(shape10, 3); }
+extern "C" int fedb_dw_conv_wgrad(const float* x, const float* dy, float* dw, float* scratch, const int* shape10, void* stream) {
+  return fedb_dw_conv_wgrad_k(x, dy, dw, scratch, shape10, 3, stream);
 }

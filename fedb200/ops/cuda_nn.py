@@ -46,13 +46,13 @@ def _bind():
         "fedb_nn_channel_copy": [_vp, _vp, _ll, _i, _i, _i, _i, _i, _i, _i, _vp],
         "fedb_nn_linear_fwd": [_vp, _vp, _vp, _vp, _i, _i, _i, _i, _vp],
         "fedb_nn_linear_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _i, _i, _i, _vp],
-        "fedb_dw_conv_fwd": [_vp, _vp, _vp, _vp, ip, _vp],
-        "fedb_dw_conv_dgrad": [_vp, _vp, _vp, ip, _vp],
-        "fedb_dw_conv_wgrad": [_vp, _vp, _vp, _vp, ip, _vp],
+        "fedb_dw_conv_fwd_k": [_vp, _vp, _vp, _vp, ip, _i, _vp],
+        "fedb_dw_conv_dgrad_k": [_vp, _vp, _vp, ip, _i, _vp],
+        "fedb_dw_conv_wgrad_k": [_vp, _vp, _vp, _vp, ip, _i, _vp],
     }
     for name, args in sigs.items():
         _lib.bind(name, C.c_int, args)
-    _lib.bind("fedb_dw_conv_wgrad_scratch", C.c_longlong, [ip])
+    _lib.bind("fedb_dw_conv_wgrad_scratch_k", C.c_longlong, [ip, _i])
     _BOUND = True
 
 
@@ -84,9 +84,10 @@ def _conv_shape(x, w, stride, padding, groups):
 
 
 def _is_depthwise(shp) -> bool:
-    """3x3 depthwise (groups == Cin == Cout), channels a multiple of 4: the streaming kernels of csrc/depthwise.cu."""
+    """3x3 / 5x5 / 7x7 depthwise (groups == Cin == Cout), channels a multiple of 4: the streaming kernels of
+    csrc/depthwise.cu."""
     N, H, W, Cc, K, R, S, P, Q, sh, sw, ph, pw, groups = shp
-    return groups == Cc == K and R == 3 and S == 3 and Cc % 4 == 0
+    return groups == Cc == K and R == S and R in (3, 5, 7) and Cc % 4 == 0
 
 
 def _dw_shape(shp):
@@ -105,7 +106,7 @@ class _Conv2d(torch.autograd.Function):
         ctx.dw = _is_depthwise(shp)
         if ctx.dw:
             ctx.tc = False
-            _call("fedb_dw_conv_fwd", x.data_ptr(), w.data_ptr(), _p(bias), y.data_ptr(), _dw_shape(shp), current_stream())
+            _call("fedb_dw_conv_fwd_k", x.data_ptr(), w.data_ptr(), _p(bias), y.data_ptr(), _dw_shape(shp), R, current_stream())
         elif cuda_tc.conv_forward(x, w, bias, y, shp):
             ctx.tc = True
         else:
@@ -129,13 +130,13 @@ class _Conv2d(torch.autograd.Function):
         if ctx.dw:
             if ctx.needs_input_grad[0]:
                 dx = torch.empty_like(x, memory_format=CL)
-                _call("fedb_dw_conv_dgrad", dy.data_ptr(), w.data_ptr(), dx.data_ptr(), _dw_shape(shp), current_stream())
+                _call("fedb_dw_conv_dgrad_k", dy.data_ptr(), w.data_ptr(), dx.data_ptr(), _dw_shape(shp), R, current_stream())
             if ctx.needs_input_grad[1]:
                 dw = torch.zeros_like(w)
                 ds = _dw_shape(shp)
                 _bind()
-                scratch = torch.empty(int(lib().fedb_dw_conv_wgrad_scratch(ds)), dtype=torch.float32, device=x.device)
-                _call("fedb_dw_conv_wgrad", x.data_ptr(), dy.data_ptr(), dw.data_ptr(), scratch.data_ptr(), ds,
+                scratch = torch.empty(int(lib().fedb_dw_conv_wgrad_scratch_k(ds, R)), dtype=torch.float32, device=x.device)
+                _call("fedb_dw_conv_wgrad_k", x.data_ptr(), dy.data_ptr(), dw.data_ptr(), scratch.data_ptr(), ds, R,
                       current_stream(), launches=2)
                 db = dy.sum(dim=(0, 2, 3)) if ctx.has_bias else None
             return dx, dw, db, None, None, None

@@ -310,6 +310,11 @@ int fedb_dw_conv_fwd(const float* x, const float* w, const float* bias, float* y
 int fedb_dw_conv_dgrad(const float* dy, const float* w, float* dx, const int* shape10, void* stream);
 long long fedb_dw_conv_wgrad_scratch(const int* shape10);          /* floats */
 int fedb_dw_conv_wgrad(const float* x, const float* dy, float* dw, float* scratch, const int* shape10, void* stream);
+/* the same with fs x fs taps, fs in {3, 5, 7} (PNASNet's and EfficientNet's separable convolutions) */
+int fedb_dw_conv_fwd_k(const float* x, const float* w, const float* bias, float* y, const int* shape10, int fs, void* stream);
+int fedb_dw_conv_dgrad_k(const float* dy, const float* w, float* dx, const int* shape10, int fs, void* stream);
+long long fedb_dw_conv_wgrad_scratch_k(const int* shape10, int fs);
+int fedb_dw_conv_wgrad_k(const float* x, const float* dy, float* dw, float* scratch, const int* shape10, int fs, void* stream);
 
 #ifdef __cplusplus
 }

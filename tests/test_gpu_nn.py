@@ -47,6 +47,7 @@ CONVS = [  # cin, cout, k, stride, pad, groups, bias, hw
     (16, 24, 3, 1, 1, 1, True, 8), (64, 128, 1, 2, 0, 1, False, 8), (3, 6, 5, 1, 0, 1, True, 32),
     # depthwise 3x3 (csrc/depthwise.cu): 32 / 16 / 8 channel quads per block row, bias, odd maps, stride 2
     (128, 128, 3, 1, 1, 128, True, 16), (64, 64, 3, 2, 1, 64, False, 7), (36, 36, 3, 1, 1, 36, False, 11),
+    (64, 64, 5, 2, 2, 64, False, 16), (88, 88, 7, 1, 3, 88, False, 8), (132, 132, 5, 1, 2, 132, True, 9),
 ]
 
 
