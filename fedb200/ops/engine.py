@@ -165,19 +165,24 @@ class CudaEngine:
         return self._test_host[0].numel() + self._test_host[1].numel() * 8
 
     # ------------------------------------------------------------------ training pass
-    COPY_CHUNK_STEPS = 8        # batches per H2D chunk (LeNet: 3 MB ~ 60 us on PCIe 5, one step is ~50 us)
+    COPY_CHUNK_STEPS = 8        # batches per H2D chunk in steady state (LeNet: 3 MB); the first chunks are 1, 2 and 4
+                                # batches so that step 0 waits for one batch only, not for a whole chunk
 
     def _issue_steps(self, sh: dict, upload: bool = False, with_test: bool = False) -> None:
         sizes = sh["sizes"]
         offs = [0]
         for n in sizes:
             offs.append(offs[-1] + n)
-        g = self.COPY_CHUNK_STEPS
-        first = list(range(0, len(sizes), g))                        # first step of every chunk
+        first, i, g = [], 0, 1                                       # first step of every chunk: 0, 1, 3, 7, 15, 23, ...
+        while i < len(sizes):
+            first.append(i)
+            i += g
+            g = min(2 * g, self.COPY_CHUNK_STEPS)
         bounds = [offs[f] for f in first] + [offs[-1]]
+        last = first[1:] + [len(sizes)]
 
         def work(c):
-            for i in range(first[c], min(first[c] + g, len(sizes))):
+            for i in range(first[c], last[c]):
                 x, y = sh["dx"][offs[i]:offs[i + 1]], sh["dy"][offs[i]:offs[i + 1]]
                 if self.is_lenet:
                     self.plan.train_step(x, y, step_seed=i + 1)
