@@ -703,7 +703,8 @@ extern "C" int fedb_conv3x3_tf32(const float* X, const float* Wk, float* Y, cons
 // caller).  Strided convolutions read X through a tensor map with element strides.
 static int conv_wgrad_impl(const uint16_t* dY, const uint16_t* X, float* dWk, int N, int H, int W, int Cin, int Cout, int fs,
                            int stride, int pad, int splits, long long dypitch, long long xpitch, int groups, void* stream) {
-  FEDB_REQUIRE(Cin % 8 == 0 && Cout % 8 == 0, "fedb_conv_wgrad_bf16: channels must be multiples of 8 (16-byte bf16 pitch)");
+  FEDB_REQUIRE((xpitch > 0 ? xpitch : Cin) % 8 == 0 && (dypitch > 0 ? dypitch : Cout) % 8 == 0,
+               "fedb_conv_wgrad_bf16: bf16 pixel pitches must be multiples of 8 channels (16 bytes); pad with fedb_cast_bf16_pad");
   FEDB_REQUIRE((fs == 3 && pad == 1) || (fs == 1 && pad == 0), "fedb_conv_wgrad_bf16: 3x3/pad 1 or 1x1/pad 0");
   FEDB_REQUIRE(stride == 1 || stride == 2, "fedb_conv_wgrad_bf16: stride 1 or 2");
   const int P = H / stride, Q = W / stride;
@@ -842,6 +843,28 @@ extern "C" int fedb_im2col_small(const float* x, float* out_f32, uint16_t* out_b
   if (blocks > fedb_num_sms() * 16) blocks = fedb_num_sms() * 16;
   im2col_small_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(x, out_f32, (__nv_bfloat16*)out_bf16, N, H, W, C, fs, stride,
                                                                      pad, P, Q);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+
+// fp32 [rows][C] -> bf16 [rows][Cpad] with zero columns: gives activations whose channel count is not a multiple of 8 the
+// 16-byte row pitch the bf16 TMA maps of the weight-gradient GEMMs need (DenseNet's 12-channel growth, ShuffleNetV2's 116)
+__global__ void __launch_bounds__(256) cast_bf16_pad_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst,
+                                                           long long rows, int C, int Cpad) {
+  const long long total = rows * Cpad;
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+    const long long r = i / Cpad;
+    const int c = (int)(i - r * Cpad);
+    dst[i] = __float2bfloat16(c < C ? src[r * C + c] : 0.f);
+  }
+}
+
+extern "C" int fedb_cast_bf16_pad(const float* src, uint16_t* dst, long long rows, int C, int Cpad, void* stream) {
+  FEDB_REQUIRE(Cpad >= C && Cpad % 8 == 0, "fedb_cast_bf16_pad: Cpad must be a multiple of 8 and >= C");
+  long long blocks = (rows * Cpad + 255) / 256;
+  if (blocks > fedb_num_sms() * 16) blocks = fedb_num_sms() * 16;
+  if (blocks < 1) blocks = 1;
+  cast_bf16_pad_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(src, (__nv_bfloat16*)dst, rows, C, Cpad);
   FEDB_LAUNCH_OK();
   return 0;
 }

@@ -27,6 +27,7 @@ def _f(name):
             "fedb_gemm_tf32": [vp, vp, vp, vp, i, i, i, ll, ll, ll, i, i, i, vp],
             "fedb_gemm_bf16_tn": [vp, vp, vp, i, i, i, ll, ll, ll, i, i, vp],
             "fedb_cast_bf16": [vp, vp, ll, vp],
+            "fedb_cast_bf16_pad": [vp, vp, ll, i, i, vp],
             "fedb_transpose": [vp, vp, i, i, vp],
             "fedb_conv3x3_tf32": [vp, vp, vp, vp, i, i, i, i, i, i, vp],
             "fedb_pack3x3": [vp, vp, i, i, i, vp],
@@ -70,6 +71,18 @@ def cast_bf16(x: torch.Tensor) -> torch.Tensor:
     check(_f("fedb_cast_bf16")(x.data_ptr(), out.data_ptr(), x.numel(), current_stream()), "fedb_cast_bf16")
     _lib.count_launch()
     return out
+
+
+def cast_bf16_rows(x: torch.Tensor, rows: int, C: int):
+    """bf16 copy of an fp32 [rows][C] matrix (an NHWC activation flattened over pixels) and its row pitch in elements:
+    C itself when that already is a 16-byte pitch, else C rounded up to 8 with zero columns."""
+    if C % 8 == 0:
+        return cast_bf16(x), C
+    Cp = (C + 7) // 8 * 8
+    out = torch.empty(rows * Cp, dtype=torch.bfloat16, device=x.device)
+    check(_f("fedb_cast_bf16_pad")(x.data_ptr(), out.data_ptr(), rows, C, Cp, current_stream()), "fedb_cast_bf16_pad")
+    _lib.count_launch()
+    return out, Cp
 
 
 def transpose(w2d: torch.Tensor, rows: int, cols: int) -> torch.Tensor:
@@ -148,9 +161,12 @@ def conv3x3_tf32(x, wk, y, bias, N, H, W, cin, cout, relu=False):
 
 
 def _small_reduction(shp) -> bool:
-    """Cin * R * S <= 32 and ungrouped (the 3-channel stem): explicit im2col to a [pixels, 32] matrix, then a GEMM."""
+    """Cin * R * S <= 32 and ungrouped (the 3-channel stem): explicit im2col to a [pixels, 32] matrix, then a GEMM.
+    A 1x1 convolution whose input already has a 16-byte pixel pitch is a GEMM as it stands and is not routed here."""
     N, H, W, Cc, K, R, S, P, Q, sh, sw, ph, pw, groups = shp
-    return groups == 1 and R == S and sh == sw and ph == pw and Cc * R * S <= 32 and K % 4 == 0 and N * P * Q >= MIN_PIXELS
+    if R == 1 and Cc % 4 == 0:
+        return False
+    return groups == 1 and R == S and sh == sw and ph == pw and Cc * R * S <= 32 and N * P * Q >= MIN_PIXELS
 
 
 def _channel_copy(src, dst, rows, cin, cout, width, accumulate=False):
@@ -313,27 +329,29 @@ def conv_wgrad(x, dy, dw, db, shp) -> bool:
     gg = _group_geometry(shp)
     if gg is not None:
         return _grouped_wgrad(x, dy, dw, db, shp, *gg)
-    if _small_reduction(shp) and shp[4] % 64 == 0:
+    if _small_reduction(shp):
         N, H, W, Cc, K, R, S, P, Q = shp[:9]
         pix = N * P * Q
         _, xcol16 = _im2col(x, shp, False, True)
-        dy16 = cast_bf16(dy)
+        dy16, kp = cast_bf16_rows(dy, pix, K)
         dwp = torch.zeros(K * 64, dtype=torch.float32, device=x.device)
         splits = max(1, min(pix // 256, 296))
-        gemm_bf16_tn(dy16, xcol16, dwp, K, 64, pix, K, 64, 64, splits=splits, accumulate=True)   # dWp[K][64] = dY^T Xcol
+        gemm_bf16_tn(dy16, xcol16, dwp, K, 64, pix, kp, 64, 64, splits=splits, accumulate=True)  # dWp[K][64] = dY^T Xcol
         _channel_copy(dwp, dw, K, 64, Cc * R * S, Cc * R * S, accumulate=True)                     # += into OIHW
         if db is not None:
             db += dy.sum(dim=(0, 2, 3))
         return True
-    if _is_3x3(shp, shp[3], shp[4]) and shp[3] % 8 == 0 and shp[4] % 8 == 0:
+    if _is_3x3(shp, shp[3], shp[4]):
         N, H, W, Cc, K = shp[:5]
         pix = N * H * W
         tiles = ((K + 127) // 128) * ((Cc + 127) // 128) * 9
         splits = max(1, min(pix // 256, 444 // max(tiles, 1)))
         dwk = torch.zeros(K * 9 * Cc, dtype=torch.float32, device=x.device)
-        dy16, x16 = cast_bf16(dy), cast_bf16(x)      # keep both alive: two temporaries would share one allocation
-        check(_f("fedb_conv3x3_wgrad_bf16")(dy16.data_ptr(), x16.data_ptr(), dwk.data_ptr(), N, H, W, Cc, K,
-                                            splits, current_stream()), "fedb_conv3x3_wgrad_bf16")
+        # keep both alive: two temporaries would share one allocation; channel counts that are not multiples of 8 get
+        # zero columns so that the bf16 rows keep a 16-byte pitch
+        (dy16, kp), (x16, cp) = cast_bf16_rows(dy, pix, K), cast_bf16_rows(x, pix, Cc)
+        check(_f("fedb_conv_wgrad_bf16_g")(dy16.data_ptr(), x16.data_ptr(), dwk.data_ptr(), N, H, W, Cc, K, 3, 1, 1,
+                                           splits, kp, cp, current_stream()), "fedb_conv_wgrad_bf16_g")
         _lib.count_launch()
         check(_f("fedb_pack3x3")(dwk.data_ptr(), dw.data_ptr(), K, Cc, 2, current_stream()), "fedb_pack3x3")   # += into OIHW
         _lib.count_launch()
@@ -341,16 +359,16 @@ def conv_wgrad(x, dy, dw, db, shp) -> bool:
             db += dy.sum(dim=(0, 2, 3))
         return True
     st = _strided(shp)
-    if st is not None and shp[3] % 8 == 0 and shp[4] % 8 == 0:
+    if st is not None:
         N, H, W, Cc, K = shp[:5]
         fs, stride, pad = st
         taps, pix = fs * fs, N * shp[7] * shp[8]
         tiles = ((K + 127) // 128) * ((Cc + 127) // 128) * taps
         splits = max(1, min(pix // 256, 444 // max(tiles, 1)))
-        dy16, x16 = cast_bf16(dy), cast_bf16(x)
+        (dy16, kp), (x16, cp) = cast_bf16_rows(dy, pix, K), cast_bf16_rows(x, N * H * W, Cc)
         dwk = torch.zeros(K * taps * Cc, dtype=torch.float32, device=x.device) if taps > 1 else dw
-        check(_f("fedb_conv_wgrad_bf16")(dy16.data_ptr(), x16.data_ptr(), dwk.data_ptr(), N, H, W, Cc, K, fs, stride, pad,
-                                         splits, current_stream()), "fedb_conv_wgrad_bf16")
+        check(_f("fedb_conv_wgrad_bf16_g")(dy16.data_ptr(), x16.data_ptr(), dwk.data_ptr(), N, H, W, Cc, K, fs, stride, pad,
+                                           splits, kp, cp, current_stream()), "fedb_conv_wgrad_bf16_g")
         _lib.count_launch()
         if taps > 1:
             check(_f("fedb_pack_filter")(dwk.data_ptr(), dw.data_ptr(), K, Cc, 2, taps, current_stream()), "fedb_pack_filter")
@@ -358,7 +376,7 @@ def conv_wgrad(x, dy, dw, db, shp) -> bool:
         if db is not None:
             db += dy.sum(dim=(0, 2, 3))
         return True
-    if not _is_pointwise(shp, 8, 8):
+    if not _is_pointwise(shp, 1, 1):
         return False
     N, H, W, Cc, K = shp[:5]
     pix = N * H * W
@@ -366,7 +384,8 @@ def conv_wgrad(x, dy, dw, db, shp) -> bool:
     # (few output tiles) still fill the machine; partial tiles are reduced with red.global.add
     tiles = ((K + 127) // 128) * ((Cc + 127) // 128)
     splits = max(1, min(pix // 256, 296 // max(tiles, 1)))
-    gemm_bf16_tn(cast_bf16(dy), cast_bf16(x), dw, K, Cc, pix, K, Cc, Cc, splits=splits, accumulate=True)
+    (dy16, kp), (x16, cp) = cast_bf16_rows(dy, pix, K), cast_bf16_rows(x, pix, Cc)
+    gemm_bf16_tn(dy16, x16, dw, K, Cc, pix, kp, cp, Cc, splits=splits, accumulate=True)
     if db is not None:
         db += dy.sum(dim=(0, 2, 3))       # bias on a pointwise conv that reaches a GEMM tile: rare in the zoo
     return True

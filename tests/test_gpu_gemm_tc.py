@@ -69,8 +69,29 @@ def test_pointwise_conv_uses_tensor_cores_and_matches(G):
     torch.testing.assert_close(wb.grad.cpu(), wa.grad, rtol=1e-2, atol=0.4)
 
 
+@pytest.mark.parametrize("B,C,K,HW", [(8, 116, 116, 16), (4, 24, 144, 32), (16, 12, 36, 8), (4, 16, 96, 32)])
+def test_pointwise_conv_any_16_byte_pitched_channel_count(G, B, C, K, HW):
+    """1x1 convolutions whose channel counts are multiples of 4 but not of 8 / 32 (ShuffleNetV2's 116, DenseNet's 12): K / N tails
+    of the GEMM tiles come from TMA zero fill, the weight gradient reads bf16 rows zero-padded to a 16-byte pitch."""
+    import torch.nn.functional as TF
+    from fedb200.ops import functional as F
+    torch.manual_seed(9)
+    x = torch.randn(B, C, HW, HW)
+    w = torch.randn(K, C, 1, 1) * 0.1
+    xa, wa = x.clone().requires_grad_(True), w.clone().requires_grad_(True)
+    xb, wb = x.clone().to(DEV).requires_grad_(True), w.clone().to(DEV).requires_grad_(True)
+    ya = TF.conv2d(xa, wa)
+    yb = F.conv2d(xb, wb)
+    torch.testing.assert_close(yb.cpu(), ya.detach(), rtol=3e-3, atol=3e-3 * float(ya.detach().abs().max()))
+    g = torch.randn_like(ya)
+    ya.backward(g), yb.backward(g.to(DEV))
+    torch.testing.assert_close(xb.grad.cpu(), xa.grad, rtol=3e-3, atol=3e-3 * float(xa.grad.abs().max()))
+    torch.testing.assert_close(wb.grad.cpu(), wa.grad, rtol=1e-2, atol=1e-2 * float(wa.grad.abs().max()))
+
+
 @pytest.mark.parametrize("B,C,K,HW", [(4, 64, 64, 32), (8, 64, 128, 16), (16, 128, 256, 8), (32, 256, 512, 4), (64, 512, 512, 2),
-                                      (5, 32, 32, 8), (4, 48, 24, 16), (8, 96, 208, 8), (4, 16, 40, 32), (8, 128, 32, 16)])
+                                      (5, 32, 32, 8), (4, 48, 24, 16), (8, 96, 208, 8), (4, 16, 40, 32), (8, 128, 32, 16),
+                                      (4, 48, 12, 32), (8, 116, 116, 8), (4, 60, 20, 16)])     # wgrad through zero-padded bf16 rows
 def test_conv3x3_implicit_gemm_fwd_and_dgrad(G, B, C, K, HW):
     """3x3 / stride 1 / pad 1 convolution as an implicit GEMM: every filter tap is a shifted 4-D TMA box of the NHWC
     activation (the zero padding comes from TMA's out-of-bounds fill)."""
@@ -116,10 +137,11 @@ def test_strided_conv_on_tensor_cores(G, B, C, K, HW, fs):
     torch.testing.assert_close(wb.grad.cpu(), wa.grad, rtol=1e-2, atol=1e-2 * float(wa.grad.abs().max()))
 
 
-@pytest.mark.parametrize("B,K,HW,bias", [(8, 64, 32, False), (4, 32, 32, True), (16, 128, 16, False)])
+@pytest.mark.parametrize("B,K,HW,bias", [(8, 64, 32, False), (4, 32, 32, True), (16, 128, 16, False), (4, 44, 32, False),
+                                         (8, 24, 16, False)])
 def test_stem_conv_through_im2col_gemm(G, B, K, HW, bias):
     """3-channel stems: Cin*9 = 27 is padded to one 32-wide K tile by an explicit im2col, then the GEMM kernel runs the
-    forward (TF32) and, when Cout is a multiple of 64, the weight gradient (bf16, split over pixels)."""
+    forward (TF32) and the weight gradient (bf16 with dY rows zero-padded to a 16-byte pitch, split over pixels)."""
     import torch.nn.functional as TF
     from fedb200.ops import functional as F
     torch.manual_seed(6)
