@@ -165,6 +165,110 @@ __global__ void __launch_bounds__(256) bn_partial_kernel(const float* __restrict
   }
 }
 
+// 128-bit forms of the four streaming BN kernels (C % 4 == 0, which is every zoo layer): a thread owns four consecutive
+// channels, a block is TX channel quads x 256/TX row lanes, every access is a whole 16-byte word and two rows are in
+// flight per thread.  BatchNorm is pure memory traffic (8 passes over the activation per training step), so this is
+// what decides its share of a zoo step.
+__device__ __forceinline__ float4 ldf4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+
+template <int TX, bool kBwd>
+__global__ void __launch_bounds__(256) bn_partial4_kernel(const float* __restrict__ x, const float* __restrict__ dy,
+                                                         const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                         const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                         float* __restrict__ scratch, long long rows, int C, int act,
+                                                         long long rows_per_chunk) {
+  constexpr int TY = 256 / TX;
+  __shared__ float4 s_a[TY][TX], s_b[TY][TX];
+  const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
+  const int c = (blockIdx.x * TX + tx) * 4;
+  const bool live = c < C;
+  const long long r0 = (long long)blockIdx.y * rows_per_chunk;
+  const long long r1 = r0 + rows_per_chunk < rows ? r0 + rows_per_chunk : rows;
+  float4 sa = make_float4(0.f, 0.f, 0.f, 0.f), sb = sa;
+  if (live) {
+    float4 m = sa, is = sa, g = sa, b = sa;
+    if (kBwd) { m = ldf4(mean + c); is = ldf4(invstd + c); g = ldf4(gamma + c); b = ldf4(beta + c); }
+    auto add = [&](const float4& xv, const float4& dv) {
+      if (!kBwd) {
+        sa.x += xv.x; sa.y += xv.y; sa.z += xv.z; sa.w += xv.w;
+        sb.x = fmaf(xv.x, xv.x, sb.x); sb.y = fmaf(xv.y, xv.y, sb.y); sb.z = fmaf(xv.z, xv.z, sb.z); sb.w = fmaf(xv.w, xv.w, sb.w);
+      } else {
+        const float xh[4] = {(xv.x - m.x) * is.x, (xv.y - m.y) * is.y, (xv.z - m.z) * is.z, (xv.w - m.w) * is.w};
+        float d[4] = {dv.x, dv.y, dv.z, dv.w};
+        if (act) {
+          d[0] *= act_bwd(fmaf(xh[0], g.x, b.x), act); d[1] *= act_bwd(fmaf(xh[1], g.y, b.y), act);
+          d[2] *= act_bwd(fmaf(xh[2], g.z, b.z), act); d[3] *= act_bwd(fmaf(xh[3], g.w, b.w), act);
+        }
+        sa.x += d[0]; sa.y += d[1]; sa.z += d[2]; sa.w += d[3];
+        sb.x = fmaf(d[0], xh[0], sb.x); sb.y = fmaf(d[1], xh[1], sb.y); sb.z = fmaf(d[2], xh[2], sb.z); sb.w = fmaf(d[3], xh[3], sb.w);
+      }
+    };
+    long long r = r0 + ty;
+    for (; r + TY < r1; r += 2 * TY) {                      // two rows in flight
+      const float4 x0 = ldf4(x + r * C + c), x1 = ldf4(x + (r + TY) * C + c);
+      float4 d0 = sa, d1 = sa;
+      if (kBwd) { d0 = ldf4(dy + r * C + c); d1 = ldf4(dy + (r + TY) * C + c); }
+      add(x0, d0);
+      add(x1, d1);
+    }
+    if (r < r1) add(ldf4(x + r * C + c), kBwd ? ldf4(dy + r * C + c) : sa);
+  }
+  s_a[ty][tx] = sa;
+  s_b[ty][tx] = sb;
+  __syncthreads();
+  if (ty == 0 && live) {
+    for (int j = 1; j < TY; ++j) {
+      const float4 a = s_a[j][tx], b2 = s_b[j][tx];
+      sa.x += a.x; sa.y += a.y; sa.z += a.z; sa.w += a.w;
+      sb.x += b2.x; sb.y += b2.y; sb.z += b2.z; sb.w += b2.w;
+    }
+    *reinterpret_cast<float4*>(scratch + ((long long)blockIdx.y * 2 + 0) * C + c) = sa;
+    *reinterpret_cast<float4*>(scratch + ((long long)blockIdx.y * 2 + 1) * C + c) = sb;
+  }
+}
+
+__global__ void __launch_bounds__(256) bn_apply4_kernel(const float* __restrict__ x, float* __restrict__ y,
+                                                       const float* __restrict__ mean, const float* __restrict__ invstd,
+                                                       const float* __restrict__ gamma, const float* __restrict__ beta,
+                                                       long long total4, int C, int act) {
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total4; i += (long long)gridDim.x * 256) {
+    const int c = (int)((i * 4) % C);
+    const float4 v = ldf4(x + i * 4), m = ldf4(mean + c), is = ldf4(invstd + c), g = ldf4(gamma + c), b = ldf4(beta + c);
+    float4 o;
+    o.x = act_fwd(fmaf((v.x - m.x) * is.x, g.x, b.x), act);
+    o.y = act_fwd(fmaf((v.y - m.y) * is.y, g.y, b.y), act);
+    o.z = act_fwd(fmaf((v.z - m.z) * is.z, g.z, b.z), act);
+    o.w = act_fwd(fmaf((v.w - m.w) * is.w, g.w, b.w), act);
+    *reinterpret_cast<float4*>(y + i * 4) = o;
+  }
+}
+
+__global__ void __launch_bounds__(256) bn_bwd_apply4_kernel(const float* __restrict__ x, const float* __restrict__ dy,
+                                                           float* __restrict__ dx, const float* __restrict__ mean,
+                                                           const float* __restrict__ invstd, const float* __restrict__ gamma,
+                                                           const float* __restrict__ beta, const float* __restrict__ dgamma,
+                                                           const float* __restrict__ dbeta, long long total4, int C,
+                                                           float inv_rows, int act, int training) {
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total4; i += (long long)gridDim.x * 256) {
+    const int c = (int)((i * 4) % C);
+    const float4 xv = ldf4(x + i * 4), dv = ldf4(dy + i * 4);
+    const float4 m = ldf4(mean + c), is = ldf4(invstd + c), g = ldf4(gamma + c), b = ldf4(beta + c);
+    const float4 dg = ldf4(dgamma + c), db = ldf4(dbeta + c);
+    const float xs[4] = {xv.x, xv.y, xv.z, xv.w}, ds[4] = {dv.x, dv.y, dv.z, dv.w};
+    const float ms[4] = {m.x, m.y, m.z, m.w}, iss[4] = {is.x, is.y, is.z, is.w}, gs[4] = {g.x, g.y, g.z, g.w};
+    const float bs[4] = {b.x, b.y, b.z, b.w}, dgs[4] = {dg.x, dg.y, dg.z, dg.w}, dbs[4] = {db.x, db.y, db.z, db.w};
+    float o[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) {
+      const float xh = (xs[k] - ms[k]) * iss[k];
+      float d = ds[k];
+      if (act) d *= act_bwd(fmaf(xh, gs[k], bs[k]), act);
+      o[k] = training ? gs[k] * iss[k] * (d - dbs[k] * inv_rows - xh * dgs[k] * inv_rows) : gs[k] * iss[k] * d;
+    }
+    *reinterpret_cast<float4*>(dx + i * 4) = make_float4(o[0], o[1], o[2], o[3]);
+  }
+}
+
 // Second pass of the chunked reductions: block = 32 channels x 8 groups of chunks.  Group w adds chunks w, w+8, ... (four
 // independent loads in flight), the eight group sums are combined in group order: the result does not depend on
 // scheduling.  Returns the two per-channel sums to the threads of group 0.
@@ -508,8 +612,21 @@ extern "C" int fedb_nn_conv_wgrad(const float* x, const float* dy, float* dw, fl
 }
 
 // how many row chunks for a [rows x C] reduction so that ~4 blocks land on every SM (bounded by the scratch size)
+static int bn_tx(int C) { const int c4 = C / 4; return c4 >= 32 ? 32 : (c4 >= 16 ? 16 : 8); }
+
+template <bool kBwd>
+static void bn_partial4(const float* x, const float* dy, const float* mean, const float* invstd, const float* gamma,
+                        const float* beta, float* scratch, long long rows, int C, int act, long long rpc, int chunks,
+                        cudaStream_t s) {
+  const int tx = bn_tx(C);
+  dim3 grid(fedb_ceil_div(C / 4, tx), chunks);
+  if (tx == 32) bn_partial4_kernel<32, kBwd><<<grid, 256, 0, s>>>(x, dy, mean, invstd, gamma, beta, scratch, rows, C, act, rpc);
+  else if (tx == 16) bn_partial4_kernel<16, kBwd><<<grid, 256, 0, s>>>(x, dy, mean, invstd, gamma, beta, scratch, rows, C, act, rpc);
+  else bn_partial4_kernel<8, kBwd><<<grid, 256, 0, s>>>(x, dy, mean, invstd, gamma, beta, scratch, rows, C, act, rpc);
+}
+
 static int bn_chunks(long long rows, int C, long long scratch_floats, long long* rows_per_chunk) {
-  const int cgroups = fedb_ceil_div(C, 32);
+  const int cgroups = C % 4 == 0 ? fedb_ceil_div(C / 4, bn_tx(C)) : fedb_ceil_div(C, 32);
   long long want = (long long)fedb_num_sms() * 4 / cgroups;
   if (want < 1) want = 1;
   const long long by_rows = (rows + 63) / 64;                  // at least 64 rows per chunk
@@ -528,11 +645,13 @@ extern "C" int fedb_nn_bn_fwd(const float* x, float* y, float* mean, float* invs
     FEDB_REQUIRE(scratch != nullptr && scratch_floats >= 2LL * C, "fedb_nn_bn_fwd: scratch of at least 2*C floats required");
     long long rpc = 0;
     const int chunks = bn_chunks(rows, C, scratch_floats, &rpc);
-    bn_partial_kernel<<<dim3(fedb_ceil_div(C, 32), chunks), 256, 0, S_>>>(x, scratch, rows, C, rpc);
+    if (C % 4 == 0) bn_partial4<false>(x, nullptr, nullptr, nullptr, nullptr, nullptr, scratch, rows, C, 0, rpc, chunks, S_);
+    else bn_partial_kernel<<<dim3(fedb_ceil_div(C, 32), chunks), 256, 0, S_>>>(x, scratch, rows, C, rpc);
     bn_finalize_kernel<<<fedb_ceil_div(C, 32), 256, 0, S_>>>(scratch, chunks, mean, invstd, run_mean, run_var, rows, C, eps, momentum);
   }
   else bn_eval_prep_kernel<<<fedb_ceil_div(C, 128), 128, 0, S_>>>(run_mean, run_var, mean, invstd, C, eps);
-  bn_apply_kernel<<<grid_for(rows * C), 256, 0, S_>>>(x, y, mean, invstd, gamma, beta, rows * C, C, act);
+  if (C % 4 == 0) bn_apply4_kernel<<<grid_for(rows * C / 4), 256, 0, S_>>>(x, y, mean, invstd, gamma, beta, rows * C / 4, C, act);
+  else bn_apply_kernel<<<grid_for(rows * C), 256, 0, S_>>>(x, y, mean, invstd, gamma, beta, rows * C, C, act);
   FEDB_LAUNCH_OK();
   return 0;
 }
@@ -542,10 +661,15 @@ extern "C" int fedb_nn_bn_bwd(const float* x, const float* dy, float* dx, const 
   FEDB_REQUIRE(scratch != nullptr && scratch_floats >= 2LL * C, "fedb_nn_bn_bwd: scratch of at least 2*C floats required");
   long long rpc = 0;
   const int chunks = bn_chunks(rows, C, scratch_floats, &rpc);
-  bn_bwd_partial_kernel<<<dim3(fedb_ceil_div(C, 32), chunks), 256, 0, S_>>>(x, dy, mean, invstd, gamma, beta, scratch, rows, C, act, rpc);
+  if (C % 4 == 0) bn_partial4<true>(x, dy, mean, invstd, gamma, beta, scratch, rows, C, act, rpc, chunks, S_);
+  else bn_bwd_partial_kernel<<<dim3(fedb_ceil_div(C, 32), chunks), 256, 0, S_>>>(x, dy, mean, invstd, gamma, beta, scratch, rows, C, act, rpc);
   bn_bwd_finalize_kernel<<<fedb_ceil_div(C, 32), 256, 0, S_>>>(scratch, chunks, dgamma, dbeta, C);
-  bn_bwd_apply_kernel<<<grid_for(rows * C), 256, 0, S_>>>(x, dy, dx, mean, invstd, gamma, beta, dgamma, dbeta, rows * C, C,
-                                                         1.f / (float)rows, act, training);
+  if (C % 4 == 0)
+    bn_bwd_apply4_kernel<<<grid_for(rows * C / 4), 256, 0, S_>>>(x, dy, dx, mean, invstd, gamma, beta, dgamma, dbeta, rows * C / 4,
+                                                                C, 1.f / (float)rows, act, training);
+  else
+    bn_bwd_apply_kernel<<<grid_for(rows * C), 256, 0, S_>>>(x, dy, dx, mean, invstd, gamma, beta, dgamma, dbeta, rows * C, C,
+                                                           1.f / (float)rows, act, training);
   FEDB_LAUNCH_OK();
   return 0;
 }
