@@ -409,6 +409,29 @@ __global__ void __launch_bounds__(256) add_act_kernel(const float* __restrict__ 
   for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n; i += (long long)gridDim.x * 256)
     y[i] = act_fwd(a[i] + b[i], act);
 }
+// 128-bit forms (n % 4 == 0, 16-byte aligned pointers): the elementwise ops are pure memory traffic
+__global__ void __launch_bounds__(256) act_fwd4_kernel(const float4* __restrict__ x, float4* __restrict__ y, long long n4, int act) {
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n4; i += (long long)gridDim.x * 256) {
+    const float4 v = x[i];
+    y[i] = make_float4(act_fwd(v.x, act), act_fwd(v.y, act), act_fwd(v.z, act), act_fwd(v.w, act));
+  }
+}
+__global__ void __launch_bounds__(256) act_bwd4_kernel(const float4* __restrict__ x, const float4* __restrict__ dy,
+                                                      float4* __restrict__ dx, long long n4, int act) {
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n4; i += (long long)gridDim.x * 256) {
+    const float4 v = x[i], d = dy[i];
+    dx[i] = make_float4(d.x * act_bwd(v.x, act), d.y * act_bwd(v.y, act), d.z * act_bwd(v.z, act), d.w * act_bwd(v.w, act));
+  }
+}
+__global__ void __launch_bounds__(256) add_act4_kernel(const float4* __restrict__ a, const float4* __restrict__ b,
+                                                      float4* __restrict__ y, long long n4, int act) {
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n4; i += (long long)gridDim.x * 256) {
+    const float4 u = a[i], v = b[i];
+    y[i] = make_float4(act_fwd(u.x + v.x, act), act_fwd(u.y + v.y, act), act_fwd(u.z + v.z, act), act_fwd(u.w + v.w, act));
+  }
+}
+__device__ __host__ inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
+
 // y[n,hw,c] = x[n,hw,c] * s[n,c] (mode 0) ; per-sample scalar s[n] (mode 1: drop-connect / dropout masks)
 __global__ void __launch_bounds__(256) scale_kernel(const float* __restrict__ x, const float* __restrict__ s,
                                                    float* __restrict__ y, long long total, long long per_sample, int C, int mode) {
@@ -520,6 +543,26 @@ __global__ void __launch_bounds__(256) channel_copy_kernel(const float* __restri
     const float v = in[row * Cin + src_off + sj];
     float* o = out + row * Cout + dst_off + j;
     *o = accumulate ? *o + v : v;
+  }
+}
+
+// the same for channel windows that are whole 16-byte words on both sides (no shuffle): cat / slice of DenseNet, GoogLeNet,
+// DPN, DLA move activations at memory speed
+__global__ void __launch_bounds__(256) channel_copy4_kernel(const float* __restrict__ in, float* __restrict__ out, long long rows,
+                                                           int Cin, int Cout, int src_off, int dst_off, int width4,
+                                                           int accumulate) {
+  const long long total = rows * width4;
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+    const int j = (int)(i % width4);
+    const long long row = i / width4;
+    const float4 v = *reinterpret_cast<const float4*>(in + row * Cin + src_off + 4 * j);
+    float4* o = reinterpret_cast<float4*>(out + row * Cout + dst_off + 4 * j);
+    if (accumulate) {
+      const float4 w = *o;
+      *o = make_float4(w.x + v.x, w.y + v.y, w.z + v.z, w.w + v.w);
+    } else {
+      *o = v;
+    }
   }
 }
 
@@ -675,17 +718,26 @@ extern "C" int fedb_nn_bn_bwd(const float* x, const float* dy, float* dx, const 
 }
 
 extern "C" int fedb_nn_act_fwd(const float* x, float* y, long long n, int act, void* stream) {
-  act_fwd_kernel<<<grid_for(n), 256, 0, S_>>>(x, y, n, act);
+  if (n % 4 == 0 && aligned16(x) && aligned16(y))
+    act_fwd4_kernel<<<grid_for(n / 4), 256, 0, S_>>>((const float4*)x, (float4*)y, n / 4, act);
+  else
+    act_fwd_kernel<<<grid_for(n), 256, 0, S_>>>(x, y, n, act);
   FEDB_LAUNCH_OK();
   return 0;
 }
 extern "C" int fedb_nn_act_bwd(const float* x, const float* dy, float* dx, long long n, int act, void* stream) {
-  act_bwd_kernel<<<grid_for(n), 256, 0, S_>>>(x, dy, dx, n, act);
+  if (n % 4 == 0 && aligned16(x) && aligned16(dy) && aligned16(dx))
+    act_bwd4_kernel<<<grid_for(n / 4), 256, 0, S_>>>((const float4*)x, (const float4*)dy, (float4*)dx, n / 4, act);
+  else
+    act_bwd_kernel<<<grid_for(n), 256, 0, S_>>>(x, dy, dx, n, act);
   FEDB_LAUNCH_OK();
   return 0;
 }
 extern "C" int fedb_nn_add_act(const float* a, const float* b, float* y, long long n, int act, void* stream) {
-  add_act_kernel<<<grid_for(n), 256, 0, S_>>>(a, b, y, n, act);
+  if (n % 4 == 0 && aligned16(a) && aligned16(b) && aligned16(y))
+    add_act4_kernel<<<grid_for(n / 4), 256, 0, S_>>>((const float4*)a, (const float4*)b, (float4*)y, n / 4, act);
+  else
+    add_act_kernel<<<grid_for(n), 256, 0, S_>>>(a, b, y, n, act);
   FEDB_LAUNCH_OK();
   return 0;
 }
@@ -725,8 +777,12 @@ extern "C" int fedb_nn_pool_bwd(const float* dy, const int* arg, float* dx, cons
 }
 extern "C" int fedb_nn_channel_copy(const float* in, float* out, long long rows, int Cin, int Cout, int src_off, int dst_off,
                                     int width, int shuffle_groups, int accumulate, void* stream) {
-  channel_copy_kernel<<<grid_for(rows * width), 256, 0, S_>>>(in, out, rows, Cin, Cout, src_off, dst_off, width,
-                                                             shuffle_groups, accumulate);
+  if (shuffle_groups <= 1 && ((Cin | Cout | src_off | dst_off | width) & 3) == 0 && aligned16(in) && aligned16(out))
+    channel_copy4_kernel<<<grid_for(rows * (width / 4)), 256, 0, S_>>>(in, out, rows, Cin, Cout, src_off, dst_off, width / 4,
+                                                                      accumulate);
+  else
+    channel_copy_kernel<<<grid_for(rows * width), 256, 0, S_>>>(in, out, rows, Cin, Cout, src_off, dst_off, width,
+                                                               shuffle_groups, accumulate);
   FEDB_LAUNCH_OK();
   return 0;
 }
