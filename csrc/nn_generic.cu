@@ -526,6 +526,85 @@ __global__ void __launch_bounds__(256) pool_bwd_kernel(const float* __restrict__
   }
 }
 
+// 128-bit forms of the two pooling kernels (C % 4 == 0): four channels per thread
+__global__ void __launch_bounds__(256) pool_fwd4_kernel(const float* __restrict__ x, float* __restrict__ y,
+                                                       int* __restrict__ arg, PoolShape s, int is_max) {
+  const int C4 = s.C >> 2;
+  const long long total = (long long)s.N * s.P * s.Q * C4;
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+    const int ch = (int)(i % C4) << 2;
+    long long t = i / C4;
+    const int q = (int)(t % s.Q); t /= s.Q;
+    const int p = (int)(t % s.P);
+    const int n = (int)(t / s.P);
+    float best[4] = {-INFINITY, -INFINITY, -INFINITY, -INFINITY}, sum[4] = {0.f, 0.f, 0.f, 0.f};
+    int besti[4] = {-1, -1, -1, -1};
+    for (int r = 0; r < s.kh; ++r) {
+      const int ih = p * s.sh - s.ph + r;
+      if (ih < 0 || ih >= s.H) continue;
+      for (int c = 0; c < s.kw; ++c) {
+        const int iw = q * s.sw - s.pw + c;
+        if (iw < 0 || iw >= s.W) continue;
+        const float4 v4 = *reinterpret_cast<const float4*>(x + (((long long)n * s.H + ih) * s.W + iw) * s.C + ch);
+        const float v[4] = {v4.x, v4.y, v4.z, v4.w};
+#pragma unroll
+        for (int k = 0; k < 4; ++k) {
+          sum[k] += v[k];
+          if (v[k] > best[k]) { best[k] = v[k]; besti[k] = ih * s.W + iw; }
+        }
+      }
+    }
+    const long long o = i * 4;
+    if (is_max) {
+      *reinterpret_cast<float4*>(y + o) = make_float4(best[0], best[1], best[2], best[3]);
+      if (arg) *reinterpret_cast<int4*>(arg + o) = make_int4(besti[0], besti[1], besti[2], besti[3]);
+    } else {
+      const float inv = 1.f / (float)(s.kh * s.kw);          // count_include_pad=True, torch's default
+      *reinterpret_cast<float4*>(y + o) = make_float4(sum[0] * inv, sum[1] * inv, sum[2] * inv, sum[3] * inv);
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) pool_bwd4_kernel(const float* __restrict__ dy, const int* __restrict__ arg,
+                                                       float* __restrict__ dx, PoolShape s, int is_max) {
+  const int C4 = s.C >> 2;
+  const long long total = (long long)s.N * s.H * s.W * C4;
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
+    const int ch = (int)(i % C4) << 2;
+    long long t = i / C4;
+    const int w = (int)(t % s.W); t /= s.W;
+    const int h = (int)(t % s.H);
+    const int n = (int)(t / s.H);
+    float acc[4] = {0.f, 0.f, 0.f, 0.f};
+    const int me = h * s.W + w;
+    for (int r = 0; r < s.kh; ++r) {
+      const int pp = h + s.ph - r;
+      if (pp < 0 || pp % s.sh) continue;
+      const int p = pp / s.sh;
+      if (p >= s.P) continue;
+      for (int c = 0; c < s.kw; ++c) {
+        const int qq = w + s.pw - c;
+        if (qq < 0 || qq % s.sw) continue;
+        const int q = qq / s.sw;
+        if (q >= s.Q) continue;
+        const long long o = (((long long)n * s.P + p) * s.Q + q) * s.C + ch;
+        const float4 d = *reinterpret_cast<const float4*>(dy + o);
+        if (is_max) {
+          const int4 a = *reinterpret_cast<const int4*>(arg + o);
+          if (a.x == me) acc[0] += d.x;
+          if (a.y == me) acc[1] += d.y;
+          if (a.z == me) acc[2] += d.z;
+          if (a.w == me) acc[3] += d.w;
+        } else {
+          const float inv = 1.f / (float)(s.kh * s.kw);
+          acc[0] += d.x * inv; acc[1] += d.y * inv; acc[2] += d.z * inv; acc[3] += d.w * inv;
+        }
+      }
+    }
+    *reinterpret_cast<float4*>(dx + i * 4) = make_float4(acc[0], acc[1], acc[2], acc[3]);
+  }
+}
+
 // ------------------------------------------------------------------------------------ channel moves (K11)
 // out[row, dst_off + j] = in[row, src_off + map(j)] for j < width; map = identity or shuffle
 __global__ void __launch_bounds__(256) channel_copy_kernel(const float* __restrict__ in, float* __restrict__ out,
@@ -762,7 +841,10 @@ extern "C" int fedb_nn_pool_fwd(const float* x, float* y, int* arg, const int* s
   const int* d = shape12;
   s.N = d[0]; s.H = d[1]; s.W = d[2]; s.C = d[3]; s.P = d[4]; s.Q = d[5]; s.kh = d[6]; s.kw = d[7]; s.sh = d[8]; s.sw = d[9];
   s.ph = d[10]; s.pw = d[11];
-  pool_fwd_kernel<<<grid_for((long long)s.N * s.P * s.Q * s.C), 256, 0, S_>>>(x, y, arg, s, is_max);
+  if (s.C % 4 == 0 && aligned16(x) && aligned16(y) && aligned16(arg))
+    pool_fwd4_kernel<<<grid_for((long long)s.N * s.P * s.Q * (s.C / 4)), 256, 0, S_>>>(x, y, arg, s, is_max);
+  else
+    pool_fwd_kernel<<<grid_for((long long)s.N * s.P * s.Q * s.C), 256, 0, S_>>>(x, y, arg, s, is_max);
   FEDB_LAUNCH_OK();
   return 0;
 }
@@ -771,7 +853,10 @@ extern "C" int fedb_nn_pool_bwd(const float* dy, const int* arg, float* dx, cons
   const int* d = shape12;
   s.N = d[0]; s.H = d[1]; s.W = d[2]; s.C = d[3]; s.P = d[4]; s.Q = d[5]; s.kh = d[6]; s.kw = d[7]; s.sh = d[8]; s.sw = d[9];
   s.ph = d[10]; s.pw = d[11];
-  pool_bwd_kernel<<<grid_for((long long)s.N * s.H * s.W * s.C), 256, 0, S_>>>(dy, arg, dx, s, is_max);
+  if (s.C % 4 == 0 && aligned16(dy) && aligned16(dx) && aligned16(arg))
+    pool_bwd4_kernel<<<grid_for((long long)s.N * s.H * s.W * (s.C / 4)), 256, 0, S_>>>(dy, arg, dx, s, is_max);
+  else
+    pool_bwd_kernel<<<grid_for((long long)s.N * s.H * s.W * s.C), 256, 0, S_>>>(dy, arg, dx, s, is_max);
   FEDB_LAUNCH_OK();
   return 0;
 }
