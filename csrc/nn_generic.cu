@@ -440,17 +440,29 @@ __global__ void __launch_bounds__(256) scale_kernel(const float* __restrict__ x,
     y[i] = x[i] * (mode == 0 ? s[n * C + (i % C)] : s[n]);
   }
 }
-// ds[n,c] = sum_hw dy*x   (SE excitation backward wrt the gate)
-__global__ void __launch_bounds__(256) scale_bwd_gate_kernel(const float* __restrict__ x, const float* __restrict__ dy,
-                                                            float* __restrict__ ds, int HW, int C, int N) {
-  const int i = blockIdx.x * 256 + threadIdx.x;
-  if (i >= N * C) return;
-  const int n = i / C, ch = i % C;
-  const float* xp = x + (long long)n * HW * C + ch;
-  const float* dp = dy + (long long)n * HW * C + ch;
+// Per-(sample, channel) reductions over the HW positions of an NHWC map: block = 32 channels x 8 position lanes of one
+// sample (grid = (N, C/32)), lanes stride over the positions, the eight lane sums are added in lane order.
+//   kGate: ds[n,c] = sum_hw dy*x   (SE excitation backward wrt the gate)
+//   else:  out[n,c] = scale * sum_hw x   (global average pooling)
+template <bool kGate>
+__global__ void __launch_bounds__(256) hw_reduce_kernel(const float* __restrict__ x, const float* __restrict__ dy,
+                                                       float* __restrict__ out, int HW, int C, float scale) {
+  __shared__ float s_acc[8][33];
+  const int cx = threadIdx.x & 31, ly = threadIdx.x >> 5;
+  const int n = blockIdx.x, ch = blockIdx.y * 32 + cx;
   float acc = 0.f;
-  for (int p = 0; p < HW; ++p) acc = fmaf(xp[(long long)p * C], dp[(long long)p * C], acc);
-  ds[i] = acc;
+  if (ch < C) {
+    const float* xp = x + (long long)n * HW * C + ch;
+    const float* dp = kGate ? dy + (long long)n * HW * C + ch : nullptr;
+    for (int p = ly; p < HW; p += 8) acc = kGate ? fmaf(xp[(long long)p * C], dp[(long long)p * C], acc) : acc + xp[(long long)p * C];
+  }
+  s_acc[ly][cx] = acc;
+  __syncthreads();
+  if (ly == 0 && ch < C) {
+#pragma unroll
+    for (int j = 1; j < 8; ++j) acc += s_acc[j][cx];
+    out[(long long)n * C + ch] = acc * scale;
+  }
 }
 // Philox-free counter hash: mask[i] = (u < keep) / keep
 __global__ void __launch_bounds__(256) bernoulli_mask_kernel(float* __restrict__ m, long long n, float keep,
@@ -827,7 +839,7 @@ extern "C" int fedb_nn_scale(const float* x, const float* s, float* y, long long
   return 0;
 }
 extern "C" int fedb_nn_scale_bwd_gate(const float* x, const float* dy, float* ds, int HW, int C, int N, void* stream) {
-  scale_bwd_gate_kernel<<<fedb_ceil_div((long long)N * C, 256), 256, 0, S_>>>(x, dy, ds, HW, C, N);
+  hw_reduce_kernel<true><<<dim3(N, fedb_ceil_div(C, 32)), 256, 0, S_>>>(x, dy, ds, HW, C, 1.f);
   FEDB_LAUNCH_OK();
   return 0;
 }
@@ -841,7 +853,10 @@ extern "C" int fedb_nn_pool_fwd(const float* x, float* y, int* arg, const int* s
   const int* d = shape12;
   s.N = d[0]; s.H = d[1]; s.W = d[2]; s.C = d[3]; s.P = d[4]; s.Q = d[5]; s.kh = d[6]; s.kw = d[7]; s.sh = d[8]; s.sw = d[9];
   s.ph = d[10]; s.pw = d[11];
-  if (s.C % 4 == 0 && aligned16(x) && aligned16(y) && aligned16(arg))
+  if (!is_max && s.P == 1 && s.Q == 1 && s.ph == 0 && s.pw == 0 && s.kh == s.H && s.kw == s.W && s.H * s.W >= 16)
+    // global average pooling (SE squeeze): a parallel reduction over the positions instead of one serial window per thread
+    hw_reduce_kernel<false><<<dim3(s.N, fedb_ceil_div(s.C, 32)), 256, 0, S_>>>(x, nullptr, y, s.H * s.W, s.C, 1.f / (float)(s.H * s.W));
+  else if (s.C % 4 == 0 && aligned16(x) && aligned16(y) && aligned16(arg))
     pool_fwd4_kernel<<<grid_for((long long)s.N * s.P * s.Q * (s.C / 4)), 256, 0, S_>>>(x, y, arg, s, is_max);
   else
     pool_fwd_kernel<<<grid_for((long long)s.N * s.P * s.Q * s.C), 256, 0, S_>>>(x, y, arg, s, is_max);
