@@ -440,6 +440,17 @@ __global__ void __launch_bounds__(256) scale_kernel(const float* __restrict__ x,
     y[i] = x[i] * (mode == 0 ? s[n * C + (i % C)] : s[n]);
   }
 }
+__global__ void __launch_bounds__(256) scale4_kernel(const float* __restrict__ x, const float* __restrict__ s,
+                                                    float* __restrict__ y, long long total4, long long per_sample, int C, int mode) {
+  for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total4; i += (long long)gridDim.x * 256) {
+    const long long e = i * 4, n = e / per_sample;
+    const float4 v = *reinterpret_cast<const float4*>(x + e);
+    float4 g;
+    if (mode == 0) g = *reinterpret_cast<const float4*>(s + n * C + (e % C));
+    else { const float f = s[n]; g = make_float4(f, f, f, f); }
+    *reinterpret_cast<float4*>(y + e) = make_float4(v.x * g.x, v.y * g.y, v.z * g.z, v.w * g.w);
+  }
+}
 // Per-(sample, channel) reductions over the HW positions of an NHWC map: block = 32 channels x 8 position lanes of one
 // sample (grid = (N, C/32)), lanes stride over the positions, the eight lane sums are added in lane order.
 //   kGate: ds[n,c] = sum_hw dy*x   (SE excitation backward wrt the gate)
@@ -834,7 +845,10 @@ extern "C" int fedb_nn_add_act(const float* a, const float* b, float* y, long lo
 }
 extern "C" int fedb_nn_scale(const float* x, const float* s, float* y, long long total, long long per_sample, int C, int mode,
                              void* stream) {
-  scale_kernel<<<grid_for(total), 256, 0, S_>>>(x, s, y, total, per_sample, C, mode);
+  if (C % 4 == 0 && per_sample % 4 == 0 && total % 4 == 0 && aligned16(x) && aligned16(y) && (mode != 0 || aligned16(s)))
+    scale4_kernel<<<grid_for(total / 4), 256, 0, S_>>>(x, s, y, total / 4, per_sample, C, mode);
+  else
+    scale_kernel<<<grid_for(total), 256, 0, S_>>>(x, s, y, total, per_sample, C, mode);
   FEDB_LAUNCH_OK();
   return 0;
 }
