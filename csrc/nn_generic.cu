@@ -280,12 +280,16 @@ __device__ __forceinline__ bool chunk_reduce2(const float* __restrict__ scratch,
   float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
   if (ch < C) {
     int k = w;
-    for (; k + 8 < chunks; k += 16) {
-      const float x0 = scratch[((long long)k * 2 + 0) * C + ch], y0 = scratch[((long long)k * 2 + 1) * C + ch];
-      const float x1 = scratch[((long long)(k + 8) * 2 + 0) * C + ch], y1 = scratch[((long long)(k + 8) * 2 + 1) * C + ch];
-      a0 += x0; b0 += y0; a1 += x1; b1 += y1;
+    for (; k + 24 < chunks; k += 32) {                     // four chunks = eight loads in flight per thread
+      float xs[4], ys[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u) {
+        xs[u] = scratch[((long long)(k + 8 * u) * 2 + 0) * C + ch];
+        ys[u] = scratch[((long long)(k + 8 * u) * 2 + 1) * C + ch];
+      }
+      a0 += xs[0]; b0 += ys[0]; a1 += xs[1]; b1 += ys[1]; a0 += xs[2]; b0 += ys[2]; a1 += xs[3]; b1 += ys[3];
     }
-    if (k < chunks) { a0 += scratch[((long long)k * 2 + 0) * C + ch]; b0 += scratch[((long long)k * 2 + 1) * C + ch]; }
+    for (; k < chunks; k += 8) { a0 += scratch[((long long)k * 2 + 0) * C + ch]; b0 += scratch[((long long)k * 2 + 1) * C + ch]; }
   }
   sa[w][lane] = a0 + a1;
   sb[w][lane] = b0 + b1;

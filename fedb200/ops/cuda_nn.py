@@ -17,7 +17,8 @@ from ._lib import check, current_stream, lib
 
 CL = torch.channels_last
 ACT = {"none": 0, "relu": 1, "swish": 2, "sigmoid": 3}
-_BN_CHUNKS = 592          # upper bound of row chunks per BatchNorm reduction (scratch = 2 * C * chunks floats): 4 per SM
+_BN_CHUNKS = 296          # upper bound of row chunks per BatchNorm reduction (scratch = 2 * C * chunks floats): 2 per SM
+                          # (more chunks make the second, per-channel pass longer than the streaming pass it serves)
 
 _vp, _i, _ll, _f = C.c_void_p, C.c_int, C.c_longlong, C.c_float
 _BOUND = False
