@@ -41,32 +41,44 @@ def classify(shp):
     return f, d, w
 
 
+def conv_rows(name):
+    """[(classification, forward FLOPs at batch 128, shape14)] for every convolution of a zoo model."""
+    net = models.build(name).eval()
+    rows = []
+
+    def hook(mod, inp, out):
+        x = inp[0]
+        w = mod.weight
+        shp = NN._conv_shape(torch.empty(128, *x.shape[1:], device="meta"), w, mod.stride, mod.padding, mod.groups)
+        flops = 2 * 128 * shp[7] * shp[8] * shp[4] * (shp[3] // shp[13]) * shp[5] * shp[6]
+        rows.append((classify(shp), flops, shp))
+
+    hs = [m.register_forward_hook(hook) for m in net.modules() if isinstance(m, Conv2d)]
+    with torch.no_grad():
+        net(torch.zeros(2, 3, 32, 32))
+    for h in hs:
+        h.remove()
+    return rows
+
+
+def generic_share(name):
+    """Share of the convolution FLOPs of a model that still runs on the generic fp32 kernels, per direction."""
+    rows = conv_rows(name)
+    tot = sum(r[1] for r in rows) or 1
+    gen = collections.Counter()
+    for (f, d, w), fl, shp in rows:
+        for tag, v in (("fwd", f), ("dgrad", d), ("wgrad", w)):
+            if v == "generic":
+                gen[tag] += fl
+    return {tag: gen[tag] / tot for tag in ("fwd", "dgrad", "wgrad")}
+
+
 def main():
     names = sys.argv[1:] or sorted(models.REGISTRY)
-    total = collections.Counter()
     for name in names:
-        net = models.build(name).eval()
-        rows = []
-
-        def hook(mod, inp, out):
-            x = inp[0]
-            w = mod.weight
-            shp = NN._conv_shape(torch.empty(128, *x.shape[1:], device="meta"), w, mod.stride, mod.padding, mod.groups)
-            flops = 2 * 128 * shp[7] * shp[8] * shp[4] * (shp[3] // shp[13]) * shp[5] * shp[6]
-            rows.append((classify(shp), flops, shp))
-
-        hs = [m.register_forward_hook(hook) for m in net.modules() if isinstance(m, Conv2d)]
-        with torch.no_grad():
-            net(torch.zeros(2, 3, 32, 32))
-        for h in hs:
-            h.remove()
+        rows = conv_rows(name)
         tot = sum(r[1] for r in rows) or 1
-        gen = collections.Counter()
-        for (f, d, w), fl, shp in rows:
-            for tag, v in (("fwd", f), ("dgrad", d), ("wgrad", w)):
-                if v == "generic":
-                    gen[tag] += fl
-        total[name] = sum(gen.values()) / (3 * tot)
+        gen = {k: v * tot for k, v in generic_share(name).items()}
         worst = [(fl, shp, c) for c, fl, shp in rows if "generic" in c]
         worst.sort(reverse=True)
         print(f"{name:18s} convs {len(rows):3d}  generic FLOP share fwd {100 * gen['fwd'] / tot:5.1f}%  dgrad {100 * gen['dgrad'] / tot:5.1f}%"
