@@ -850,23 +850,31 @@ extern "C" int fedb_im2col_small(const float* x, float* out_f32, uint16_t* out_b
 // fp32 [rows][C] -> bf16 [rows][Cpad] with zero columns: gives activations whose channel count is not a multiple of 8 the
 // 16-byte row pitch the bf16 TMA maps of the weight-gradient GEMMs need (DenseNet's 12-channel growth, ShuffleNetV2's 116)
 __global__ void __launch_bounds__(256) cast_bf16_pad_kernel(const float* __restrict__ src, __nv_bfloat16* __restrict__ dst,
-                                                           long long rows, int C, int Cpad) {
+                                                           long long rows, int C, int Cpad, long long src_pitch) {
   const long long total = rows * Cpad;
   for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total; i += (long long)gridDim.x * 256) {
     const long long r = i / Cpad;
     const int c = (int)(i - r * Cpad);
-    dst[i] = __float2bfloat16(c < C ? src[r * C + c] : 0.f);
+    dst[i] = __float2bfloat16(c < C ? src[r * src_pitch + c] : 0.f);
   }
 }
 
-extern "C" int fedb_cast_bf16_pad(const float* src, uint16_t* dst, long long rows, int C, int Cpad, void* stream) {
+// src rows are src_pitch floats apart (0 = C, dense): with src pointing at a group's first channel of an NHWC tensor this
+// extracts that group's channels into a dense, zero-padded bf16 matrix
+extern "C" int fedb_cast_bf16_pad_p(const float* src, uint16_t* dst, long long rows, int C, int Cpad, long long src_pitch,
+                                    void* stream) {
   FEDB_REQUIRE(Cpad >= C && Cpad % 8 == 0, "fedb_cast_bf16_pad: Cpad must be a multiple of 8 and >= C");
   long long blocks = (rows * Cpad + 255) / 256;
   if (blocks > fedb_num_sms() * 16) blocks = fedb_num_sms() * 16;
   if (blocks < 1) blocks = 1;
-  cast_bf16_pad_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(src, (__nv_bfloat16*)dst, rows, C, Cpad);
+  cast_bf16_pad_kernel<<<(int)blocks, 256, 0, (cudaStream_t)stream>>>(src, (__nv_bfloat16*)dst, rows, C, Cpad,
+                                                                      src_pitch > 0 ? src_pitch : C);
   FEDB_LAUNCH_OK();
   return 0;
+}
+
+extern "C" int fedb_cast_bf16_pad(const float* src, uint16_t* dst, long long rows, int C, int Cpad, void* stream) {
+  return fedb_cast_bf16_pad_p(src, dst, rows, C, Cpad, 0, stream);
 }
 
 extern "C" int fedb_transpose(const float* in, float* out, int rows, int cols, void* stream) {

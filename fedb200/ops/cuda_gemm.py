@@ -28,6 +28,7 @@ def _f(name):
             "fedb_gemm_bf16_tn": [vp, vp, vp, i, i, i, ll, ll, ll, i, i, vp],
             "fedb_cast_bf16": [vp, vp, ll, vp],
             "fedb_cast_bf16_pad": [vp, vp, ll, i, i, vp],
+            "fedb_cast_bf16_pad_p": [vp, vp, ll, i, i, ll, vp],
             "fedb_transpose": [vp, vp, i, i, vp],
             "fedb_conv3x3_tf32": [vp, vp, vp, vp, i, i, i, i, i, i, vp],
             "fedb_pack3x3": [vp, vp, i, i, i, vp],
@@ -186,14 +187,19 @@ def _im2col(x, shp, f32: bool, bf16: bool):
     return o32, o16
 
 
-def _group_geometry(shp):
+def _group_geometry(shp, direction: str = "any"):
     """(Cg, Kg) when a grouped 3x3 / 1x1 convolution (stride 1 or 2) can run on the implicit-GEMM kernels: ALL groups in
-    one launch, the group index shifts the channel coordinates of the TMA boxes (ResNeXt, RegNet, DPN)."""
+    one launch, the group index shifts the channel coordinates of the TMA boxes (ResNeXt, RegNet, DPN, ShuffleNet).
+    Only the REDUCTION side needs 16-byte aligned group offsets (it is the TMA operand): the input channels per group for
+    the forward pass, the output channels per group for the data gradient; the other side is written by the epilogue,
+    which falls back to scalar stores.  ``direction``: "fwd", "dgrad" or "any" (either one qualifies)."""
     N, H, W, Cc, K, R, S, P, Q, sh, sw, ph, pw, groups = shp
     if groups < 2 or Cc % groups or K % groups:
         return None
     Cg, Kg = Cc // groups, K // groups
-    if Cg % 4 or Kg % 4 or R != S or R not in (1, 3) or sh != sw or sh not in (1, 2) or ph != (R - 1) // 2 or pw != ph:
+    ok = {"fwd": Cg % 4 == 0, "dgrad": Kg % 4 == 0, "wgrad": True}
+    ok["any"] = ok["fwd"] or ok["dgrad"]
+    if not ok[direction] or R != S or R not in (1, 3) or sh != sw or sh not in (1, 2) or ph != (R - 1) // 2 or pw != ph:
         return None
     if not (_pow2(P) and _pow2(Q) and 2 <= Q <= 32 and P * sh == H and Q * sw == W and N * P * Q >= MIN_PIXELS):
         return None
@@ -242,10 +248,41 @@ def _grouped_dgrad(dy, w, dx, shp, Cg, Kg) -> bool:
     return True
 
 
+MAX_SPLIT_GROUPS = 8       # odd per-group channel counts: weight gradient group by group, up to this many groups
+
+
+def _grouped_wgrad_by_group(x, dy, dw, db, shp, Cg, Kg) -> bool:
+    """Per-group channel counts that give no 16-byte bf16 offset inside the whole tensor (ShuffleNetG: 25, 100): every
+    group's channels are extracted into dense zero-padded bf16 matrices and run through the ungrouped kernel."""
+    N, H, W, Cc, K, R, S, P, Q, sh, sw, ph, pw, groups = shp
+    taps, pix, pix_in = R * R, N * P * Q, N * H * W
+    kp, cp = (Kg + 7) // 8 * 8, (Cg + 7) // 8 * 8
+    tiles = ((Kg + 127) // 128) * ((Cg + 127) // 128) * taps
+    splits = max(1, min(pix // 256, 444 // max(tiles, 1)))
+    cast = _f("fedb_cast_bf16_pad_p")
+    for g in range(groups):
+        dy16 = torch.empty(pix * kp, dtype=torch.bfloat16, device=x.device)
+        x16 = torch.empty(pix_in * cp, dtype=torch.bfloat16, device=x.device)
+        check(cast(dy.data_ptr() + 4 * g * Kg, dy16.data_ptr(), pix, Kg, kp, K, current_stream()), "fedb_cast_bf16_pad_p")
+        check(cast(x.data_ptr() + 4 * g * Cg, x16.data_ptr(), pix_in, Cg, cp, Cc, current_stream()), "fedb_cast_bf16_pad_p")
+        _lib.count_launch(2)
+        dwg = dw[g * Kg:(g + 1) * Kg]
+        dwk = torch.zeros(Kg * taps * Cg, dtype=torch.float32, device=x.device) if taps > 1 else dwg
+        check(_f("fedb_conv_wgrad_bf16_g")(dy16.data_ptr(), x16.data_ptr(), dwk.data_ptr(), N, H, W, Cg, Kg, R, sh, ph, splits,
+                                           kp, cp, current_stream()), "fedb_conv_wgrad_bf16_g")
+        _lib.count_launch()
+        if taps > 1:
+            check(_f("fedb_pack_filter")(dwk.data_ptr(), dwg.data_ptr(), Kg, Cg, 2, taps, current_stream()), "fedb_pack_filter")
+            _lib.count_launch()
+    if db is not None:
+        db += dy.sum(dim=(0, 2, 3))
+    return True
+
+
 def _grouped_wgrad(x, dy, dw, db, shp, Cg, Kg) -> bool:
     N, H, W, Cc, K, R, S, P, Q, sh, sw, ph, pw, groups = shp
-    if Cg % 8 or Kg % 8:
-        return False                                     # bf16 operands need a 16-byte channel pitch per group
+    if Cg % 8 or Kg % 8:                                 # no 16-byte bf16 group offsets inside the whole tensors
+        return _grouped_wgrad_by_group(x, dy, dw, db, shp, Cg, Kg) if groups <= MAX_SPLIT_GROUPS else False
     taps, pix = R * R, N * P * Q
     tiles = ((Kg + 127) // 128) * ((Cg + 127) // 128) * taps * groups
     splits = max(1, min(pix // 256, 444 // max(tiles, 1)))
@@ -263,9 +300,11 @@ def _grouped_wgrad(x, dy, dw, db, shp, Cg, Kg) -> bool:
 
 
 def conv_forward(x, w, bias, y, shp) -> bool:
-    gg = _group_geometry(shp)
+    gg = _group_geometry(shp, "fwd")
     if gg is not None:
         return _grouped_forward(x, w, bias, y, shp, *gg)
+    if shp[13] > 1:
+        return False
     if _small_reduction(shp):
         N, H, W, Cc, K, R, S, P, Q = shp[:9]
         xcol, _ = _im2col(x, shp, True, False)
@@ -294,9 +333,11 @@ def conv_forward(x, w, bias, y, shp) -> bool:
 
 
 def conv_dgrad(dy, w, dx, shp) -> bool:
-    gg = _group_geometry(shp)
+    gg = _group_geometry(shp, "dgrad")
     if gg is not None:
         return _grouped_dgrad(dy, w, dx, shp, *gg)
+    if shp[13] > 1:
+        return False
     if _is_3x3(shp, shp[4], shp[3]):
         N, H, W, Cc, K = shp[:5]
         conv3x3_tf32(dy, pack3x3(w, 1), dx, None, N, H, W, K, Cc)    # dX = conv3x3(dY, flipped + transposed filter)
@@ -326,9 +367,11 @@ def conv_dgrad(dy, w, dx, shp) -> bool:
 
 
 def conv_wgrad(x, dy, dw, db, shp) -> bool:
-    gg = _group_geometry(shp)
+    gg = _group_geometry(shp, "wgrad")
     if gg is not None:
         return _grouped_wgrad(x, dy, dw, db, shp, *gg)
+    if shp[13] > 1:
+        return False
     if _small_reduction(shp):
         N, H, W, Cc, K, R, S, P, Q = shp[:9]
         pix = N * P * Q

@@ -267,6 +267,8 @@ int fedb_im2col_small(const float* x, float* out_f32, uint16_t* out_bf16, int N,
 int fedb_cast_bf16(const float* src, uint16_t* dst, long long n, void* stream);          /* n % 4 == 0 */
 /* fp32 [rows][C] -> bf16 [rows][Cpad], zero columns appended (Cpad % 8 == 0): 16-byte pitch for any channel count */
 int fedb_cast_bf16_pad(const float* src, uint16_t* dst, long long rows, int C, int Cpad, void* stream);
+/* the same from rows that are src_pitch floats apart: extracts one group's channels of an NHWC tensor (src at its first channel) */
+int fedb_cast_bf16_pad_p(const float* src, uint16_t* dst, long long rows, int C, int Cpad, long long src_pitch, void* stream);
 int fedb_transpose(const float* in, float* out, int rows, int cols, void* stream);        /* out[cols][rows] */
 
 /* ------------------------------------------------------------------ generic NHWC layer kernels (csrc/nn_generic.cu)

@@ -164,7 +164,8 @@ def test_stem_conv_through_im2col_gemm(G, B, K, HW, bias):
 
 @pytest.mark.parametrize("B,C,K,HW,fs,stride,groups", [(4, 128, 128, 16, 3, 1, 2), (4, 256, 256, 16, 3, 2, 4), (8, 64, 128, 8, 1, 1, 2),
                                                      (4, 128, 256, 32, 1, 2, 8), (4, 192, 96, 8, 3, 1, 3), (4, 128, 128, 8, 3, 1, 32),
-                                                     (8, 152, 152, 8, 3, 2, 19), (4, 368, 368, 4, 3, 1, 46), (4, 96, 192, 16, 3, 2, 8)])
+                                                     (8, 152, 152, 8, 3, 2, 19), (4, 368, 368, 4, 3, 1, 46), (4, 96, 192, 16, 3, 2, 8),
+                                                     (4, 200, 50, 16, 1, 1, 2), (4, 50, 176, 16, 1, 1, 2), (8, 60, 240, 8, 1, 1, 3)])
 def test_grouped_conv_on_tensor_cores(G, B, C, K, HW, fs, stride, groups):
     """Grouped convolutions (ResNeXt, RegNet, DPN): all groups in one implicit-GEMM launch; the group index shifts the channel
     coordinate of the TMA boxes, spill-over into the next group meets zeros of the packed filter or the epilogue masks."""

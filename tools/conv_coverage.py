@@ -17,9 +17,12 @@ def classify(shp):
     N, H, W, Cc, K, R, S, P, Q, sh, sw, ph, pw, groups = shp
     if NN._is_depthwise(shp):
         return ("depthwise",) * 3
-    gg = G._group_geometry(shp)
-    if gg is not None:
-        return ("tc-grouped", "tc-grouped", "tc-grouped" if gg[0] % 8 == 0 and gg[1] % 8 == 0 else "generic")
+    if groups > 1:
+        gf, gd = G._group_geometry(shp, "fwd"), G._group_geometry(shp, "dgrad")
+        Cg, Kg = Cc // groups, K // groups
+        geo = G._group_geometry(shp, "wgrad") is not None
+        return ("tc-grouped" if gf else "generic", "tc-grouped" if gd else "generic",
+                "tc-grouped" if geo and ((Cg % 8 == 0 and Kg % 8 == 0) or groups <= G.MAX_SPLIT_GROUPS) else "generic")
     if G._small_reduction(shp):
         return ("tc-im2col", "-", "tc-im2col")
     f = d = w = "generic"
