@@ -26,11 +26,19 @@ struct Taps;
 template <int R>
 struct Taps<R, true> {
   float4 t[R * R];
+  // the taps of four consecutive channels are 4 * R * R CONTIGUOUS floats of the OIHW filter, starting at a multiple of
+  // 16 bytes (c % 4 == 0): R * R 128-bit loads and a register transpose instead of 4 * R * R scalar loads (on the small
+  // late maps a thread computes only a few pixels, so the tap loads are a large part of its work)
   __device__ __forceinline__ void load(const float* __restrict__ w, int c) {
+    float f[4 * R * R];
+    const float4* p = reinterpret_cast<const float4*>(w + (long long)c * R * R);
 #pragma unroll
-    for (int k = 0; k < R * R; ++k)
-      t[k] = make_float4(__ldg(w + (c + 0) * R * R + k), __ldg(w + (c + 1) * R * R + k), __ldg(w + (c + 2) * R * R + k),
-                         __ldg(w + (c + 3) * R * R + k));
+    for (int i = 0; i < R * R; ++i) {
+      const float4 v = __ldg(p + i);
+      f[4 * i] = v.x; f[4 * i + 1] = v.y; f[4 * i + 2] = v.z; f[4 * i + 3] = v.w;
+    }
+#pragma unroll
+    for (int k = 0; k < R * R; ++k) t[k] = make_float4(f[k], f[R * R + k], f[2 * R * R + k], f[3 * R * R + k]);
   }
   __device__ __forceinline__ float4 get(int k) const { return t[k]; }
 };
