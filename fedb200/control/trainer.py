@@ -115,6 +115,13 @@ class LocalTrainer:
     def dumps(self, epoch: int = 1) -> bytes:
         return ckpt.dumps(self.state_dict(), acc=1, epoch=epoch)
 
+    def set_lr(self, lr: float) -> None:
+        """New learning rate for the following passes (standalone training with a schedule, fedb200/main.py).  The rate
+        is an argument baked into captured graphs, so the GPU engine drops them and captures again on the next pass."""
+        self.cfg.lr = float(lr)
+        if self._engine is not None:
+            self._engine.rebind_arena(self.arena)
+
     # ------------------------------------------------------------------ training
     def shard(self, rank: int, world: int):
         nb = self.dataset.num_train_batches(self.cfg.batch_size)
