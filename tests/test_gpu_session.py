@@ -44,3 +44,16 @@ def test_round_is_reproducible_across_upload_modes_and_async():
     assert a.h2d_bytes_per_round() == (128 * 20 + 17) * (3072 + 8) + 1003 * (3072 + 8)
     for f in (a, b, c):
         f.close()
+
+
+def test_standalone_trainer_on_gpu_follows_the_cpu_run(tmp_path):
+    """python -m fedb200.main on cuda: two epochs with the cosine schedule (the learning rate changes between epochs, so
+    the captured pass is dropped and captured again) track the CPU run of the same seed."""
+    from fedb200 import main as M
+    ds = D.synthetic_cifar(128 * 4, 200, seed=2)
+    common = ["--model", "LeNet", "--epochs", "2", "--lr", "0.05", "--t-max", "3", "--seed", "4"]
+    cpu = M.run(common + ["--name", "c", "--checkpoint-root", str(tmp_path / "c")], dataset=ds)
+    gpu = M.run(common + ["--name", "g", "--checkpoint-root", str(tmp_path / "g"), "--device", "cuda:0"], dataset=ds)
+    assert gpu["last"]["steps"] == cpu["last"]["steps"] == 4 and gpu["last"]["lr"] == cpu["last"]["lr"]
+    assert abs(gpu["last"]["train_loss"] - cpu["last"]["train_loss"]) < 2e-3
+    assert abs(gpu["last"]["test_loss"] - cpu["last"]["test_loss"]) < 2e-3
