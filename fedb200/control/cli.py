@@ -4,7 +4,7 @@
   client:  -a/--address HOST:PORT   -c/--compressFlag Y   -r/--resume   --lr LR
 
 and everything the reference hard-codes (B10) became a flag: --workers, --rounds, --model,
---batch-size, --watchdog, --plane, --device, --dataset-size, --seed, --metrics.
+--batch-size, --watchdog, --plane, --device, --dataset-size, --data-root, --seed, --metrics.
 """
 from __future__ import annotations
 
@@ -86,6 +86,8 @@ def client_parser() -> argparse.ArgumentParser:
     p.add_argument("--plane", choices=("legacy", "peer"), default="legacy")
     p.add_argument("--dataset-size", type=int, default=50000)
     p.add_argument("--test-size", type=int, default=10000)
+    p.add_argument("--data-root", default=None,
+                   help="directory holding cifar-10-batches-py: train on the real CIFAR-10 instead of the synthetic set")
     p.add_argument("--data-seed", type=int, default=0)
     p.add_argument("--pad-from", type=int, default=None, help="draw SxS images, zero-pad to 32x32")
     p.add_argument("--augment", action="store_true", help="RandomCrop(32,4)+flip like the reference")
@@ -111,7 +113,8 @@ def client_main(argv=None) -> int:
     device = args.device or ("cuda" if torch.cuda.is_available() else "cpu")
     print(f"Client is running on {args.address} ")
     print(f"Compression {args.compressFlag} enabled")
-    ds = D.synthetic_cifar(args.dataset_size, args.test_size, seed=args.data_seed, pad_from=args.pad_from)
+    ds = D.load_cifar10(args.data_root) if args.data_root else \
+        D.synthetic_cifar(args.dataset_size, args.test_size, seed=args.data_seed, pad_from=args.pad_from)
     tcfg = TrainerConfig(model=args.model, lr=args.lr, batch_size=args.batch_size, device=device,
                          seed=args.seed, augment=args.augment, resume=args.resume,
                          checkpoint_path=ckpt.worker_checkpoint_path(args.address))

@@ -37,6 +37,7 @@ def parser() -> argparse.ArgumentParser:
     p.add_argument("--augment", action="store_true", help="random crop + flip like the reference's train transform")
     p.add_argument("--dataset-size", type=int, default=50000, help="synthetic CIFAR-shaped train samples")
     p.add_argument("--test-size", type=int, default=10000)
+    p.add_argument("--data-root", default=None, help="directory holding cifar-10-batches-py (real CIFAR-10)")
     p.add_argument("--seed", type=int, default=0)
     p.add_argument("--metrics", default=None, help="JSONL file for per-epoch records")
     return p
@@ -50,7 +51,7 @@ def cosine_lr(base_lr: float, epoch: int, t_max: int) -> float:
 def run(argv: Optional[Sequence[str]] = None, dataset: Optional[D.ImageDataset] = None) -> dict:
     a = parser().parse_args(argv)
     path = ckpt.worker_checkpoint_path(a.name, a.checkpoint_root)
-    ds = dataset if dataset is not None else D.synthetic_cifar(a.dataset_size, a.test_size, seed=a.seed)
+    ds = dataset if dataset is not None else D.get_dataset(a.data_root, a.dataset_size, a.test_size, seed=a.seed)
     cfg = TrainerConfig(model=a.model, lr=a.lr, batch_size=a.batch_size, augment=a.augment, device=a.device, seed=a.seed,
                         checkpoint_path=path, resume=a.resume and os.path.exists(path))
     t = LocalTrainer(cfg, ds)

@@ -93,3 +93,43 @@ def shard_batches(num_batches: int, rank: int, world: int):
     counter is advanced before the test, so 0-based batch ``b`` belongs to rank ``(b+1) % world``.
     world=2: rank0 gets b=1,3,.. (195 of 391), rank1 gets b=0,2,.. (196)."""
     return [b for b in range(num_batches) if (b + 1) % world == rank]
+
+
+def load_cifar10(root: str) -> ImageDataset:
+    """The real CIFAR-10 from the standard python archive (``<root>/cifar-10-batches-py/data_batch_1..5, test_batch``, the
+    files torchvision's ``CIFAR10(root, download=True)`` leaves behind - src/main.py:43-56).  Nothing is downloaded; the
+    pickles are read directly, so torchvision is not needed.  Images come back as uint8 HWC like the synthetic set."""
+    import os
+    import pickle
+
+    import numpy as np
+
+    base = os.path.join(root, "cifar-10-batches-py")
+    if not os.path.isdir(base):
+        base = root
+
+    def read(names):
+        xs, ys = [], []
+        for n in names:
+            with open(os.path.join(base, n), "rb") as f:
+                d = pickle.load(f, encoding="latin1")
+            xs.append(np.asarray(d["data"], dtype=np.uint8).reshape(-1, 3, 32, 32).transpose(0, 2, 3, 1))
+            ys.append(np.asarray(d.get("labels", d.get("fine_labels")), dtype=np.int64))
+        return torch.from_numpy(np.ascontiguousarray(np.concatenate(xs))), torch.from_numpy(np.concatenate(ys))
+
+    tx, ty = read([f"data_batch_{i}" for i in range(1, 6)])
+    vx, vy = read(["test_batch"])
+    return ImageDataset(tx, ty, vx, vy, name="cifar10")
+
+
+def get_dataset(root: Optional[str] = None, n_train: int = 50000, n_test: int = 10000, seed: int = 0) -> ImageDataset:
+    """CIFAR-10 from ``root`` when given, else the synthetic stand-in (this image has no network)."""
+    return load_cifar10(root) if root else synthetic_cifar(n_train, n_test, seed=seed)
+
+
+def get_mean_and_std(images_u8: torch.Tensor) -> Tuple[torch.Tensor, torch.Tensor]:
+    """Per-channel mean of the per-image means and of the per-image standard deviations of a uint8 [N, H, W, 3] set
+    scaled to [0, 1] - the statistic the reference's (unused, broken: it never imports torch) ``get_mean_and_std``
+    describes (src/utils.py:15-27), computed in one vectorised pass instead of a batch-size-1 DataLoader loop."""
+    x = images_u8.to(torch.float32).div_(255.0).flatten(1, 2)         # [N, H*W, 3]
+    return x.mean(1).mean(0), x.std(1, unbiased=True).mean(0)
