@@ -92,6 +92,7 @@ def client_parser() -> argparse.ArgumentParser:
     p.add_argument("--pad-from", type=int, default=None, help="draw SxS images, zero-pad to 32x32")
     p.add_argument("--augment", action="store_true", help="RandomCrop(32,4)+flip like the reference")
     p.add_argument("--no-eval", action="store_true", help="skip the eval inside SendModel")
+    p.add_argument("--progress", action="store_true", help="reference-style per-batch progress bar when stdout is a TTY (CPU trainer)")
     p.add_argument("--peer-rank", type=int, default=0, help="peer plane: this worker's index in the coordinator's --workers list")
     p.add_argument("--peer-world", type=int, default=1, help="peer plane: number of configured workers")
     p.add_argument("--peer-tag", default="fed", help="peer plane: job tag shared by all workers (names the unix sockets)")
@@ -116,7 +117,7 @@ def client_main(argv=None) -> int:
     ds = D.load_cifar10(args.data_root) if args.data_root else \
         D.synthetic_cifar(args.dataset_size, args.test_size, seed=args.data_seed, pad_from=args.pad_from)
     tcfg = TrainerConfig(model=args.model, lr=args.lr, batch_size=args.batch_size, device=device,
-                         seed=args.seed, augment=args.augment, resume=args.resume,
+                         seed=args.seed, augment=args.augment, resume=args.resume, progress=args.progress,
                          checkpoint_path=ckpt.worker_checkpoint_path(args.address))
     wcfg = WorkerConfig(address=args.address, compress=args.compressFlag == "Y", plane=args.plane,
                         eval_on_send=not args.no_eval)

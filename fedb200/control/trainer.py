@@ -30,6 +30,7 @@ from ..ops import functional as F
 from ..parallel.arena import Arena
 from ..utils import checkpoint as ckpt
 from ..utils import data as D
+from ..utils.metrics import ProgressBar
 
 
 @dataclass
@@ -64,6 +65,7 @@ class TrainerConfig:
     resume: bool = False
     use_cuda_graph: bool = True
     max_batches: Optional[int] = None   # truncate the pass (tests)
+    progress: bool = False              # reference-style progress bar per batch on a TTY (src/main.py:157-158, utils.py:51-92)
 
 
 def sgd_step_flat_(p: torch.Tensor, g: torch.Tensor, v: torch.Tensor, lr: float, momentum: float,
@@ -152,7 +154,8 @@ class LocalTrainer:
         cfg, a = self.cfg, self.arena
         st = TrainStats()
         self.model.train()
-        for b in batches:
+        bar = ProgressBar(len(batches)) if cfg.progress and batches else None
+        for i, b in enumerate(batches):
             x, y = self._cpu_batch(b)
             a.zero_grad()
             out = self.model(x)
@@ -167,6 +170,8 @@ class LocalTrainer:
                 st.correct += int((out.argmax(1) == y).sum())
             st.samples += y.numel()
             st.steps += 1
+            if bar is not None:
+                bar.update(i, "Loss: %.3f | Acc: %.3f%% (%d/%d)" % (st.mean_loss, 100.0 * st.accuracy, st.correct, st.samples))
         return st
 
     # ------------------------------------------------------------------ evaluation
@@ -185,6 +190,7 @@ class LocalTrainer:
         self.model.eval()
         bs = self.cfg.test_batch_size
         n = self.dataset.test_x.shape[0]
+        bar = ProgressBar((n + bs - 1) // bs) if self.cfg.progress and n else None
         with torch.no_grad():
             for lo in range(0, n, bs):
                 x = D.normalize_batch(self.dataset.test_x[lo:lo + bs])
@@ -194,4 +200,6 @@ class LocalTrainer:
                 st.correct += int((out.argmax(1) == y).sum())
                 st.samples += y.numel()
                 st.steps += 1
+                if bar is not None:
+                    bar.update(lo // bs, "Loss: %.3f | Acc: %.3f%% (%d/%d)" % (st.mean_loss, 100.0 * st.accuracy, st.correct, st.samples))
         return st

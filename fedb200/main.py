@@ -40,6 +40,7 @@ def parser() -> argparse.ArgumentParser:
     p.add_argument("--data-root", default=None, help="directory holding cifar-10-batches-py (real CIFAR-10)")
     p.add_argument("--seed", type=int, default=0)
     p.add_argument("--metrics", default=None, help="JSONL file for per-epoch records")
+    p.add_argument("--progress", action="store_true", help="per-batch progress bar on a TTY (CPU trainer), like the reference")
     return p
 
 
@@ -52,7 +53,7 @@ def run(argv: Optional[Sequence[str]] = None, dataset: Optional[D.ImageDataset] 
     a = parser().parse_args(argv)
     path = ckpt.worker_checkpoint_path(a.name, a.checkpoint_root)
     ds = dataset if dataset is not None else D.get_dataset(a.data_root, a.dataset_size, a.test_size, seed=a.seed)
-    cfg = TrainerConfig(model=a.model, lr=a.lr, batch_size=a.batch_size, augment=a.augment, device=a.device, seed=a.seed,
+    cfg = TrainerConfig(model=a.model, lr=a.lr, batch_size=a.batch_size, augment=a.augment, device=a.device, seed=a.seed, progress=a.progress,
                         checkpoint_path=path, resume=a.resume and os.path.exists(path))
     t = LocalTrainer(cfg, ds)
     sink = JsonlSink(a.metrics)
