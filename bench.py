@@ -49,6 +49,10 @@ def parse():
     ap.add_argument("--no-multicast", action="store_true")
     ap.add_argument("--repl", choices=("overlap", "fused"), default="overlap")
     ap.add_argument("--ref-gpu-workers", action="store_true", help="reference arm: R-gpu variant (DP shim)")
+    ap.add_argument("--eval", choices=("overlap", "inline"), default="overlap",
+                    help="overlap: every client scores the whole test set every round on a second stream, concurrently "
+                         "with the next local pass; inline: on the round's critical path, as the reference does")
+    ap.add_argument("--no-augment", action="store_true", help="skip RandomCrop+Flip (the reference arm always applies them)")
     ap.add_argument("--no-l2-flush", action="store_true", help="diagnostic: skip the L2 flush between device-timed rounds")
     return ap.parse_args()
 
@@ -146,7 +150,8 @@ def run_ours(a) -> dict:
     ds = D.synthetic_cifar(a.n_train, a.n_test, seed=0)
     fed = GpuFederation(model=a.model, rank=rank, world=world, device=local, dataset=ds, seed=1000 + rank,
                         batch_size=a.batch_size, codec=a.codec, nvls_reduce=a.nvls_reduce,
-                        use_multicast=not a.no_multicast, repl_mode=a.repl,
+                        use_multicast=not a.no_multicast, repl_mode=a.repl, eval_mode=a.eval,
+                        augment=not a.no_augment,
                         tag=f"bench-{os.environ.get('MASTER_PORT', 'solo')}-{os.getppid()}")
     flush = torch.empty(256 << 20, dtype=torch.uint8, device="cuda")      # > 126 MB L2
 
@@ -157,6 +162,7 @@ def run_ours(a) -> dict:
     W = max(a.warmup, 3)
     for i in range(W):
         last = fed.run_round(upload=i < W - 1, sync=True)
+    fed.drain()
     barrier()
 
     # ---------------------------------------------------------------- device-timed rounds
@@ -166,11 +172,13 @@ def run_ours(a) -> dict:
     ev = [(torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)) for _ in range(a.steps)]
     launches0 = _lib.launches
     barrier()
-    for s, e in ev:
+    for i, (s, e) in enumerate(ev):
         if not a.no_l2_flush:
             flush.zero_()                   # L2 flush between timed iterations, outside the events
         s.record()
         fed.run_round(upload=False, sync=False)
+        if i == a.steps - 1:
+            fed.drain(sync=False)           # the evaluation still in flight on the second stream ends inside the timed region
         e.record()
     barrier()
     launches = _lib.launches - launches0
@@ -189,10 +197,21 @@ def run_ours(a) -> dict:
             last = pending.result()                 # result of the previous round, read while this one runs
         pending = h
     last = pending.result()
+    last_eval = fed.drain()                        # overlap mode: the last round's evaluation, still inside the timed region
     barrier()
     e2e_s = max_over_ranks(time.perf_counter() - t0)
     h2d, d2h = fed.h2d_bytes_per_round(), fed.d2h_bytes_per_round()
-    train_st, eval_st = last
+    train_st, eval_st = last[0], last_eval
+
+    # ---------------------------------------------------------------- correctness of the multi-GPU round (untimed)
+    def all_gather(t):
+        if world == 1:
+            return [t]
+        outs = [torch.empty_like(t) for _ in range(world)]
+        dist.all_gather(outs, t.contiguous())
+        return outs
+    check = fed.aggregation_selfcheck(all_gather) if a.codec == "none" and not a.nvls_reduce else \
+        {"agg_check": "skipped (lossy codec / in-switch reduction order)", "arenas_equal": None}
     out = {
         "metric": METRIC, "value": value, "unit": "rounds/s", "n_gpus": world, "steps": a.steps, "warmup": a.warmup,
         "ms_per_step": dev_ms / a.steps, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
@@ -203,6 +222,10 @@ def run_ours(a) -> dict:
         "config": {"model": a.model, "clients": world, "global_batch": a.batch_size * world, "seq_len": None,
                    "parallelism": f"fedavg{world}", "train_samples": a.n_train, "test_samples": a.n_test,
                    "local_epochs": 1, "steps_per_client_per_round": train_st.steps, "eval_in_round": True,
+                   "eval": ("overlap: all %d test images scored by every client every round on a second stream, concurrent "
+                            "with the next local pass; K evaluations end inside the K timed rounds" % a.n_test)
+                   if a.eval == "overlap" else "inline (on the round's critical path)",
+                   "augment": not a.no_augment, "agg_check": check["agg_check"], "arenas_equal": check["arenas_equal"],
                    "l2": "flushed between rounds (256 MiB memset outside the timed events); round inputs are "
                          f"{h2d / 1e6:.0f} MB per client",
                    "codec": a.codec, "multicast": bool(fed.group.peers.mc_base), "nvls_reduce": a.nvls_reduce,

@@ -26,6 +26,7 @@ __device__ __forceinline__ bool spin_until_ge(const uint32_t* flag, uint32_t wan
   unsigned int backoff = 32;
   while ((int32_t)(ld_acquire_sys_u32(flag) - want) < 0) {
     if (ld_acquire_sys_u32(abort_flag) != 0) { atomicMax(status, 3u); return false; }
+    if (*reinterpret_cast<volatile uint32_t*>(status) != 0) return false;   // another waiter of this rank gave up
     if (globaltimer_ns() - t0 > timeout_ns) { atomicMax(status, code); return false; }
     __nanosleep(backoff);
     if (backoff < 1024) backoff <<= 1;
@@ -81,11 +82,14 @@ __device__ __forceinline__ uint2 pack_bf16x4(float4 v) {
   return r;
 }
 
-template <bool kNvls, bool kDecode>
-__global__ void __launch_bounds__(kThreads, 4) fedavg_kernel(const __grid_constant__ fedb_agg_desc_t p) {
+// kSrc > 0: the number of sources is a compile-time constant, so ALL kSrc * kUnroll 128-bit loads of a thread are issued
+// before the first add (kSrc * kUnroll * 16 B in flight per thread hides the NVLink round trip); kSrc == 0: run-time count.
+template <bool kNvls, bool kDecode, int kSrc>
+__global__ void __launch_bounds__(kThreads, (kSrc > 4 ? 2 : 4)) fedavg_kernel(const __grid_constant__ fedb_agg_desc_t p) {
   const int tid = threadIdx.x;
   __shared__ uint32_t s_epoch;
   __shared__ int s_last;
+  bool ok = p.gate == nullptr || ld_acquire_sys_u32(p.gate) == 0;
 
   // ---------------------------------------------------------------- (A) arrive + wait
   if (p.sync_mode == 1) {
@@ -96,52 +100,79 @@ __global__ void __launch_bounds__(kThreads, 4) fedavg_kernel(const __grid_consta
       __threadfence_system();
       st_release_sys_u32(&p.ctrl_peer[tid]->arrive[p.rank], epoch);
     }
+    bool mine = true;
     if (tid < p.world)
-      spin_until_ge(&p.ctrl_local->arrive[tid], epoch, &p.ctrl_local->abort_flag, p.timeout_ns,
-                    &p.ctrl_local->status, 1u);
-    __syncthreads();
+      mine = spin_until_ge(&p.ctrl_local->arrive[tid], epoch, &p.ctrl_local->abort_flag, p.timeout_ns,
+                           &p.ctrl_local->status, 1u);
+    // A failed wait (dead or late peer, abort) must leave EVERY arena untouched: the round did not happen.  The outcome is
+    // block-wide (one vote), and a block that got through still yields to a failure another block of this rank recorded.
+    ok = __syncthreads_and(mine ? 1 : 0) != 0;
+    if (ok && ld_acquire_sys_u32(&p.ctrl_local->status) != 0) ok = false;
+    if (!ok && blockIdx.x == 0 && tid < p.world) {
+      // withdraw my announcement, so that a peer which shows up later cannot complete the round on its own
+      st_release_sys_u32(&p.ctrl_peer[tid]->arrive[p.rank], epoch - 1);
+    }
   }
 
   // ---------------------------------------------------------------- (B)+(C) reduce + fan-out
   const long long v_begin = p.begin >> 2, v_end = p.end >> 2;
   const long long stride = (long long)gridDim.x * kThreads;
-  const float n_div = (float)p.n_src;
+  const int n_src = kSrc > 0 ? kSrc : p.n_src;
+  const float n_div = (float)n_src;
   float wsum = 0.f;
   if (!p.uniform)
-    for (int k = 0; k < p.n_src; ++k) wsum += p.weight[k];
+    for (int k = 0; k < n_src; ++k) wsum += p.weight[k];
 
-  for (long long i0 = v_begin + (long long)blockIdx.x * kThreads + tid; i0 < v_end; i0 += stride * kUnroll) {
+  for (long long i0 = v_begin + (long long)blockIdx.x * kThreads + tid; ok && i0 < v_end; i0 += stride * kUnroll) {
     float4 acc[kUnroll];
     bool live[kUnroll];
 #pragma unroll
-    for (int u = 0; u < kUnroll; ++u) {
-      const long long i = i0 + u * stride;
-      live[u] = i < v_end;
-      if (!live[u]) continue;
-      if constexpr (kNvls) {
-        acc[u] = mc_ld_reduce_f4(p.mc_src, i);
-      } else if constexpr (kDecode) {
-        acc[u] = dequant4(p.src_q[0], p.src_scale[0], i);
-        if (!p.uniform) acc[u] = f4_fma_s(acc[u], p.weight[0], make_float4(0.f, 0.f, 0.f, 0.f));
-      } else {
-        acc[u] = ld_src_f4(p.src[0], i);
-        if (!p.uniform) acc[u] = f4_fma_s(acc[u], p.weight[0], make_float4(0.f, 0.f, 0.f, 0.f));
+    for (int u = 0; u < kUnroll; ++u) live[u] = i0 + u * stride < v_end;
+    if constexpr (kSrc > 0 && !kNvls && !kDecode) {
+      float4 v[kSrc][kUnroll];
+#pragma unroll
+      for (int k = 0; k < kSrc; ++k)
+#pragma unroll
+        for (int u = 0; u < kUnroll; ++u)
+          if (live[u]) v[k][u] = ld_src_f4(p.src[k], i0 + u * stride);
+#pragma unroll
+      for (int u = 0; u < kUnroll; ++u) {
+        if (!live[u]) continue;
+        acc[u] = p.uniform ? v[0][u] : f4_fma_s(v[0][u], p.weight[0], make_float4(0.f, 0.f, 0.f, 0.f));
+#pragma unroll
+        for (int k = 1; k < kSrc; ++k)
+          acc[u] = p.uniform ? f4_add(acc[u], v[k][u]) : f4_fma_s(v[k][u], p.weight[k], acc[u]);
       }
-    }
-    if constexpr (!kNvls) {
-      for (int k = 1; k < p.n_src; ++k) {
-        float4 v[kUnroll];
+    } else {
 #pragma unroll
-        for (int u = 0; u < kUnroll; ++u) {
-          if (!live[u]) continue;
-          const long long i = i0 + u * stride;
-          if constexpr (kDecode) v[u] = dequant4(p.src_q[k], p.src_scale[k], i);
-          else v[u] = ld_src_f4(p.src[k], i);
+      for (int u = 0; u < kUnroll; ++u) {
+        const long long i = i0 + u * stride;
+        if (!live[u]) continue;
+        if constexpr (kNvls) {
+          acc[u] = mc_ld_reduce_f4(p.mc_src, i);
+        } else if constexpr (kDecode) {
+          acc[u] = dequant4(p.src_q[0], p.src_scale[0], i);
+          if (!p.uniform) acc[u] = f4_fma_s(acc[u], p.weight[0], make_float4(0.f, 0.f, 0.f, 0.f));
+        } else {
+          acc[u] = ld_src_f4(p.src[0], i);
+          if (!p.uniform) acc[u] = f4_fma_s(acc[u], p.weight[0], make_float4(0.f, 0.f, 0.f, 0.f));
         }
+      }
+      if constexpr (!kNvls) {
+        for (int k = 1; k < n_src; ++k) {
+          float4 v[kUnroll];
 #pragma unroll
-        for (int u = 0; u < kUnroll; ++u) {
-          if (!live[u]) continue;
-          acc[u] = p.uniform ? f4_add(acc[u], v[u]) : f4_fma_s(v[u], p.weight[k], acc[u]);
+          for (int u = 0; u < kUnroll; ++u) {
+            if (!live[u]) continue;
+            const long long i = i0 + u * stride;
+            if constexpr (kDecode) v[u] = dequant4(p.src_q[k], p.src_scale[k], i);
+            else v[u] = ld_src_f4(p.src[k], i);
+          }
+#pragma unroll
+          for (int u = 0; u < kUnroll; ++u) {
+            if (!live[u]) continue;
+            acc[u] = p.uniform ? f4_add(acc[u], v[u]) : f4_fma_s(v[u], p.weight[k], acc[u]);
+          }
         }
       }
     }
@@ -160,10 +191,10 @@ __global__ void __launch_bounds__(kThreads, 4) fedavg_kernel(const __grid_consta
   }
 
   // int64 counters (N3): tiny, one block.  sum in int64, fp32 true division, truncate.
-  if (p.do_i64 && blockIdx.x == 0) {
+  if (ok && p.do_i64 && blockIdx.x == 0) {
     for (long long i = tid; i < p.n_i64; i += kThreads) {
       long long s = p.src_i64[0][i];
-      for (int k = 1; k < p.n_src; ++k) s += p.src_i64[k][i];
+      for (int k = 1; k < n_src; ++k) s += p.src_i64[k][i];
       long long r = (long long)truncf(__fdiv_rn(__ll2float_rn(s), n_div));
       for (int d = 0; d < p.n_dst_i64; ++d)
         if (p.dst_i64[d] != nullptr) p.dst_i64[d][i] = r;
@@ -180,9 +211,10 @@ __global__ void __launch_bounds__(kThreads, 4) fedavg_kernel(const __grid_consta
   __syncthreads();
   if (!s_last) return;
   // last block of this rank: every store of the grid is globally performed
-  if (p.version != 0 && tid < p.n_dst && p.dst_ctrl[tid] != nullptr)
+  if (ok && p.sync_mode == 1 && ld_acquire_sys_u32(&p.ctrl_local->status) != 0) ok = false;
+  if (ok && p.version != 0 && tid < p.n_dst && p.dst_ctrl[tid] != nullptr)
     st_release_sys_u32(&p.dst_ctrl[tid]->version, p.version);
-  if (p.sync_mode == 1) {
+  if (ok && p.sync_mode == 1) {
     const uint32_t epoch = s_epoch;
     if (tid < p.world) {
       st_release_sys_u32(&p.ctrl_peer[tid]->done[p.rank], epoch);
@@ -190,7 +222,8 @@ __global__ void __launch_bounds__(kThreads, 4) fedavg_kernel(const __grid_consta
                     &p.ctrl_local->status, 2u);
     }
     __syncthreads();
-    if (tid == 0) st_release_sys_u32(&p.ctrl_local->epoch, epoch);
+    // the epoch only advances over a completed round; after a failure the host picks a fresh one (reset_sync)
+    if (tid == 0 && ld_acquire_sys_u32(&p.ctrl_local->status) == 0) st_release_sys_u32(&p.ctrl_local->epoch, epoch);
   }
   if (tid == 0) {
     p.ctrl_local->blocks_done = 0;
@@ -252,13 +285,23 @@ extern "C" int fedb_fedavg(const fedb_agg_desc_t* d, int max_blocks, void* strea
   FEDB_REQUIRE(!decode || d->base != nullptr, "fedb_fedavg: compressed uploads need a base model");
   const long long n4 = (d->end - d->begin) / 4;
   int blocks = fedb_ceil_div(n4, (long long)kThreads * kUnroll);
-  const int cap = max_blocks > 0 ? max_blocks : fedb_num_sms() * 4;
+  const bool plain = !nvls && !decode;
+  const int per_sm = (plain && d->n_src > 4 && d->n_src <= 8) ? 2 : 4;   // matches the kernels' launch bounds
+  const int cap = max_blocks > 0 ? max_blocks : fedb_num_sms() * per_sm;
   if (blocks > cap) blocks = cap;
   if (blocks < 1) blocks = 1;
   cudaStream_t s = (cudaStream_t)stream;
-  if (nvls) fedavg_kernel<true, false><<<blocks, kThreads, 0, s>>>(*d);
-  else if (decode) fedavg_kernel<false, true><<<blocks, kThreads, 0, s>>>(*d);
-  else fedavg_kernel<false, false><<<blocks, kThreads, 0, s>>>(*d);
+  if (nvls) fedavg_kernel<true, false, 0><<<blocks, kThreads, 0, s>>>(*d);
+  else if (decode) fedavg_kernel<false, true, 0><<<blocks, kThreads, 0, s>>>(*d);
+  else {
+    switch (d->n_src) {
+#define FEDB_AGG_CASE(N) case N: fedavg_kernel<false, false, N><<<blocks, kThreads, 0, s>>>(*d); break;
+      FEDB_AGG_CASE(1) FEDB_AGG_CASE(2) FEDB_AGG_CASE(3) FEDB_AGG_CASE(4)
+      FEDB_AGG_CASE(5) FEDB_AGG_CASE(6) FEDB_AGG_CASE(7) FEDB_AGG_CASE(8)
+#undef FEDB_AGG_CASE
+      default: fedavg_kernel<false, false, 0><<<blocks, kThreads, 0, s>>>(*d);
+    }
+  }
   FEDB_LAUNCH_OK();
   return 0;
 }

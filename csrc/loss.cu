@@ -6,7 +6,8 @@
 
 namespace {
 
-// one warp per sample; C <= 1024
+// one warp per sample (the entry points accept C <= 4096).  A label outside [0, C) is never dereferenced: the row's loss
+// becomes NaN (torch raises for such a label; a kernel cannot, so the poison value makes it visible in the counters).
 __global__ void __launch_bounds__(128) ce_kernel(const float* __restrict__ logits, const int64_t* __restrict__ target,
                                                 float* __restrict__ dlogits, float* __restrict__ loss_rows,
                                                 float* __restrict__ correct_rows, int B, int C) {
@@ -31,7 +32,9 @@ __global__ void __launch_bounds__(128) ce_kernel(const float* __restrict__ logit
   for (int c = lane; c < C; c += 32) se += expf(z[c] - mx);
   se = warp_sum(se);
   const float lse = logf(se) + mx;
-  const int t = (int)target[row];
+  const long long t64 = target[row];
+  const bool t_ok = t64 >= 0 && t64 < C;
+  const int t = t_ok ? (int)t64 : -1;
   if (dlogits != nullptr) {
     const float invB = 1.f / (float)B;
     for (int c = lane; c < C; c += 32) {
@@ -40,7 +43,7 @@ __global__ void __launch_bounds__(128) ce_kernel(const float* __restrict__ logit
     }
   }
   if (lane == 0) {
-    loss_rows[row] = lse - z[t];
+    loss_rows[row] = t_ok ? lse - z[t] : __int_as_float(0x7fc00000);
     correct_rows[row] = (arg == t) ? 1.f : 0.f;
   }
 }
@@ -124,6 +127,8 @@ extern "C" int fedb_cross_entropy(const float* logits, const int64_t* target, fl
 //    kernels are always given the looked-up pointer.
 // FEDB_CE_STATIC_MAX_ROWS (16384) comes from include/fedb200.h: 2 x 16384 floats = 128 KiB
 #define FEDB_CE_STATIC_MAX_DEVICES 64
+#define FEDB_STR2(x) #x
+#define FEDB_STR(x) FEDB_STR2(x)
 
 static __device__ __align__(256) float g_ce_static_rows[2 * FEDB_CE_STATIC_MAX_ROWS];
 static float* g_ce_static_addr[FEDB_CE_STATIC_MAX_DEVICES] = {nullptr};
@@ -134,7 +139,7 @@ extern "C" int fedb_cross_entropy_static(const float* logits, const int64_t* tar
   FEDB_REQUIRE(B > 0 && C > 0 && C <= 4096, "fedb_cross_entropy_static: bad shape");
   if (B > FEDB_CE_STATIC_MAX_ROWS)
     return fedb_fail(-2, __FILE__, __LINE__,
-                     "fedb_cross_entropy_static: batch exceeds FEDB_CE_STATIC_MAX_ROWS (16384 rows); "
+                     "fedb_cross_entropy_static: batch exceeds FEDB_CE_STATIC_MAX_ROWS (" FEDB_STR(FEDB_CE_STATIC_MAX_ROWS) " rows); "
                      "split the batch or call fedb_cross_entropy");
   int dev = -1;
   FEDB_CHECK(cudaGetDevice(&dev));

@@ -99,6 +99,9 @@ def client_parser() -> argparse.ArgumentParser:
     p.add_argument("--codec", choices=("none", "fp8"), default="none",
                    help="peer plane meaning of -c: none = lossless fp32 words, fp8 = block-scaled e4m3 deltas")
     p.add_argument("--agg-timeout", type=float, default=20.0, help="peer plane: bound of the device-flag waits (s)")
+    p.add_argument("--no-multicast", action="store_true",
+                   help="peer plane: broadcast with unicast peer stores even where NVLS multicast is available")
+    p.add_argument("--dump-root", default=".", help="peer plane: 'dump' descriptors may only write below this directory")
     p.add_argument("--rejoin", action="store_true", help="peer plane: this worker restarts into a running job")
     return p
 
@@ -120,15 +123,15 @@ def client_main(argv=None) -> int:
                          seed=args.seed, augment=args.augment, resume=args.resume, progress=args.progress,
                          checkpoint_path=ckpt.worker_checkpoint_path(args.address))
     wcfg = WorkerConfig(address=args.address, compress=args.compressFlag == "Y", plane=args.plane,
-                        eval_on_send=not args.no_eval)
+                        eval_on_send=not args.no_eval, dump_root=args.dump_root)
     if args.plane == "peer":
         from ..parallel.session import GpuFederation, PeerWorker
         dev = torch.device(device)
         fed = GpuFederation(model=args.model, rank=args.peer_rank, world=args.peer_world,
                             device=dev.index if dev.index is not None else args.peer_rank, dataset=ds, seed=args.seed,
                             tag=args.peer_tag, lr=args.lr, batch_size=args.batch_size, augment=args.augment,
-                            codec=args.codec, use_multicast=False, timeout_ns=int(args.agg_timeout * 1e9),
-                            persistent_server=True, rejoin=args.rejoin)
+                            codec=args.codec, use_multicast=not (args.no_multicast or args.rejoin), timeout_ns=int(args.agg_timeout * 1e9),
+                            persistent_server=True, rejoin=args.rejoin, eval_mode="inline")
         fed.trainer.cfg.checkpoint_path = tcfg.checkpoint_path
         serve_worker(fed.trainer, wcfg, sink=JsonlSink(args.metrics), peer_endpoint=PeerWorker(fed), block=True)
         return 0

@@ -190,11 +190,14 @@ class Coordinator:
                         # pulls the global model out of the primary's peer memory
                         r = list(self.cfg.workers).index(w)
                         remap = desc.encode("remap", rank=r)
-                        for other in self.members.live_workers():
+                        survivors = self.members.live_workers()
+                        for other in survivors:
                             self._send_model_to(other, remap)
                         self.members.readmit(w, ch)
-                        if self.round > 0:
-                            self._send_model_to(w, desc.encode("pull"))
+                        if self.round > 0 and survivors:
+                            # the lowest live rank holds the global model (fedb200/parallel/group.py: _assign_roles)
+                            holder = min(list(self.cfg.workers).index(o) for o in survivors)
+                            self._send_model_to(w, desc.encode("pull", src=holder))
                         self._need_reset = True
                         continue
                     self.members.readmit(w, ch)

@@ -21,6 +21,7 @@ peer-mapped GPU memory and the broadcast lands in this worker's arena without an
 """
 from __future__ import annotations
 
+import os
 import threading
 from dataclasses import dataclass
 from typing import Optional
@@ -42,6 +43,7 @@ class WorkerConfig:
     eval_on_send: bool = True             # N8: evaluate inside SendModel
     write_checkpoint: bool = True         # keep ./checkpoint/<address>.pth current
     checkpoint_root: str = "./checkpoint"
+    dump_root: str = "."                  # "dump" descriptors may only write below this directory
     max_rpc_workers: int = 10
 
 
@@ -90,7 +92,8 @@ class WorkerServicer(proto.TrainerServicer):
             context.abort(grpc.StatusCode.ABORTED, "a local pass is already running")
         try:
             if self.cfg.plane == "peer" and self.peer is not None:
-                st = self.peer.start_round(request.rank, request.world, desc.read_live(context.invocation_metadata()))
+                st = self.peer.start_round(request.rank, request.world, desc.read_live(context.invocation_metadata()),
+                                           round_id=self.round)
             else:
                 st = self.trainer.train(1, request.rank, request.world)
             self.passes += 1
@@ -126,10 +129,19 @@ class WorkerServicer(proto.TrainerServicer):
                     self.peer.remap(int(d["rank"]))
                     return proto.SendModelReply(reply="success")
                 if kind == "pull":
-                    self.peer.pull_global()
+                    self.peer.pull_global(int(d["src"]) if "src" in d else None)
                     return proto.SendModelReply(reply="success")
                 if kind == "dump":
-                    self.peer.dump_global(d["path"])
+                    # the path comes in over an unauthenticated channel: only files below the configured root
+                    root = os.path.realpath(self.cfg.dump_root)
+                    path = os.path.realpath(d["path"])
+                    if os.path.commonpath([root, path]) != root:
+                        context.abort(grpc.StatusCode.PERMISSION_DENIED, f"dump path outside {root}")
+                    self.peer.dump(path, what=d.get("what", "global"))
+                    return proto.SendModelReply(reply="success")
+                if kind == "status":
+                    self.sink.write("peer_status", address=self.cfg.address, round=self.round, term=self.term,
+                                    **self.peer.status())
                     return proto.SendModelReply(reply="success")
                 if kind != "global":
                     context.abort(grpc.StatusCode.INVALID_ARGUMENT, f"unexpected descriptor {d}")

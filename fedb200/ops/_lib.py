@@ -44,6 +44,7 @@ class AggDesc(C.Structure):
         ("sync_mode", C.c_int32), ("rank", C.c_int32), ("world", C.c_int32),
         ("ctrl_local", vp), ("ctrl_peer", vp * MAX_PEERS),
         ("timeout_ns", C.c_uint64), ("version", C.c_uint32), ("dst_ctrl", vp * MAX_DST),
+        ("gate", vp),
     ]
 
 
@@ -71,6 +72,7 @@ _SIGS = {
                                  C.c_float, vp, vp]),
     "fedb_cross_entropy": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_int, vp]),
     "fedb_prepare_batch": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, C.c_uint64, vp]),
+    "fedb_prepare_batch_dev": (C.c_int, [vp, vp, C.c_int, C.c_int, C.c_int, C.c_uint64, vp, vp]),
     "fedb_lenet_workspace_bytes": (C.c_size_t, [C.c_int]),
     "fedb_lenet_eval_bytes": (C.c_size_t, [C.c_int]),
     "fedb_lenet_train_step": (C.c_int, [C.POINTER(LeNetDesc), vp, vp, C.c_int, vp, vp, C.c_uint64, vp]),

@@ -34,7 +34,7 @@ def fedavg_raw(src_f32: Sequence[int], dst_f32: Sequence[int], begin: int, end: 
                src_q: Sequence[int] = (), src_scale: Sequence[int] = (), base: int = 0,
                mc_src: int = 0, mc_dst: int = 0, sync_mode: int = 0, rank: int = 0, world: int = 1,
                ctrl_peer: Sequence[int] = (), timeout_ns: int = DEFAULT_TIMEOUT_NS, version: int = 0,
-               dst_ctrl: Sequence[int] = (), max_blocks: int = 0, stream: Optional[int] = None) -> None:
+               dst_ctrl: Sequence[int] = (), max_blocks: int = 0, stream: Optional[int] = None, gate: int = 0) -> None:
     """Pointer-level entry (addresses as ints): used by the peer plane where sources and destinations
     are mappings of other processes' memory."""
     d = AggDesc()
@@ -71,6 +71,7 @@ def fedavg_raw(src_f32: Sequence[int], dst_f32: Sequence[int], begin: int, end: 
     d.base, d.mc_src, d.mc_dst = base, mc_src, mc_dst
     d.sync_mode, d.rank, d.world = sync_mode, rank, world
     d.ctrl_local, d.timeout_ns, d.version = ctrl_local, timeout_ns, version
+    d.gate = gate
     check(lib().fedb_fedavg(C.byref(d), max_blocks, current_stream() if stream is None else stream), "fedb_fedavg")
     _lib.count_launch()
 
@@ -200,11 +201,13 @@ def cross_entropy(logits, target):
 
 
 # ------------------------------------------------------------------------------------ K14
-def prepare_batch(images_u8: torch.Tensor, nhwc: bool = False, augment: bool = False, seed: int = 0) -> torch.Tensor:
+def prepare_batch(images_u8: torch.Tensor, nhwc: bool = False, augment: bool = False, seed: int = 0,
+                  seed_dev: Optional[torch.Tensor] = None) -> torch.Tensor:
+    """``seed_dev``: int64 device word mixed into the seed at run time (stays live across CUDA-graph replays)."""
     B = images_u8.shape[0]
     out = torch.empty((B, 32, 32, 3) if nhwc else (B, 3, 32, 32), dtype=torch.float32, device=images_u8.device)
-    check(lib().fedb_prepare_batch(images_u8.data_ptr(), out.data_ptr(), B, int(nhwc), int(augment), seed,
-                                   current_stream()), "fedb_prepare_batch")
+    check(lib().fedb_prepare_batch_dev(images_u8.data_ptr(), out.data_ptr(), B, int(nhwc), int(augment), seed,
+                                       ptr(seed_dev), current_stream()), "fedb_prepare_batch_dev")
     _lib.count_launch()
     return out.permute(0, 3, 1, 2) if nhwc else out
 
@@ -268,9 +271,18 @@ class LeNetPlan:
             self._aux_cap = B
         return self._aux_workspace
 
-    def eval_batch(self, images_u8: torch.Tensor, labels: torch.Tensor, stats: Optional[torch.Tensor] = None) -> None:
+    def bind_eval_params(self, f32: torch.Tensor) -> None:
+        """Evaluation reads its weights from ``f32`` (same layout as the arena) instead of the live arena: the snapshot
+        of a global model that is scored on a second stream while the next local pass already trains the arena."""
+        d = LeNetDesc()
+        C.memmove(C.byref(d), C.byref(self.desc), C.sizeof(LeNetDesc))
+        d.param = f32.data_ptr()
+        self._eval_desc, self._eval_params = d, f32
+
+    def eval_batch(self, images_u8: torch.Tensor, labels: torch.Tensor, stats: Optional[torch.Tensor] = None,
+                   snapshot: bool = False) -> None:
         B = images_u8.shape[0]
-        check(lib().fedb_lenet_eval(C.byref(self.desc), images_u8.data_ptr(), labels.data_ptr(), B,
+        check(lib().fedb_lenet_eval(C.byref(self._eval_desc if snapshot else self.desc), images_u8.data_ptr(), labels.data_ptr(), B,
                                     self._eval_ws(B).data_ptr(), ptr(self.stats if stats is None else stats),
                                     current_stream()), "fedb_lenet_eval")
         _lib.count_launch(2)

@@ -58,6 +58,9 @@ class CudaEngine:
         self._slot = 0                    # half of the exchange double buffer that holds / receives the current round's set
         self._tex_on = False
         self._eval_graph = None
+        self.snap = None                  # snapshot arena scored by the off-critical-path evaluation
+        self.eval_model = None
+        self.eval_stream = None
         self.h2d_bytes_last = 0
         self.d2h_bytes_last = 0
         self.seed_dev = torch.zeros(1, dtype=torch.int64, device=self.dev)
@@ -80,6 +83,35 @@ class CudaEngine:
                 self.stats = self.plan.stats
             else:
                 self.stats = torch.zeros(4, dtype=torch.float32, device=self.dev)
+            if self.snap is not None and self.is_lenet:
+                self.plan.bind_eval_params(self.snap.f32)
+
+    # ------------------------------------------------------------------ evaluation off the critical path
+    def enable_snapshot_eval(self) -> None:
+        """Evaluation of a round's global model from a private copy on a second stream, so that the next local pass
+        (which overwrites the arena) does not have to wait for it.  The reference evaluates inside ``SendModel``
+        (src/client.py:30, src/main.py:167-191), i.e. on the round's critical path; the same 10,000 images are still
+        scored on every client every round here, only concurrently with the next round's training."""
+        if self.snap is not None:
+            return
+        from .. import models
+        from ..parallel.arena import Arena
+        with torch.cuda.device(self.dev):
+            if self.is_lenet:
+                self.snap = Arena(self.arena.manifest, self.dev)
+                self.plan.bind_eval_params(self.snap.f32)
+            else:
+                self.eval_model = models.build(self.cfg.model).to(self.dev)
+                self.snap = Arena.adopt(self.eval_model, self.dev)
+                self.eval_model.eval()
+            self.eval_stream = torch.cuda.Stream(device=self.dev)
+            self.eval_copy_stream = torch.cuda.Stream(device=self.dev)
+            self.eval_stats_prev = torch.zeros(4, dtype=torch.float32, device=self.dev)
+        self._eval_graph = None
+
+    def snapshot(self) -> None:
+        """arena -> snapshot on the current stream (one K-BCAST launch over local memory)."""
+        K.broadcast(self.arena, [self.snap])
 
     # ------------------------------------------------------------------ data staging
     def _shard(self, batches: List[int]) -> dict:
@@ -111,7 +143,7 @@ class CudaEngine:
         _lib.check(_lib.lib().fedb_copy_async(dst.data_ptr() + lo * row, src.data_ptr() + lo * row, (hi - lo) * row,
                                               stream.cuda_stream), "fedb_copy_async")
 
-    def _streamed(self, pairs, bounds: List[int], work, upload: bool, tail=None) -> None:
+    def _streamed(self, pairs, bounds: List[int], work, upload: bool, tail=None, side=None) -> None:
         """Runs work(i) for every chunk i = rows [bounds[i], bounds[i+1]) on the current stream.  With ``upload`` the
         rows of every (device, pinned) pair are first copied H2D chunk by chunk on the copy stream, and work(i) waits
         for chunk i only; ``tail()`` then queues further copies behind them (they finish under the remaining work).
@@ -121,7 +153,7 @@ class CudaEngine:
             for i in range(len(bounds) - 1):
                 work(i)
             return
-        side = self.copy_stream
+        side = self.copy_stream if side is None else side
         side.wait_stream(cur)                                         # fork
         ready = []
         for i in range(len(bounds) - 1):
@@ -207,7 +239,7 @@ class CudaEngine:
 
     def _generic_step(self, x_u8, y, seed):
         a, cfg = self.arena, self.cfg
-        x = K.prepare_batch(x_u8, nhwc=True, augment=cfg.augment, seed=seed)
+        x = K.prepare_batch(x_u8, nhwc=True, augment=cfg.augment, seed=seed, seed_dev=self.seed_dev)
         a.grad.zero_()
         out = self.t.model(x)
         dlogits = torch.empty_like(out)
@@ -274,7 +306,7 @@ class CudaEngine:
         return st
 
     # ---- pipelined result read-back: the copy is enqueued with the round, the host reads it one round later
-    def enqueue_round_stats(self, status_word: Optional[torch.Tensor] = None):
+    def enqueue_round_stats(self, status_word: Optional[torch.Tensor] = None, eval_src: Optional[torch.Tensor] = None):
         """Queues the D2H copy of this round's counters (train 4 + eval 4 floats, plus an optional int32 status word
         such as the K-AGG flag status) into a pinned slot and returns a ticket for ``fetch_round_stats``.  Nothing
         blocks here, so the next round can be enqueued while this one still runs."""
@@ -286,7 +318,7 @@ class CudaEngine:
         self._ring_next = (self._ring_next + 1) % len(self._ring)
         with torch.cuda.device(self.dev):
             buf[:4].copy_(self.stats, non_blocking=True)
-            buf[4:].copy_(self.eval_stats, non_blocking=True)
+            buf[4:].copy_(self.eval_stats if eval_src is None else eval_src, non_blocking=True)
             if status_word is not None:
                 st.copy_(status_word, non_blocking=True)
             else:
@@ -302,6 +334,8 @@ class CudaEngine:
 
     def read_round_stats(self):
         """Train + eval counters of a round in ONE pinned D2H copy (32 bytes) and one sync."""
+        if self.eval_stream is not None:
+            torch.cuda.current_stream(self.dev).wait_stream(self.eval_stream)
         self._pinned_stats[:4].copy_(self.stats, non_blocking=True)
         self._pinned_stats[4:].copy_(self.eval_stats, non_blocking=True)
         torch.cuda.current_stream(self.dev).synchronize()
@@ -309,14 +343,16 @@ class CudaEngine:
         return self._to_stats(self._pinned_stats[:4]), self._to_stats(self._pinned_stats[4:])
 
     # ------------------------------------------------------------------ evaluation pass
-    def eval_pass(self, upload: bool = True, sync: bool = True, chunk: int = 2000):
+    def eval_pass(self, upload: bool = True, sync: bool = True, chunk: int = 2000, snapshot: bool = False):
         """Evaluation of the current model on the whole test set.  ``upload`` copies the test set H2D first, in chunks
         that overlap the evaluation kernels - unless the preceding ``train_pass(with_test=True)`` of this round already
         brought it over, in which case the pass is a single launch over the resident copy."""
         with torch.cuda.device(self.dev):
-            self.t.model.eval()
+            model = self.eval_model if (snapshot and self.eval_model is not None) else self.t.model
+            model.eval()
             ds = self.t.dataset
             pairs = self._test_buffers()
+            side = self.eval_copy_stream if snapshot else None
             copy = bool(upload) and not self._test_resident
             self._test_resident = False
             if copy:
@@ -331,21 +367,21 @@ class CudaEngine:
 
                 def work(c):
                     lo, hi = bounds[c], bounds[c + 1]
-                    self.plan.eval_batch(imgs[lo:hi], self._test_dev[1][lo:hi], self.eval_stats)
+                    self.plan.eval_batch(imgs[lo:hi], self._test_dev[1][lo:hi], self.eval_stats, snapshot=snapshot)
 
                 graphs = self._eval_graph if self._eval_graph is not None else {}
                 self._eval_graph = graphs
-                gkey = (copy, self._slot)
+                gkey = (copy, self._slot, snapshot)
                 if self.cfg.use_cuda_graph and gkey in graphs:
                     graphs[gkey].replay()
                     _lib.count_launch(2 * (len(bounds) - 1))
                 else:
-                    self._streamed(pairs, bounds, work, copy)
+                    self._streamed(pairs, bounds, work, copy, side=side)
                     if self.cfg.use_cuda_graph:
                         torch.cuda.synchronize(self.dev)
                         g = torch.cuda.CUDAGraph()
                         with _quiet_gc(), torch.cuda.graph(g, stream=torch.cuda.Stream(device=self.dev)):
-                            self._streamed(pairs, bounds, work, copy)
+                            self._streamed(pairs, bounds, work, copy, side=side)
                         graphs[gkey] = g
             else:
                 # eval-mode results do not depend on the batch size (BN uses running statistics): evaluate in batches of
@@ -358,21 +394,21 @@ class CudaEngine:
                 def work(c):
                     lo, hi = bounds[c], bounds[c + 1]
                     x = K.prepare_batch(imgs[lo:hi], nhwc=True)
-                    out = self.t.model(x)
+                    out = model(x)
                     K.cross_entropy_raw(out.contiguous(), self._test_dev[1][lo:hi], None, None, self.eval_stats)
 
                 graphs = self._eval_graph if self._eval_graph is not None else {}
                 self._eval_graph = graphs
-                gkey = (copy, self._slot)                    # graph key: which half of the double buffer is read
+                gkey = (copy, self._slot, snapshot)          # graph key: which half of the double buffer is read
                 with torch.no_grad():
                     if self.cfg.use_cuda_graph and gkey in graphs:
                         graphs[gkey].replay()
                     else:
-                        self._streamed(pairs, bounds, work, copy)
+                        self._streamed(pairs, bounds, work, copy, side=side)
                         if self.cfg.use_cuda_graph:
                             torch.cuda.synchronize(self.dev)
                             g = torch.cuda.CUDAGraph()
                             with _quiet_gc(), torch.cuda.graph(g, stream=torch.cuda.Stream(device=self.dev)):
-                                self._streamed(pairs, bounds, work, copy)
+                                self._streamed(pairs, bounds, work, copy, side=side)
                             graphs[gkey] = g
             return self.read_stats("eval") if sync else None

@@ -37,8 +37,12 @@ class FedGroup:
         self.device = trainer.device.index or 0
         self.man = trainer.arena.manifest
         self.codec, self.nvls_reduce, self.repl_mode = codec, nvls_reduce, repl_mode
-        self.primary_rank = primary_rank
-        self.backup_rank = (primary_rank + 1) % world if backup_rank is None else backup_rank
+        # roles follow the membership: the preferred ranks hold the global model / the replica while they are alive,
+        # otherwise the two lowest live ranks do (the reference re-admits ANY worker, src/server.py:78-101, so no rank
+        # may be special); see _assign_roles
+        self._pref_primary = primary_rank
+        self._pref_backup = (primary_rank + 1) % world if backup_rank is None else backup_rank
+        self.primary_rank, self.backup_rank = self._pref_primary, self._pref_backup
         self.timeout_ns = timeout_ns
         self.layout = PeerLayout.for_manifest(self.man, with_codec=True)
         torch.cuda.set_device(self.device)
@@ -61,6 +65,7 @@ class FedGroup:
         self._side_ctrl = K.new_ctrl(trainer.device)      # completion counter of the side-stream copy kernel
         self._common_base = False
         self._repl_pending = False
+        self._remapped = False            # a restarted peer's new memory is not bound to the multicast object
         if codec == "fp8":
             dev = trainer.device
             self.residual = torch.zeros(self.man.n_f32, dtype=torch.float32, device=dev)
@@ -81,6 +86,19 @@ class FedGroup:
     def set_live(self, live: Sequence[int]) -> None:
         """Membership change: only these ranks take part in (and are averaged by) the next rounds."""
         self.live = sorted(live)
+        self._assign_roles()
+
+    def _assign_roles(self) -> None:
+        """Who keeps the server's global model (aux arena of ``primary_rank``) and its replica (``backup_rank``): the
+        preferred ranks while they are live, else the lowest live ranks.  Every rank derives the same answer from the
+        same live list, and the holder refreshes both copies from its own client arena right after each K-AGG, so a
+        newly appointed holder is up to date after the first committed round of its tenure."""
+        lv = self.live
+        if not lv:
+            return
+        self.primary_rank = self._pref_primary if self._pref_primary in lv else lv[0]
+        rest = [r for r in lv if r != self.primary_rank]
+        self.backup_rank = (self._pref_backup if self._pref_backup in rest else rest[0]) if rest else self.primary_rank
 
     # ------------------------------------------------------------------ one aggregation
     def aggregate(self, weights: Optional[Sequence[float]] = None) -> None:
@@ -101,7 +119,7 @@ class FedGroup:
         if fused_repl:
             dst.append(bufs[self.backup_rank].aux_f32_ptr())
             dst_i64.append(bufs[self.backup_rank].aux_i64_ptr())
-        mc_dst = self.peers.mc_client_f32_ptr() if len(live) == self.world else 0
+        mc_dst = self.peers.mc_client_f32_ptr() if (len(live) == self.world and not self._remapped) else 0
         if not mc_dst:
             dst += [bufs[r].client_f32_ptr() for r in live]
         dst_i64 += [bufs[r].client_i64_ptr() for r in live]
@@ -141,7 +159,8 @@ class FedGroup:
             with torch.cuda.stream(self.side_stream):
                 K.fedavg_raw([me_buf.client_f32_ptr()], d32, 0, self.man.n_f32, ctrl_local=self._side_ctrl.data_ptr(),
                              src_i64=[me_buf.client_i64_ptr()], dst_i64=d64, n_i64=self.man.n_i64,
-                             version=self.round, dst_ctrl=[0] + ([bk.ctrl_ptr] if to_replica else []))
+                             version=self.round, dst_ctrl=[0] + ([bk.ctrl_ptr] if to_replica else []),
+                             gate=self.peers.me.ctrl_ptr + _lib.CTRL_OFF["status"])   # a failed K-AGG copies nothing
             self._repl_done.record(self.side_stream)
             self._repl_pending = True
 
@@ -173,13 +192,24 @@ class FedGroup:
         """A restarted worker re-joined with a fresh allocation: map it (worker re-admission)."""
         torch.cuda.synchronize(self.device)
         self.peers.remap(r)
+        self._remapped = True             # from now on the fan-out uses unicast peer stores (the NVLS alias still
+                                          # reaches the dead process's pages for that rank)
 
-    def pull_global(self) -> None:
-        """Newcomer side of re-admission: copy the server's global model out of the primary's peer memory into
-        this worker's arena (what the reference does by re-sending the checkpoint, src/server.py:92-97)."""
-        if self.peers.buffers[self.primary_rank].base == 0:
-            raise _lib.FedbError("the primary's memory is not mapped here")
-        K.broadcast(self.global_arena, [self.trainer.arena])
+    def pull_global(self, src: Optional[int] = None) -> None:
+        """Newcomer side of re-admission: copy the server's global model out of the holder's peer memory into
+        this worker's arena (what the reference does by re-sending the checkpoint, src/server.py:92-97).  ``src``: the
+        rank that holds the global model right now (the coordinator names it; default: this rank's view)."""
+        src = self.primary_rank if src is None else int(src)
+        if self.peers.buffers[src].base == 0:
+            raise _lib.FedbError(f"the memory of rank {src} (holder of the global model) is not mapped here")
+        # also into this rank's own aux arena: should the roles fall to this rank before the next committed round, it
+        # already holds a valid global model for the next newcomer
+        K.broadcast(self.peers.buffers[src].aux_arena(self.man), [self.trainer.arena, self.peers.me.aux_arena(self.man)])
+        if self.codec == "fp8":
+            # the pulled model IS the common base of the next round's deltas (the survivors hold the same one)
+            self.base.copy_(self.trainer.arena.f32[:self.man.n_f32])
+            self.residual.zero_()
+            self._common_base = True
         torch.cuda.synchronize(self.device)
 
     def abort(self) -> None:

@@ -115,6 +115,39 @@ def supported(device: int = 0):
     return bool(vmm.value), bool(fd_ok.value), bool(mc.value)
 
 
+def fs_min_barrier(sock_dir: str, tag: str, rank: int, world: int, timeout_s: float = 120.0):
+    """all-reduce(MIN) of a 0/1 flag over files in ``sock_dir`` - the rendezvous of processes that share a box but no
+    torch.distributed group (gRPC-driven workers).  Returns ``fn(flag_tensor)`` with the same contract as the
+    torch.distributed version used by torchrun jobs; every call is a new stage."""
+    import time
+    stage = [0]
+
+    def fn(flag: torch.Tensor) -> None:
+        stage[0] += 1
+        mine = os.path.join(sock_dir, f"fedb200-{tag}-bar{stage[0]}-{rank}")
+        with open(mine + ".tmp", "w") as f:
+            f.write(str(int(flag.item())))
+        os.replace(mine + ".tmp", mine)
+        end = time.time() + timeout_s
+        vals = {}
+        while len(vals) < world:
+            for r in range(world):
+                if r in vals:
+                    continue
+                try:
+                    with open(os.path.join(sock_dir, f"fedb200-{tag}-bar{stage[0]}-{r}")) as f:
+                        vals[r] = int(f.read().strip() or 0)
+                except (OSError, ValueError):
+                    pass
+            if len(vals) < world:
+                if time.time() > end:
+                    vals = {r: 0 for r in range(world)}       # somebody never showed up: nobody uses the feature
+                    break
+                time.sleep(0.01)
+        flag.fill_(min(vals.values()))
+    return fn
+
+
 class PeerGroup:
     """All ranks' allocations mapped here.  ``buffers[r]`` is rank r's memory; ``mc_base`` is the
     multicast alias of the whole layout (0 when NVLS is unavailable or disabled)."""
@@ -132,7 +165,9 @@ class PeerGroup:
         self.mc = None
         self.mc_base = 0
         vmm, fd_ok, mc_ok = supported(device)
-        want_mc = bool(use_multicast and mc_ok and world > 1)
+        want_mc = bool(use_multicast and mc_ok and world > 1 and not rejoin)
+        if want_mc and barrier is None:
+            barrier = fs_min_barrier(sock_dir, tag, rank, world)
         path = lambda r: os.path.join(sock_dir, f"fedb200-{tag}-{r}.sock")   # noqa: E731
 
         fds = [self.local.fd]

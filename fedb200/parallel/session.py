@@ -99,10 +99,17 @@ class GpuFederation:
     def __init__(self, model: str = "LeNet", rank: int = 0, world: int = 1, device: Optional[int] = None,
                  dataset: Optional[D.ImageDataset] = None, seed: Optional[int] = None, tag: Optional[str] = None,
                  lr: float = 0.1, batch_size: int = 128, augment: bool = False, evaluate: bool = True,
-                 test_allgather: Optional[bool] = None, **group_kw):
+                 test_allgather: Optional[bool] = None, eval_mode: str = "overlap", **group_kw):
+        """``eval_mode``: where the evaluation of a round's global model runs (every client scores the whole test set
+        every round in all modes, N8).  "overlap" (default): on a second stream, from a snapshot of the global model,
+        concurrently with the next round's local pass - ``run_round_async`` then reports it one round late;
+        "inline": on the round's critical path, as the reference does (src/client.py:30)."""
         device = rank if device is None else device
         torch.cuda.set_device(device)
+        if eval_mode not in ("overlap", "inline"):
+            raise ValueError(f"eval_mode {eval_mode!r} (overlap | inline)")
         self.rank, self.world, self.evaluate = rank, world, evaluate
+        self.eval_mode = eval_mode if evaluate else "inline"
         ds = dataset if dataset is not None else D.synthetic_cifar(seed=0)
         cfg = TrainerConfig(model=model, lr=lr, batch_size=batch_size, device=f"cuda:{device}",
                             seed=(rank if seed is None else seed), augment=augment)
@@ -111,6 +118,10 @@ class GpuFederation:
         tag = tag or os.environ.get("MASTER_PORT", "solo") + f"-{os.getppid()}"
         self.group = FedGroup(self.trainer, rank, world, tag, dist_barrier=dist_min_barrier(), **group_kw)
         self.rounds = 0
+        self._eval_done = None            # event: the overlapped evaluation of the previous round has finished
+        self._eval_round = 0              # round whose global model the newest finished/enqueued evaluation scores
+        if self.eval_mode == "overlap":
+            self.engine.enable_snapshot_eval()
         # evaluation-set all-gather over NVLink: on by default for rank-symmetric multi-GPU sessions (torchrun); workers
         # that may be restarted one by one (gRPC plane: persistent_server / rejoin) keep the plain per-rank upload
         if test_allgather is None:
@@ -126,15 +137,20 @@ class GpuFederation:
                 self.engine.set_test_exchange(self.exchange)
 
     def run_round(self, upload: bool = True, sync: bool = True):
-        """One federated round.  Returns (train_stats, eval_stats) when ``sync``; with ``sync=False``
-        everything is only enqueued (device-timed benchmarking)."""
+        """One federated round.  Returns (train_stats, eval_stats) of THIS round when ``sync`` (an overlapped evaluation is
+        waited for); with ``sync=False`` everything is only enqueued (device-timed benchmarking)."""
         live = self.group.live
         batches = self.trainer.shard(live.index(self.rank), self.world) if self.rank in live else []
         self.group.before_local_pass()
         self.engine.train_pass(batches, upload=upload, sync=False, with_test=self.evaluate)
+        if self.eval_mode == "overlap":
+            self._join_eval(keep=True)
         self.group.aggregate()
         if self.evaluate:
-            self.engine.eval_pass(upload=upload, sync=False)
+            if self.eval_mode == "overlap":
+                self._launch_overlapped_eval(upload)
+            else:
+                self.engine.eval_pass(upload=upload, sync=False)
         self.rounds += 1
         if not sync:
             return None
@@ -142,14 +158,88 @@ class GpuFederation:
         self.group.check()
         return out
 
+    # ---- evaluation on a second stream (eval_mode="overlap")
+    def _join_eval(self, keep: bool = False) -> None:
+        """The main stream waits for the previous round's evaluation.  In steady state it ended long ago (it is a
+        fraction of a local pass); the wait is what makes it safe to overwrite the snapshot and, two rounds later, the
+        half of the test-set double buffer it read - a rank only announces itself to K-AGG after this point.  ``keep``
+        parks the finished counters so that the round's result copy can pick them up."""
+        if self._eval_done is None:
+            return
+        cur = torch.cuda.current_stream(self.engine.dev)
+        cur.wait_event(self._eval_done)
+        if keep:
+            self.engine.eval_stats_prev.copy_(self.engine.eval_stats, non_blocking=True)
+
+    def _launch_overlapped_eval(self, upload: bool) -> None:
+        eng = self.engine
+        cur = torch.cuda.current_stream(eng.dev)
+        eng.snapshot()                                   # the new global model, before the next pass trains on it
+        if self._eval_done is None:
+            self._eval_done, self._snap_ready = torch.cuda.Event(), torch.cuda.Event()
+        self._snap_ready.record(cur)
+        with torch.cuda.stream(eng.eval_stream):
+            eng.eval_stream.wait_event(self._snap_ready)
+            eng.eval_pass(upload=upload, sync=False, snapshot=True)
+            self._eval_done.record(eng.eval_stream)
+
+    def drain(self, sync: bool = True):
+        """Waits (on the stream; on the host too when ``sync``) for the evaluation that is still in flight and returns
+        its statistics: the score of the LAST round's global model."""
+        if self.eval_mode == "overlap":
+            self._join_eval(keep=True)
+        if not sync:
+            return None
+        torch.cuda.current_stream(self.engine.dev).synchronize()
+        return self.engine.read_stats("eval")
+
     def run_round_async(self, upload: bool = True) -> "RoundHandle":
         """One federated round, enqueued only.  The round's loss / accuracy counters and the K-AGG status travel to a
         pinned slot at the end of the round; ``handle.result()`` waits for exactly that copy.  Calling it after the
-        NEXT round has been enqueued keeps the GPU busy across the round boundary (up to three rounds may be in flight)."""
+        NEXT round has been enqueued keeps the GPU busy across the round boundary (up to three rounds may be in flight).
+        With ``eval_mode="overlap"`` the evaluation half of the result is the one that finished last, i.e. the score of
+        the PREVIOUS round's global model (``handle.eval_round``; zero samples for the first round); ``drain()``
+        returns the last one."""
         self.run_round(upload=upload, sync=False)
         c = self.group.peers.me.ctrl()
         off = _lib.CTRL_OFF["status"] // 4
-        return RoundHandle(self, self.engine.enqueue_round_stats(c[off:off + 1]))
+        lag = self.eval_mode == "overlap"
+        h = RoundHandle(self, self.engine.enqueue_round_stats(c[off:off + 1],
+                                                              eval_src=self.engine.eval_stats_prev if lag else None))
+        h.round, h.eval_round = self.rounds, self.rounds - 1 if lag else self.rounds
+        return h
+
+    def aggregation_selfcheck(self, all_gather=None) -> dict:
+        """Proof that the multi-GPU aggregation did what the reference's allreduce() does (src/server.py:155-179), for
+        hosts that cannot look into the GPUs: one extra local pass, the pre-aggregation arenas of ALL ranks are gathered
+        (``all_gather(tensor) -> list of tensors``, e.g. over torch.distributed), K-AGG runs, and (i) the result is
+        compared bit for bit with the CPU oracle fed with the gathered arenas, (ii) a 64-bit checksum of every rank's
+        fp32 + int64 arena is compared across ranks.  Lossless codec only (fp8 deltas are not bit-exact by design)."""
+        from .fedavg import fedavg_flat_cpu
+        man = self.group.man
+        live = self.group.live
+        batches = self.trainer.shard(live.index(self.rank), self.world)
+        self.group.before_local_pass()
+        self.engine.train_pass(batches, upload=False, sync=False, with_test=False)
+        if self.eval_mode == "overlap":
+            self._join_eval()
+        torch.cuda.synchronize()
+        a = self.trainer.arena
+        pre32, pre64 = a.f32[:man.n_f32].clone(), a.i64[:man.n_i64].clone()
+        gather = all_gather if all_gather is not None else (lambda t: [t])
+        all32 = [t.cpu() for t in gather(pre32)]
+        all64 = [t.cpu() for t in gather(pre64)] if man.n_i64 else [pre64.cpu() for _ in all32]
+        self.group.aggregate()
+        torch.cuda.synchronize()
+        self.group.check()
+        post32, post64 = a.f32[:man.n_f32].clone(), a.i64[:man.n_i64].clone()
+        want32, want64 = torch.empty(man.n_f32), torch.empty(man.n_i64, dtype=torch.int64)
+        fedavg_flat_cpu(all32, all64, None, want32, want64)
+        exact = torch.equal(post32.cpu(), want32) and torch.equal(post64.cpu(), want64)
+        chk = (post32.view(torch.int32).to(torch.int64).sum() + post64.sum()).reshape(1)
+        sums = [int(t) for t in gather(chk)]
+        return {"agg_check": "bit-exact" if exact else "failed", "arenas_equal": len(set(sums)) == 1,
+                "ranks_gathered": len(all32), "checksum": sums[0]}
 
     def h2d_bytes_per_round(self) -> int:
         return self.engine.h2d_bytes_last
@@ -187,11 +277,15 @@ class PeerWorker:
         self.name = f"rank{fed.rank}"
         self.device = fed.trainer.device
 
-    def start_round(self, rank: int, world: int, live=None):
+    def start_round(self, rank: int, world: int, live=None, round_id=None):
         torch.cuda.set_device(self.device)
         fed = self.fed
         if live is not None:
             fed.group.set_live(live)
+        if round_id is not None:
+            # the replica's version stamp is the COORDINATOR's round number (+1 = rounds committed once this one is),
+            # not a per-rank launch count: a round that failed and was re-run must not advance it twice
+            fed.group.round = int(round_id)
         batches = fed.trainer.shard(rank, world)
         fed.group.before_local_pass()
         st = fed.engine.train_pass(batches, upload=True, sync=True, with_test=True)
@@ -201,6 +295,7 @@ class PeerWorker:
     def finish_round(self, evaluate: bool = True):
         torch.cuda.set_device(self.device)
         torch.cuda.current_stream(self.device).synchronize()
+        self.fed.group.side_stream.synchronize()     # holder: global model + replica of this round are complete
         self.fed.group.check()                       # raises FedbError when a peer never showed up
         return self.fed.engine.eval_pass(upload=True, sync=True) if evaluate else None
 
@@ -212,13 +307,29 @@ class PeerWorker:
         torch.cuda.set_device(self.device)
         self.fed.group.remap_peer(r)
 
-    def pull_global(self) -> None:
+    def pull_global(self, src=None) -> None:
         torch.cuda.set_device(self.device)
-        self.fed.group.pull_global()
+        self.fed.group.pull_global(src)
 
-    def dump_global(self, path: str) -> None:
-        """Writes the server's global model (primary's aux arena) as a reference-format checkpoint."""
+    def dump(self, path: str, what: str = "global") -> None:
+        """Writes the server's global model (aux arena of the current holder) or, ``what="client"``, this worker's own
+        arena as a reference-format checkpoint."""
         from ..utils import checkpoint as ckpt
         torch.cuda.set_device(self.device)
         torch.cuda.synchronize(self.device)
-        ckpt.save_checkpoint(path, self.fed.group.global_arena.state_dict(to_cpu=True), acc=1, epoch=1)
+        arena = self.fed.group.global_arena if what == "global" else self.fed.trainer.arena
+        ckpt.save_checkpoint(path, arena.state_dict(to_cpu=True), acc=1, epoch=1)
+
+    dump_global = dump
+
+    def status(self) -> dict:
+        """Roles, replica version and a checksum of this worker's arena (one small D2H read): what an operator - or
+        tools/grpc_gpu_check.py - needs to see that the data plane followed a membership change."""
+        torch.cuda.set_device(self.device)
+        torch.cuda.synchronize(self.device)
+        g = self.fed.group
+        a = self.fed.trainer.arena
+        chk = int(a.f32[:g.man.n_f32].view(torch.int32).to(torch.int64).sum()) + (int(a.i64.sum()) if g.man.n_i64 else 0)
+        return {"rank": g.rank, "primary_rank": g.primary_rank, "backup_rank": g.backup_rank, "live": list(g.live),
+                "replica_version": K.ctrl_field(g.peers.me.ctrl(), "version"), "arena_checksum": chk,
+                "multicast": bool(g.peers.mc_base) and not g._remapped, "agg_round": g.round}

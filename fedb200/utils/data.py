@@ -42,16 +42,32 @@ class ImageDataset:
 
 
 def synthetic_cifar(n_train: int = 50000, n_test: int = 10000, seed: int = 0,
-                    pad_from: Optional[int] = None, classes: int = 10) -> ImageDataset:
+                    pad_from: Optional[int] = None, classes: int = 10, learnable: bool = False,
+                    signal: float = 0.35) -> ImageDataset:
     """Seeded CIFAR-shaped data.  ``pad_from=28`` draws 28x28 images and zero-pads them to 32x32
-    (BASELINE config 1: LeNet needs 3x32x32)."""
+    (BASELINE config 1: LeNet needs 3x32x32).
+
+    ``learnable``: class-conditional images - every class has a smooth random pattern (an 8x8 field, bilinearly
+    enlarged) that is mixed into per-pixel noise with weight ``signal`` - so that a few federated rounds move the
+    accuracy well above chance and accuracy COMPARISONS between two runs mean something (the accuracy gate of the
+    lossy codec, tools/codec_gate.py).  The default keeps the byte-identical data of the benchmarks (uniform noise
+    with labels from a random linear probe, which a small CNN barely learns)."""
     g = torch.Generator().manual_seed(seed)
     side = pad_from or 32
     probe = torch.randn(3 * side * side, classes, generator=g)
+    if learnable:
+        coarse = torch.randn(classes, 3, 8, 8, generator=g)
+        pattern = torch.nn.functional.interpolate(coarse, size=(side, side), mode="bilinear", align_corners=False)
+        pattern = pattern.permute(0, 2, 3, 1).contiguous()                 # [classes, side, side, 3]
 
     def draw(n):
-        x = torch.randint(0, 256, (n, side, side, 3), dtype=torch.uint8, generator=g)
-        y = ((x.reshape(n, -1).float() / 255.0 - 0.5) @ probe).argmax(1)
+        if learnable:
+            y = torch.randint(0, classes, (n,), generator=g)
+            noise = torch.randn(n, side, side, 3, generator=g)
+            x = (127.5 + 64.0 * (signal * pattern[y] + noise)).clamp_(0, 255).to(torch.uint8)
+        else:
+            x = torch.randint(0, 256, (n, side, side, 3), dtype=torch.uint8, generator=g)
+            y = ((x.reshape(n, -1).float() / 255.0 - 0.5) @ probe).argmax(1)
         if side != 32:
             lo = (32 - side) // 2
             full = torch.zeros(n, 32, 32, 3, dtype=torch.uint8)

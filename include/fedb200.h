@@ -2,8 +2,9 @@
  *
  * Conventions: every function returns 0 on success, a non-zero code otherwise, and leaves a
  * human-readable message in fedb_last_error().  `stream` is a cudaStream_t passed as void*.
- * All pointers are device pointers unless the name says host.  Nothing here allocates device
- * memory except the fedb_mem_* family and fedb_scratch_*.
+ * All pointers are device pointers unless the name says host.  Device memory is allocated only by the
+ * fedb_mem_* / fedb_mc_* family (peer-shared arenas) and by fedb_cross_entropy (a per-device row scratch
+ * that grows with cudaMalloc/cudaFree when the batch grows; fedb_cross_entropy_static never allocates).
  *
  * "reference:" lines cite the file:line of amolahinge/739-839-federated-learning-using-grpc whose
  * behaviour the entry point replaces.
@@ -79,6 +80,10 @@ typedef struct {
   uint64_t timeout_ns;
   uint32_t version;                       /* stamped into ctrl of every destination when nonzero */
   fedb_ctrl_t* dst_ctrl[FEDB_MAX_DST];    /* optional: where to stamp the version */
+  /* optional gate: when non-NULL and *gate != 0 at run time the launch does nothing (no stores, no version stamp).
+   * The follow-up copies of a round (global model, replica) pass the status word of the round's K-AGG here, so a
+   * round whose flag wait failed cannot leak un-averaged weights into the server's copies. */
+  const uint32_t* gate;
 } fedb_agg_desc_t;
 
 int fedb_fedavg(const fedb_agg_desc_t* desc, int max_blocks, void* stream);
@@ -119,7 +124,8 @@ int fedb_adam_step(float* param, const float* grad, float* m, float* v, int64_t 
 
 /* ------------------------------------------------------------------ K9/K13 loss + counters
  * logits [B, C] -> mean CE loss; dlogits = (softmax - onehot)/B; stats[0] += loss_sum (fp32),
- * stats[1] += correct (as float), stats[2] += B.  reference: src/main.py:98,149,153-156 */
+ * stats[1] += correct (as float), stats[2] += B.  A label outside [0, C) is not dereferenced; it turns
+ * that row's loss (and so the batch loss) into NaN.  reference: src/main.py:98,149,153-156 */
 int fedb_cross_entropy(const float* logits, const int64_t* target, float* dlogits, float* loss_out,
                        float* stats, int B, int C, void* stream);
 
@@ -144,6 +150,11 @@ int fedb_cross_entropy_static(const float* logits, const int64_t* target, float*
  * RandomCrop(32,4)+flip drawn from (seed, sample index).  reference: src/main.py:36-46 */
 int fedb_prepare_batch(const uint8_t* src_u8, float* dst, int B, int nhwc_out, int augment,
                        uint64_t seed, void* stream);
+/* Same, with a device-side seed word mixed into `seed` at run time: a step captured in a CUDA graph bakes `seed`
+ * in, the word (bumped by the host once per pass) keeps every replayed pass drawing fresh crops and flips, as the
+ * reference does every epoch (src/main.py:36-41). */
+int fedb_prepare_batch_dev(const uint8_t* src_u8, float* dst, int B, int nhwc_out, int augment,
+                           uint64_t seed, const uint64_t* seed_dev, void* stream);
 
 /* ------------------------------------------------------------------ LeNet fused training step
  * Whole step in 4 kernels: features fwd, classifier fwd+loss+bwd, features bwd, reduce+SGD.

@@ -34,7 +34,8 @@ class WorkerProc:
 
     def start(self):
         cfg = WorkerConfig(address=self.address, plane=self.plane, eval_on_send=self.eval_on_send,
-                           compress=self.compress, checkpoint_root=str(self.tmp_path / "checkpoint"))
+                           compress=self.compress, checkpoint_root=str(self.tmp_path / "checkpoint"),
+                           dump_root=str(self.tmp_path))
         self.server, self.servicer = serve_worker(self.trainer, cfg, sink=self.sink, block=False)
 
     def kill(self):

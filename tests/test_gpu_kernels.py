@@ -78,6 +78,59 @@ def test_fedavg_bf16_shadow_and_aggregate_arenas_dispatch(K):
     assert torch.equal(out2.f32, out.f32)
 
 
+@pytest.mark.parametrize("how", ["timeout", "abort"])
+def test_fedavg_failed_flag_wait_leaves_every_arena_untouched(K, how):
+    """A peer that never arrives (dead worker) or an abort: the launch must neither reduce nor fan out (SURVEY B3 must
+    not come back through the failure path), must record the reason and must not advance the epoch."""
+    from fedb200.ops import _lib
+    ms = _client_models(2, "LeNet")
+    arenas = [Arena.adopt(m.to(DEV), DEV) for m in ms]
+    before = [a.f32.clone() for a in arenas]
+    before_i = [a.i64.clone() for a in arenas]
+    ctrl = [K.new_ctrl(DEV), K.new_ctrl(DEV)]           # rank 0 launches, "rank 1" never does
+    if how == "abort":
+        ctrl[0][_lib.CTRL_OFF["abort_flag"] // 4] = 1
+    n = arenas[0].manifest.n_f32
+    K.fedavg_raw([a.f32.data_ptr() for a in arenas], [a.f32.data_ptr() for a in arenas], 0, n,
+                 ctrl_local=ctrl[0].data_ptr(), src_i64=[a.i64.data_ptr() for a in arenas],
+                 dst_i64=[a.i64.data_ptr() for a in arenas], n_i64=arenas[0].manifest.n_i64,
+                 sync_mode=1, rank=0, world=2, ctrl_peer=[c.data_ptr() for c in ctrl],
+                 timeout_ns=2_000_000 if how == "timeout" else 5_000_000_000)
+    torch.cuda.synchronize()
+    assert K.ctrl_field(ctrl[0], "status") == (1 if how == "timeout" else 3)
+    assert K.ctrl_field(ctrl[0], "epoch") == 0 and K.ctrl_field(ctrl[0], "blocks_done") == 0
+    for a, b, bi in zip(arenas, before, before_i):
+        assert torch.equal(a.f32, b) and torch.equal(a.i64, bi)
+    # the announcement was withdrawn from the peer's block: a late peer cannot finish the round alone
+    assert int(ctrl[1][0]) == 0 and int(ctrl[1][16]) == 0          # arrive[0], done[0] as seen by rank 1
+
+
+def test_fedavg_flag_protocol_two_ranks_on_one_gpu(K):
+    """Both ranks of a 2-rank K-AGG launched on one GPU (two streams): bit-exact mean in both arenas, epoch advanced."""
+    ms = _client_models(2, "LeNet")
+    sds = [{k: v.clone() for k, v in m.state_dict().items()} for m in ms]
+    arenas = [Arena.adopt(m.to(DEV), DEV) for m in ms]
+    ctrl = [K.new_ctrl(DEV), K.new_ctrl(DEV)]
+    n = arenas[0].manifest.n_f32
+    half = (n // 2) // 4 * 4
+    streams = [torch.cuda.Stream(), torch.cuda.Stream()]
+    torch.cuda.synchronize()
+    for r, (lo, hi) in enumerate([(0, half), (half, n)]):
+        with torch.cuda.stream(streams[r]):
+            K.fedavg_raw([a.f32.data_ptr() for a in arenas], [a.f32.data_ptr() for a in arenas], lo, hi,
+                         ctrl_local=ctrl[r].data_ptr(), src_i64=[a.i64.data_ptr() for a in arenas],
+                         dst_i64=[a.i64.data_ptr() for a in arenas], n_i64=arenas[0].manifest.n_i64 if r == 0 else 0,
+                         sync_mode=1, rank=r, world=2, ctrl_peer=[c.data_ptr() for c in ctrl],
+                         timeout_ns=5_000_000_000, max_blocks=64)
+    torch.cuda.synchronize()
+    want = fedavg_state_dicts(sds)
+    for c in ctrl:
+        assert K.ctrl_field(c, "status") == 0 and K.ctrl_field(c, "epoch") == 1
+    for a in arenas:
+        for k, v in want.items():
+            assert torch.equal(a.view(k).cpu(), v), k
+
+
 def test_replicate_stamps_version(K):
     m = models.MobileNet().to(DEV)
     src = Arena.adopt(m, DEV)

@@ -10,16 +10,18 @@ import torch
 from fedb200.utils import data as D
 
 pytestmark = pytest.mark.gpu
+_TAG = iter(range(1 << 30))
 
 
 def _fed(seed, **kw):
     from fedb200.parallel.session import GpuFederation
     ds = D.synthetic_cifar(128 * 20 + 17, 1003, seed=3)
-    return GpuFederation(model="LeNet", rank=0, world=1, device=0, dataset=ds, seed=seed, tag=f"t-sess-{seed}-{len(kw)}", **kw)
+    return GpuFederation(model="LeNet", rank=0, world=1, device=0, dataset=ds, seed=seed, tag=f"t-sess-{seed}-{next(_TAG)}", **kw)
 
 
-def test_round_is_reproducible_across_upload_modes_and_async():
-    a, b, c = _fed(11), _fed(11), _fed(11)
+@pytest.mark.parametrize("eval_mode", ["overlap", "inline"])
+def test_round_is_reproducible_across_upload_modes_and_async(eval_mode):
+    a, b, c = _fed(11, eval_mode="inline"), _fed(11, eval_mode=eval_mode), _fed(11, eval_mode=eval_mode)
     outs = {"sync": [], "resident": [], "async": []}
     pending = None
     for r in range(4):
@@ -34,16 +36,43 @@ def test_round_is_reproducible_across_upload_modes_and_async():
             outs["async"].append(pending.result())
         pending = h
     outs["async"].append(pending.result())
+    last_eval = c.drain()
+    lag = 1 if eval_mode == "overlap" else 0          # the overlapped evaluation is reported one round late
     for mode in ("resident", "async"):
-        for (t0, e0), (t1, e1) in zip(outs["sync"], outs[mode]):
+        for r, ((t0, e0), (t1, e1)) in enumerate(zip(outs["sync"], outs[mode])):
             assert t0.steps == t1.steps == 21 and t0.samples == t1.samples == 128 * 20 + 17
             assert t0.loss_sum == t1.loss_sum and t0.correct == t1.correct, mode
-            assert e0.samples == e1.samples == 1003 and e0.loss_sum == e1.loss_sum and e0.correct == e1.correct, mode
+            if mode == "async" and lag:
+                if r == 0:
+                    assert e1.samples == 0
+                    continue
+                e0 = outs["sync"][r - 1][1]
+            assert e0.samples == e1.samples == 1003 and e0.loss_sum == e1.loss_sum and e0.correct == e1.correct, (mode, r)
+    e_last = outs["sync"][-1][1]
+    assert last_eval.samples == 1003 and last_eval.loss_sum == e_last.loss_sum and last_eval.correct == e_last.correct
     pa = a.trainer.arena.f32.clone()
     assert torch.equal(pa, b.trainer.arena.f32) and torch.equal(pa, c.trainer.arena.f32)
     assert a.h2d_bytes_per_round() == (128 * 20 + 17) * (3072 + 8) + 1003 * (3072 + 8)
     for f in (a, b, c):
         f.close()
+
+
+def test_overlapped_eval_of_a_zoo_model_scores_the_snapshot():
+    """Generic-model path: the second-stream evaluation reads a private copy of the global model through a second
+    module bound to the snapshot arena.  After a synchronous round the arena still holds that global model, so the
+    inline evaluation of the arena must give the very same counters (the forward kernels are deterministic; the
+    training pass of a zoo model is not bit-reproducible across runs - split-K atomics - so two federations are not
+    compared with each other)."""
+    from fedb200.parallel.session import GpuFederation
+    ds = D.synthetic_cifar(128 * 3, 300, seed=5)
+    fed = GpuFederation(model="MobileNet", rank=0, world=1, device=0, dataset=ds, seed=7, tag="t-zoo-overlap", eval_mode="overlap")
+    for _ in range(3):
+        tr, ev = fed.run_round(upload=True, sync=True)
+        inline = fed.engine.eval_pass(upload=True, sync=True)
+        assert tr.steps == 3 and ev.samples == inline.samples == 300
+        assert ev.loss_sum == inline.loss_sum and ev.correct == inline.correct
+    assert torch.equal(fed.engine.snap.f32, fed.trainer.arena.f32) and torch.equal(fed.engine.snap.i64, fed.trainer.arena.i64)
+    fed.close()
 
 
 def test_standalone_trainer_on_gpu_follows_the_cpu_run(tmp_path):

@@ -8,6 +8,8 @@ again; a re-admitted worker is "remap"-ped by the others and "pull"-s the global
 "dump"-s a reference-format checkpoint.
 """
 import threading
+
+import pytest
 import time
 
 from fedb200.control.coordinator import Coordinator, CoordinatorConfig
@@ -30,8 +32,9 @@ class FakePeer:
         with self.lock:
             self.calls.append(what)
 
-    def start_round(self, rank, world, live=None):
+    def start_round(self, rank, world, live=None, round_id=None):
         self._log("start", rank, world, tuple(live) if live is not None else None)
+        self.round_ids = getattr(self, "round_ids", []) + [round_id]
         st = TrainStats()
         st.loss_sum, st.correct, st.samples, st.steps = 2.3, 13, 128, 1
         return st
@@ -51,12 +54,15 @@ class FakePeer:
     def remap(self, r):
         self._log("remap", r)
 
-    def pull_global(self):
-        self._log("pull")
+    def pull_global(self, src=None):
+        self._log("pull", src)
 
-    def dump_global(self, path):
-        self._log("dump", path)
+    def dump(self, path, what="global"):
+        self._log("dump", path, what)
         open(path, "wb").write(b"stub")
+
+    def status(self):
+        return {"rank": 0, "primary_rank": 0, "backup_rank": 1, "replica_version": 0, "multicast": False}
 
 
 def _peer_workers(tmp_path, n, **fake_kw):
@@ -78,6 +84,25 @@ def _coord(tmp_path, ws, **kw):
 
 def _kinds(peer):
     return [c[0] for c in peer.calls]
+
+
+def test_dump_descriptor_is_confined_to_the_dump_root_and_status_is_recorded(tmp_path):
+    import grpc
+    from fedb200 import proto
+    from fedb200.control import descriptor as desc
+    (w,) = _peer_workers(tmp_path, 1)
+    try:
+        stub = proto.TrainerStub(proto.make_channel(w.address, False))
+        ok = stub.SendModel(proto.SendModelRequest(model=desc.encode("dump", path=str(tmp_path / "sub" / ".." / "g.pth"), what="client")))
+        assert ok.reply == "success" and ("dump", str(tmp_path / "g.pth"), "client") in w.servicer.peer.calls
+        with pytest.raises(grpc.RpcError) as e:
+            stub.SendModel(proto.SendModelRequest(model=desc.encode("dump", path="/tmp/../etc/fedb200-escape.pth")))
+        assert e.value.code() == grpc.StatusCode.PERMISSION_DENIED
+        assert stub.SendModel(proto.SendModelRequest(model=desc.encode("status"))).reply == "success"
+        rec = [r for r in w.sink.records if r["event"] == "peer_status"]
+        assert rec and rec[-1]["primary_rank"] == 0 and rec[-1]["multicast"] is False
+    finally:
+        w.kill()
 
 
 def test_descriptor_rounds_and_periodic_dump(tmp_path):

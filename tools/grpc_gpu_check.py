@@ -4,8 +4,12 @@
   (``python -m fedb200.client --plane peer``), one per GPU, whose arenas are peer-mapped; FedAvg, broadcast and
   the backup replica run as K-AGG/K-REPL kernels over NVLink.  Then: kill a worker mid-run (bounded flag wait ->
   ABORTED -> reset -> live-only rounds), restart it with --rejoin (survivor re-maps its memory, newcomer pulls the
-  global model), and check the rounds continue with both.
+  global model), and check the rounds continue with both.  No rank is special: the worker that HOSTS the global model
+  (rank 0) is killed too - the lowest live rank takes the global model and the next one the replica, the replica's version
+  follows the committed rounds, a restarted rank 0 pulls from the new holder - and, with >= 4 GPUs, ranks 0 and 1 die in
+  consecutive rounds.  Finally the primary PROCESS is killed mid-round and the backup takes over.
 """
+import json
 import os
 import signal
 import socket
@@ -44,12 +48,57 @@ WORLD = int(os.environ.get("FEDB200_CHECK_WORLD", "2"))     # workers = GPUs (co
 def spawn_worker(rank, port, tag, work, rejoin=False):
     cmd = [sys.executable, "-m", "fedb200.client", "-a", f"127.0.0.1:{port}", "--plane", "peer", "--model", "LeNet",
            "--device", f"cuda:{rank}", "--peer-rank", str(rank), "--peer-world", str(WORLD), "--peer-tag", tag,
-           "--dataset-size", "2048", "--test-size", "500", "--seed", str(10 + rank), "--agg-timeout", "4"]
+           "--dataset-size", "2048", "--test-size", "500", "--seed", str(10 + rank), "--agg-timeout", "4",
+           "--dump-root", work, "--metrics", os.path.join(work, f"worker{rank}.jsonl")]
     if rejoin:
         cmd.append("--rejoin")
     log = open(os.path.join(work, f"worker{rank}{'-re' if rejoin else ''}.log"), "w")
     env = dict(os.environ, PYTHONPATH=ROOT)
     return subprocess.Popen(cmd, cwd=work, stdout=log, stderr=subprocess.STDOUT, env=env, start_new_session=True)
+
+
+def statuses(c, work, ranks):
+    """'status' descriptor to the given workers -> their newest peer_status records (roles, replica version, checksum)."""
+    from fedb200.control import descriptor as desc
+    out = {}
+    for r in ranks:
+        assert c._send_model_to(c.cfg.workers[r], desc.encode("status")), f"status RPC to worker {r} failed"
+        recs = [json.loads(line) for line in open(os.path.join(work, f"worker{r}.jsonl")) if '"peer_status"' in line]
+        out[r] = recs[-1]
+    return out
+
+
+def check_roles(c, work, live, label):
+    """After committed rounds with the live set ``live``: every survivor agrees on the holders (lowest live ranks), the
+    replica on the backup rank carries the coordinator's committed-round count, all client arenas hold the same bits,
+    and they are the bits of the global model the holder dumps."""
+    import torch
+    from fedb200.control import descriptor as desc
+    st = statuses(c, work, live)
+    prim = live[0]
+    bak = live[1] if len(live) > 1 else live[0]
+    assert all(s["primary_rank"] == prim and s["backup_rank"] == bak for s in st.values()), (label, st)
+    assert len({s["arena_checksum"] for s in st.values()}) == 1, (label, st)
+    if bak != prim:
+        assert st[bak]["replica_version"] == c.round, (label, st[bak]["replica_version"], c.round)
+    gpath = os.path.join(work, f"global-{label}.pth")
+    assert c._send_model_to(c.cfg.workers[prim], desc.encode("dump", path=gpath, what="global"))
+    glob = ckpt.load_checkpoint(gpath)["net"]
+    for r in live:
+        cpath = os.path.join(work, f"client{r}-{label}.pth")
+        assert c._send_model_to(c.cfg.workers[r], desc.encode("dump", path=cpath, what="client"))
+        mine = ckpt.load_checkpoint(cpath)["net"]
+        assert all(torch.equal(mine[k], glob[k]) for k in glob), (label, r)
+    return st
+
+
+def rejoin(c, procs, ports, tag, work, r):
+    procs[r] = spawn_worker(r, ports[r], tag, work, rejoin=True)
+    assert wait_port(ports[r])
+    end = time.time() + 60
+    while time.time() < end and not c.members.snapshot()[c.cfg.workers[r]]:
+        time.sleep(0.2)
+    assert c.members.snapshot()[c.cfg.workers[r]], f"worker {r} was not re-admitted"
 
 
 def main():
@@ -75,7 +124,9 @@ def main():
         glob = ckpt.load_checkpoint(os.path.join(work, "Primary", "optimizedModel.pth"))
         assert list(glob["net"].keys())[0] == "conv1.weight" and glob["acc"] == 1
         assert backup.next_round == 3                                          # replica metadata followed
-        print("phase 1 ok: 3 descriptor rounds,", [round(r["total_s"], 3) for r in rounds])
+        st = check_roles(c, work, list(range(WORLD)), "p1")
+        print("phase 1 ok: 3 descriptor rounds,", [round(r["total_s"], 3) for r in rounds],
+              f"multicast: {str(st[0]['multicast']).lower()}, replica version {st[1 % WORLD]['replica_version']}")
 
         # ---- kill worker 1: the survivor's flag wait is bounded, the round is dropped, the next ones are live-only
         os.killpg(procs[1].pid, signal.SIGKILL)
@@ -99,6 +150,48 @@ def main():
         rounds = [r for r in c.sink.records if r["event"] == "round"]
         assert done == 2 and rounds[-1]["uploads"] == WORLD, (done, rounds[-2:])
         print("phase 3 ok: worker 1 re-admitted, uploads per round:", [r["uploads"] for r in rounds])
+        check_roles(c, work, list(range(WORLD)), "p3")
+
+        # ---- phase 3b: the worker that HOSTS the global model dies.  The round in flight is dropped (nobody's arena is
+        # touched by the failed K-AGG), the survivors re-run it live-only, rank 1 now keeps the global model, the next
+        # live rank the replica; a restarted rank 0 pulls from rank 1.
+        os.killpg(procs[0].pid, signal.SIGKILL)
+        procs[0].wait()
+        c.cfg.rounds = c.round + 3
+        done = c.run()
+        rounds = [r for r in c.sink.records if r["event"] == "round"]
+        assert done == 3 and rounds[-1]["uploads"] == WORLD - 1, (done, rounds[-3:])
+        survivors = list(range(1, WORLD))
+        st = check_roles(c, work, survivors, "p3b")
+        print(f"phase 3b ok: worker 0 (global model host) killed; holder is now rank {st[1]['primary_rank']}, replica on rank "
+              f"{st[1]['backup_rank']} at version {st[st[1]['backup_rank']]['replica_version']} == committed rounds {c.round}")
+        rejoin(c, procs, ports, tag, work, 0)
+        c.cfg.rounds = c.round + 2
+        assert c.run() == 2
+        rounds = [r for r in c.sink.records if r["event"] == "round"]
+        assert rounds[-1]["uploads"] == WORLD, rounds[-2:]
+        check_roles(c, work, list(range(WORLD)), "p3c")
+        print("phase 3c ok: worker 0 re-admitted from the new holder; all arenas equal, roles back on ranks 0/1")
+
+        if WORLD >= 4:
+            # ---- phase 3d: ranks 0 and 1 die in consecutive rounds
+            os.killpg(procs[0].pid, signal.SIGKILL)
+            procs[0].wait()
+            c.cfg.rounds = c.round + 1
+            assert c.run() == 1
+            os.killpg(procs[1].pid, signal.SIGKILL)
+            procs[1].wait()
+            c.cfg.rounds = c.round + 2
+            assert c.run() == 2
+            st = check_roles(c, work, list(range(2, WORLD)), "p3d")
+            print(f"phase 3d ok: workers 0 and 1 killed in consecutive rounds; holder rank {st[2]['primary_rank']}, replica rank "
+                  f"{st[2]['backup_rank']} at version {st[st[2]['backup_rank']]['replica_version']} == {c.round}")
+            rejoin(c, procs, ports, tag, work, 0)
+            rejoin(c, procs, ports, tag, work, 1)
+            c.cfg.rounds = c.round + 2
+            assert c.run() == 2
+            check_roles(c, work, list(range(WORLD)), "p3e")
+            print("phase 3e ok: both re-admitted")
         last_round = c.round
         c.close()
         backup.stop()
@@ -118,7 +211,6 @@ def main():
                                 stderr=subprocess.STDOUT, start_new_session=True)
         procs.append(prim)
         # the backup (watchdog 1.5 s) starts once the primary is up and running rounds, like an operator would
-        import json
         end = time.time() + 120
         while time.time() < end:
             try:
