@@ -49,9 +49,10 @@ def parse():
     ap.add_argument("--no-multicast", action="store_true")
     ap.add_argument("--repl", choices=("overlap", "fused"), default="overlap")
     ap.add_argument("--ref-gpu-workers", action="store_true", help="reference arm: R-gpu variant (DP shim)")
-    ap.add_argument("--eval", choices=("overlap", "inline"), default="overlap",
-                    help="overlap: every client scores the whole test set every round on a second stream, concurrently "
-                         "with the next local pass; inline: on the round's critical path, as the reference does")
+    ap.add_argument("--eval", choices=("overlap", "inline"), default="inline",
+                    help="inline: every client scores the whole test set every round on the round's critical path, as the "
+                         "reference does; overlap: on a second stream, concurrently with the next local pass (measured "
+                         "slower for LeNet on B200, see GpuFederation)")
     ap.add_argument("--no-augment", action="store_true", help="skip RandomCrop+Flip (the reference arm always applies them)")
     ap.add_argument("--no-l2-flush", action="store_true", help="diagnostic: skip the L2 flush between device-timed rounds")
     return ap.parse_args()

@@ -192,22 +192,35 @@ __global__ void __launch_bounds__(256) dw_wgrad_partial_kernel(const float* __re
   }
 }
 
-// dw[c][tap] += sum_chunk part[chunk][tap][c]   (chunks added in order; four independent partial sums in flight)
+// dw[c][tap] += sum_chunk part[chunk][tap][c].  Block = 32 elements x 8 groups of chunks: group w adds chunks w, w+8, ...
+// (four independent loads in flight), the eight group sums are combined in group order, so the result does not depend on
+// scheduling.  (One thread per element walking all chunks - up to 592 - was a 29 us latency chain per layer.)
 __global__ void __launch_bounds__(256) dw_wgrad_final_kernel(const float* __restrict__ part, float* __restrict__ dw, int chunks,
                                                             int C, int T) {
-  const int i = blockIdx.x * 256 + threadIdx.x;      // i = tap * C + c
-  if (i >= T * C) return;
+  __shared__ float red[8][32];
+  const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+  const int i = blockIdx.x * 32 + lane;              // i = tap * C + c
+  const long long TC = (long long)T * C;
   float a0 = 0.f, a1 = 0.f, a2 = 0.f, a3 = 0.f;
-  int k = 0;
-  for (; k + 3 < chunks; k += 4) {
-    a0 += part[(long long)(k + 0) * T * C + i];
-    a1 += part[(long long)(k + 1) * T * C + i];
-    a2 += part[(long long)(k + 2) * T * C + i];
-    a3 += part[(long long)(k + 3) * T * C + i];
+  if (i < TC) {
+    int k = w;
+    for (; k + 24 < chunks; k += 32) {
+      a0 += part[(long long)(k + 0) * TC + i];
+      a1 += part[(long long)(k + 8) * TC + i];
+      a2 += part[(long long)(k + 16) * TC + i];
+      a3 += part[(long long)(k + 24) * TC + i];
+    }
+    for (; k < chunks; k += 8) a0 += part[(long long)k * TC + i];
   }
-  for (; k < chunks; ++k) a0 += part[(long long)k * T * C + i];
-  const int tap = i / C, c = i - tap * C;
-  dw[c * T + tap] += (a0 + a1) + (a2 + a3);
+  red[w][lane] = (a0 + a1) + (a2 + a3);
+  __syncthreads();
+  if (w == 0 && i < TC) {
+    float sum = 0.f;
+#pragma unroll
+    for (int q = 0; q < 8; ++q) sum += red[q][lane];
+    const int tap = i / C, c = i - tap * C;
+    dw[c * T + tap] += sum;
+  }
 }
 
 template <int TX, int R, int RB>
@@ -293,7 +306,7 @@ extern "C" int fedb_dw_conv_wgrad_k(const float* x, const float* dy, float* dw, 
   if (fs == 3) launch_wgrad_tx<3, 3>(TX, x, dy, scratch, d, ppc, grid, s);
   else if (fs == 5) launch_wgrad_tx<5, 5>(TX, x, dy, scratch, d, ppc, grid, s);
   else launch_wgrad_tx<7, 4>(TX, x, dy, scratch, d, ppc, grid, s);
-  dw_wgrad_final_kernel<<<fedb_ceil_div(fs * fs * d.C, 256), 256, 0, s>>>(scratch, dw, chunks, d.C, fs * fs);
+  dw_wgrad_final_kernel<<<fedb_ceil_div(fs * fs * d.C, 32), 256, 0, s>>>(scratch, dw, chunks, d.C, fs * fs);
   FEDB_LAUNCH_OK();
   return 0;
 }

@@ -50,6 +50,9 @@ __device__ __forceinline__ void mbar_init(uint64_t* bar, uint32_t count) {
 __device__ __forceinline__ void mbar_expect_tx(uint64_t* bar, uint32_t bytes) {
   asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(smem_u32(bar)), "r"(bytes) : "memory");
 }
+__device__ __forceinline__ void mbar_arrive(uint64_t* bar) {
+  asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(smem_u32(bar)) : "memory");
+}
 __device__ __forceinline__ void mbar_wait(uint64_t* bar, uint32_t parity) {
   const uint32_t addr = smem_u32(bar);
   uint32_t done;
@@ -169,6 +172,7 @@ struct GemmArgs {
   // masked by the M / N guards of the epilogue.
   int groups, a_goff, b_goff;
   long long d_goff;
+  int gx, gy, gz;          // logical tile grid (M tiles, N tiles [x taps x groups], splits / groups), walked persistently
 };
 
 __device__ __forceinline__ long long out_row(const GemmArgs& g, int row) {
@@ -177,106 +181,145 @@ __device__ __forceinline__ long long out_row(const GemmArgs& g, int row) {
   return ((long long)(n * g.H + p) * g.ostride + g.oy) * (g.W * g.ostride) + q * g.ostride + g.ox;
 }
 
-// smem stage layout: A tile then B tile, each a multiple of 1024 B (swizzle atom)
+// smem layout: NST pipeline stages (A tile then B tile, each a multiple of the 1024 B swizzle atom), then a staging tile of
+// the epilogue (128 rows x (BN + 4) floats: its own memory, because the main loop of the NEXT tile runs while a tile is
+// written out), then the barriers.  One CTA per SM: the stages take what is left of the 227 KB.
+#ifndef FEDB_GEMM_CTAS_SMALL
+#define FEDB_GEMM_CTAS_SMALL 2      // 2: tiles of at most 64 columns run two CTAs per SM (eight epilogue warps draining the
+                                    // memory-bound narrow layers), three stages each; 1: one CTA per SM everywhere.
+                                    // Measured on B200: ResNet-18 step 4.10 -> 3.88 ms, VGG16 3.11 -> 3.06 ms with 2.
+#endif
 template <int BN, int KIND>
 struct Smem {
+  static constexpr int kCtas = (BN <= 64 && FEDB_GEMM_CTAS_SMALL == 2) ? 2 : 1;
   static constexpr int kBN = (KIND == 1 && BN < 64) ? 64 : BN;                 // MN-major chunks are 64 wide
   static constexpr int kABytes = BM * Kind<KIND>::kBK * Kind<KIND>::kElem;     // 16 KiB
   static constexpr int kBBytes = kBN * Kind<KIND>::kBK * Kind<KIND>::kElem;
   static constexpr int kStage = kABytes + kBBytes;
-  static constexpr int kStages = kStage > 24 * 1024 ? 3 : STAGES;
-  static constexpr int kTotal = kStages * kStage + 1024 /*align slack*/ + 256 /*barriers*/;
+  static constexpr int kPitch = BN + 4;                                        // floats; +4 keeps 128-bit accesses conflict-free
+  static constexpr int kStaging = (BM * kPitch * 4 + 1023) / 1024 * 1024;
+  static constexpr int kBudget = (kCtas == 2 ? 110 : 200) * 1024 - kStaging;
+  static constexpr int kStages = kBudget / kStage > 8 ? 8 : kBudget / kStage;
+  static constexpr int kTotal = kStages * kStage + kStaging + 1024 /*align slack*/ + 256 /*barriers*/;
 };
 
+struct TileCoord { int bx, by, bz; };
+// tile order: by fastest (CTAs that run at the same time share the activation rows of one M tile through L2), then bz, then bx
+__device__ __forceinline__ TileCoord tile_coord(const GemmArgs& g, int tile) {
+  TileCoord t;
+  t.by = tile % g.gy;
+  const int r = tile / g.gy;
+  t.bz = r % g.gz;
+  t.bx = r / g.gz;
+  return t;
+}
+
+// PERSISTENT kernel: gridDim.x CTAs (one per SM) walk the tiles tile = blockIdx.x, + gridDim.x, ...  The TMA producer runs
+// ahead across tile boundaries (the smem ring never drains), the accumulator is double-buffered in TMEM (2 x BN columns), so
+// the MMA warp starts tile i+1 while warps 2..5 drain tile i.
 template <int BN, int KIND>
-__global__ void __launch_bounds__(kThreads, 2)
+__global__ void __launch_bounds__(kThreads, Smem<BN, KIND>::kCtas)
 gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__ CUtensorMap mapB, GemmArgs g) {
   constexpr int NST = Smem<BN, KIND>::kStages;
   extern __shared__ uint8_t smem_raw[];
   uint8_t* smem = (uint8_t*)(((uintptr_t)smem_raw + 1023) & ~(uintptr_t)1023);
-  uint64_t* full = (uint64_t*)(smem + NST * Smem<BN, KIND>::kStage);
+  float* staging = reinterpret_cast<float*>(smem + NST * Smem<BN, KIND>::kStage);
+  uint64_t* full = (uint64_t*)(smem + NST * Smem<BN, KIND>::kStage + Smem<BN, KIND>::kStaging);
   uint64_t* empty = full + NST;
-  uint64_t* accum_ready = empty + NST;
-  uint32_t* tmem_slot = (uint32_t*)(accum_ready + 1);
+  uint64_t* accum_full = empty + NST;       // [2] MMA -> epilogue: accumulator buffer complete
+  uint64_t* accum_empty = accum_full + 2;   // [2] epilogue -> MMA: accumulator buffer drained
+  uint32_t* tmem_slot = (uint32_t*)(accum_empty + 2);
 
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  // conv wgrad (g.conv == 2): blockIdx.y enumerates (filter tap, N tile); the tap selects the spatial shift of the
+  // conv wgrad (g.conv == 2): by enumerates (group, filter tap, N tile); the tap selects the spatial shift of the
   // X operand and the column block [tap*Cin, (tap+1)*Cin) of the packed gradient dWk[Cout][9*Cin]
   const int n_tiles = (g.N + BN - 1) / BN;
   const bool grouped = g.groups > 1;
-  const int ytap = g.conv == 2 ? blockIdx.y / n_tiles : 0;                       // (group, tap) of a weight-gradient tile
   const int ntaps = g.fs * g.fs;
-  const int tap = grouped ? ytap % ntaps : ytap;
-  const int grp = !grouped ? 0 : (g.conv == 2 ? ytap / ntaps : blockIdx.z);
-  const int m0 = blockIdx.x * BM, n0 = (g.conv == 2 ? blockIdx.y % n_tiles : blockIdx.y) * BN;
-  const int k_begin = (grouped && g.conv == 1) ? 0 : blockIdx.z * g.k_per_split;
-  const int k_end = min(g.K, k_begin + g.k_per_split);
   constexpr int BK = Kind<KIND>::kBK;
   constexpr int kChunkBytes = BK * 128;          // one MN-major chunk: BK K-rows of 128 bytes
-  const int num_k = (k_end - k_begin + BK - 1) / BK;
-  constexpr uint32_t kTmemCols = BN < 32 ? 32 : BN;   // power of two >= 32
+  constexpr uint32_t kTmemCols = BN < 32 ? 32 : BN;   // power of two >= 32, per accumulator buffer
+  const int total_tiles = g.gx * g.gy * g.gz;
 
   if (threadIdx.x == 0) {
     for (int s = 0; s < NST; ++s) { mbar_init(&full[s], 1); mbar_init(&empty[s], 1); }
-    mbar_init(accum_ready, 1);
+    for (int b = 0; b < 2; ++b) { mbar_init(&accum_full[b], 1); mbar_init(&accum_empty[b], 4); }
     asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
   }
-  if (warp == 1) tmem_alloc(tmem_slot, kTmemCols);
+  if (warp == 1) tmem_alloc(tmem_slot, 2 * kTmemCols);
   tc_fence_before();
   __syncthreads();
   tc_fence_after();
   const uint32_t tmem_base = *tmem_slot;
+
+  // per tile, identical in every role
+  auto k_range = [&](const TileCoord& t, int& k_begin, int& num_k) {
+    k_begin = (grouped && g.conv == 1) ? 0 : t.bz * g.k_per_split;
+    const int k_end = min(g.K, k_begin + g.k_per_split);
+    num_k = (k_end - k_begin + BK - 1) / BK;
+    if (num_k < 0) num_k = 0;
+  };
 
   if (warp == 0) {
     // ===================================================================== TMA producer
     if (lane == 0) {
       asm volatile("prefetch.tensormap [%0];" ::"l"(&mapA) : "memory");
       asm volatile("prefetch.tensormap [%0];" ::"l"(&mapB) : "memory");
-      for (int i = 0; i < num_k; ++i) {
-        const int s = i % NST;
-        const uint32_t ph = (i / NST) & 1;
-        mbar_wait(&empty[s], ph ^ 1);
-        uint8_t* a_dst = smem + s * Smem<BN, KIND>::kStage;
-        uint8_t* b_dst = a_dst + Smem<BN, KIND>::kABytes;
-        mbar_expect_tx(&full[s], Smem<BN, KIND>::kStage);
-        const int k0 = k_begin + i * BK;
-        if constexpr (KIND == 0) {
-          if (g.conv) {
-            // K index = (tap, channel chunk); the weight matrix is [Cout][9*Cin] with the same ordering
-            const int per_tap = g.Cin / BK;
-            const int kk = k0 / BK;
-            const int tap = kk / per_tap, c0 = (kk % per_tap) * BK;
-            const int r = tap / g.fs, sx = tap % g.fs;
-            int n_img, h0;
-            if (g.bn == 1) { const int tpi = g.H / g.bh; n_img = blockIdx.x / tpi; h0 = (blockIdx.x % tpi) * g.bh; }
-            else           { n_img = blockIdx.x * g.bn; h0 = 0; }
-            // box [32 ch x bw x bh x bn] output pixels; with stride 2 the tensor map itself skips every other input
-            // pixel (elementStrides), so the same 128 x 32 tile lands in shared memory
-            tma_load_4d(a_dst, &mapA, &full[s], c0 + grp * g.a_goff, sx - g.cpad, h0 * g.cstride + r - g.cpad, n_img);
-            tma_load_2d(b_dst, &mapB, &full[s], k0, n0 + grp * g.b_goff);
-          } else {
-            tma_load_2d(a_dst, &mapA, &full[s], k0, m0);                   // box [32 fp32 (K) x BM rows]
-            tma_load_2d(b_dst, &mapB, &full[s], k0, n0);                   // box [32 fp32 (K) x BN rows]
-          }
-        } else {
-#pragma unroll
-          for (int c = 0; c < BM / 64; ++c)                                // box [64 bf16 (M) x BK K-rows] per chunk
-            tma_load_2d(a_dst + c * kChunkBytes, &mapA, &full[s], m0 + c * 64 + grp * g.b_goff, k0);
-          if (g.conv == 2) {
-            // K runs over output pixels in tiles of 64 = one [bw x bh x bn] box of the bf16 NHWC activation, shifted
-            // by the filter tap (zero fill outside the image = the padding)
-            const int pt = k0 / BK;
-            int n_img, h0;
-            if (g.bn == 1) { const int tpi = g.H / g.bh; n_img = pt / tpi; h0 = (pt % tpi) * g.bh; }
-            else           { n_img = pt * g.bn; h0 = 0; }
-#pragma unroll
-            for (int c = 0; c < Smem<BN, KIND>::kBN / 64; ++c)
-              tma_load_4d(b_dst + c * kChunkBytes, &mapB, &full[s], n0 + c * 64 + grp * g.a_goff, tap % g.fs - g.cpad,
-                          h0 * g.cstride + tap / g.fs - g.cpad, n_img);
+      uint32_t it = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const TileCoord tc = tile_coord(g, tile);
+        const int ytap = g.conv == 2 ? tc.by / n_tiles : 0;
+        const int tap = grouped ? ytap % ntaps : ytap;
+        const int grp = !grouped ? 0 : (g.conv == 2 ? ytap / ntaps : tc.bz);
+        const int m0 = tc.bx * BM, n0 = (g.conv == 2 ? tc.by % n_tiles : tc.by) * BN;
+        int k_begin, num_k;
+        k_range(tc, k_begin, num_k);
+        for (int i = 0; i < num_k; ++i, ++it) {
+          const int s = it % NST;
+          const uint32_t ph = (it / NST) & 1;
+          mbar_wait(&empty[s], ph ^ 1);
+          uint8_t* a_dst = smem + s * Smem<BN, KIND>::kStage;
+          uint8_t* b_dst = a_dst + Smem<BN, KIND>::kABytes;
+          mbar_expect_tx(&full[s], Smem<BN, KIND>::kStage);
+          const int k0 = k_begin + i * BK;
+          if constexpr (KIND == 0) {
+            if (g.conv) {
+              // K index = (tap, channel chunk); the weight matrix is [Cout][9*Cin] with the same ordering
+              const int per_tap = g.Cin / BK;
+              const int kk = k0 / BK;
+              const int ktap = kk / per_tap, c0 = (kk % per_tap) * BK;
+              const int r = ktap / g.fs, sx = ktap % g.fs;
+              int n_img, h0;
+              if (g.bn == 1) { const int tpi = g.H / g.bh; n_img = tc.bx / tpi; h0 = (tc.bx % tpi) * g.bh; }
+              else           { n_img = tc.bx * g.bn; h0 = 0; }
+              // box [32 ch x bw x bh x bn] output pixels; with stride 2 the tensor map itself skips every other input
+              // pixel (elementStrides), so the same 128 x 32 tile lands in shared memory
+              tma_load_4d(a_dst, &mapA, &full[s], c0 + grp * g.a_goff, sx - g.cpad, h0 * g.cstride + r - g.cpad, n_img);
+              tma_load_2d(b_dst, &mapB, &full[s], k0, n0 + grp * g.b_goff);
+            } else {
+              tma_load_2d(a_dst, &mapA, &full[s], k0, m0);                   // box [32 fp32 (K) x BM rows]
+              tma_load_2d(b_dst, &mapB, &full[s], k0, n0);                   // box [32 fp32 (K) x BN rows]
+            }
           } else {
 #pragma unroll
-            for (int c = 0; c < Smem<BN, KIND>::kBN / 64; ++c)
-              tma_load_2d(b_dst + c * kChunkBytes, &mapB, &full[s], n0 + c * 64, k0);
+            for (int c = 0; c < BM / 64; ++c)                                // box [64 bf16 (M) x BK K-rows] per chunk
+              tma_load_2d(a_dst + c * kChunkBytes, &mapA, &full[s], m0 + c * 64 + grp * g.b_goff, k0);
+            if (g.conv == 2) {
+              // K runs over output pixels in tiles of 64 = one [bw x bh x bn] box of the bf16 NHWC activation, shifted
+              // by the filter tap (zero fill outside the image = the padding)
+              const int pt = k0 / BK;
+              int n_img, h0;
+              if (g.bn == 1) { const int tpi = g.H / g.bh; n_img = pt / tpi; h0 = (pt % tpi) * g.bh; }
+              else           { n_img = pt * g.bn; h0 = 0; }
+#pragma unroll
+              for (int c = 0; c < Smem<BN, KIND>::kBN / 64; ++c)
+                tma_load_4d(b_dst + c * kChunkBytes, &mapB, &full[s], n0 + c * 64 + grp * g.a_goff, tap % g.fs - g.cpad,
+                            h0 * g.cstride + tap / g.fs - g.cpad, n_img);
+            } else {
+#pragma unroll
+              for (int c = 0; c < Smem<BN, KIND>::kBN / 64; ++c)
+                tma_load_2d(b_dst + c * kChunkBytes, &mapB, &full[s], n0 + c * 64, k0);
+            }
           }
         }
       }
@@ -285,51 +328,73 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
     // ===================================================================== MMA issuer
     if (lane == 0) {
       constexpr uint32_t idesc = make_idesc(BN, KIND);
-      for (int i = 0; i < num_k; ++i) {
-        const int s = i % NST;
-        const uint32_t ph = (i / NST) & 1;
-        mbar_wait(&full[s], ph);
+      uint32_t it = 0, t = 0;
+      for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+        const TileCoord tc = tile_coord(g, tile);
+        int k_begin, num_k;
+        k_range(tc, k_begin, num_k);
+        if (num_k == 0) continue;
+        const uint32_t acc = t & 1;
+        mbar_wait(&accum_empty[acc], ((t >> 1) & 1) ^ 1);      // the epilogue has drained this buffer (two tiles ago)
         tc_fence_after();
-        const uint32_t a_base = smem_u32(smem + s * Smem<BN, KIND>::kStage);
-        const uint32_t b_base = a_base + Smem<BN, KIND>::kABytes;
+        const uint32_t tmem_d = tmem_base + acc * kTmemCols;
+        for (int i = 0; i < num_k; ++i, ++it) {
+          const int s = it % NST;
+          const uint32_t ph = (it / NST) & 1;
+          mbar_wait(&full[s], ph);
+          tc_fence_after();
+          const uint32_t a_base = smem_u32(smem + s * Smem<BN, KIND>::kStage);
+          const uint32_t b_base = a_base + Smem<BN, KIND>::kABytes;
 #pragma unroll
-        for (int k = 0; k < Kind<KIND>::kSteps; ++k) {
-          // K-major (tf32): 8 rows x 128 B swizzle atoms, SBO = 1024 B between 8-row groups; one MMA consumes
-          //   32 B of K, so the start address advances 32 B inside the swizzled row.
-          // MN-major (bf16): 64-element chunks of M/N lie kChunkBytes apart (LBO); 8 K-rows x 128 B form one
-          //   1024 B atom (SBO); one MMA consumes 16 K-rows = 2048 B.
-          const uint64_t ad = KIND == 0 ? make_smem_desc(a_base + k * 32, 16, 1024)
-                                        : make_smem_desc(a_base + k * 2048, kChunkBytes, 1024);
-          const uint64_t bd = KIND == 0 ? make_smem_desc(b_base + k * 32, 16, 1024)
-                                        : make_smem_desc(b_base + k * 2048, kChunkBytes, 1024);
-          umma<KIND>(tmem_base, ad, bd, idesc, (i | k) != 0 ? 1u : 0u);
+          for (int k = 0; k < Kind<KIND>::kSteps; ++k) {
+            // K-major (tf32): 8 rows x 128 B swizzle atoms, SBO = 1024 B between 8-row groups; one MMA consumes
+            //   32 B of K, so the start address advances 32 B inside the swizzled row.
+            // MN-major (bf16): 64-element chunks of M/N lie kChunkBytes apart (LBO); 8 K-rows x 128 B form one
+            //   1024 B atom (SBO); one MMA consumes 16 K-rows = 2048 B.
+            const uint64_t ad = KIND == 0 ? make_smem_desc(a_base + k * 32, 16, 1024)
+                                          : make_smem_desc(a_base + k * 2048, kChunkBytes, 1024);
+            const uint64_t bd = KIND == 0 ? make_smem_desc(b_base + k * 32, 16, 1024)
+                                          : make_smem_desc(b_base + k * 2048, kChunkBytes, 1024);
+            umma<KIND>(tmem_d, ad, bd, idesc, (i | k) != 0 ? 1u : 0u);
+          }
+          umma_commit(&empty[s]);          // frees the smem stage once these MMAs have read it
         }
-        umma_commit(&empty[s]);          // frees the smem stage once these MMAs have read it
+        umma_commit(&accum_full[acc]);     // accumulator complete -> epilogue
+        ++t;
       }
-      umma_commit(accum_ready);          // accumulator complete -> epilogue
     }
   } else {
     // ===================================================================== epilogue (warps 2..5)
     const int q = warp & 3;                                  // TMEM lane quarter this warp may access
-    const int row = m0 + q * 32 + lane;
-    mbar_wait(accum_ready, 0);
-    tc_fence_after();
-    // accum_ready also means every MMA has consumed its smem stage: the ring is free and becomes the staging
-    // tile of the epilogue.  Each lane owns one accumulator ROW (tcgen05.ld 32x32b), but a row-per-lane global
-    // store is 32 scattered 64-byte pieces; staging through smem turns the write-out into whole 512-byte rows.
-    constexpr int PITCH = BN + 4;                            // floats; +4 keeps 128-bit smem accesses conflict-free
-    float* stage = reinterpret_cast<float*>(smem) + (size_t)(q * 32) * PITCH;
+    constexpr int PITCH = Smem<BN, KIND>::kPitch;
+    // Each lane owns one accumulator ROW (tcgen05.ld 32x32b), but a row-per-lane global store is 32 scattered 64-byte
+    // pieces; staging through smem turns the write-out into whole rows.  A warp only ever touches its own 32 rows.
+    float* stage = staging + (size_t)(q * 32) * PITCH;
     const bool vec_ok = !g.atomic_out && (g.ldd % 4 == 0) && (g.N % 4 == 0) && (g.d_goff % 4 == 0) &&
                         ((reinterpret_cast<uintptr_t>(g.D) & 15) == 0);
-    if (num_k > 0) {
+    uint32_t t = 0;
+    for (int tile = blockIdx.x; tile < total_tiles; tile += gridDim.x) {
+      const TileCoord tc = tile_coord(g, tile);
+      int k_begin, num_k;
+      k_range(tc, k_begin, num_k);
+      if (num_k == 0) continue;
+      const int ytap = g.conv == 2 ? tc.by / n_tiles : 0;
+      const int tap = grouped ? ytap % ntaps : ytap;
+      const int grp = !grouped ? 0 : (g.conv == 2 ? ytap / ntaps : tc.bz);
+      const int m0 = tc.bx * BM, n0 = (g.conv == 2 ? tc.by % n_tiles : tc.by) * BN;
+      const int row = m0 + q * 32 + lane;
+      const uint32_t acc = t & 1;
+      mbar_wait(&accum_full[acc], (t >> 1) & 1);
+      tc_fence_after();
+      const uint32_t tmem_d = tmem_base + acc * kTmemCols;
 #pragma unroll 1
       for (int c0 = 0; c0 < BN; c0 += 16) {
         float v[16];
-        tmem_ld16(tmem_base + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
+        tmem_ld16(tmem_d + ((uint32_t)(q * 32) << 16) + (uint32_t)c0, v);
 #pragma unroll
         for (int j = 0; j < 16; ++j) {
           const int col = n0 + c0 + j;
-          if (g.bias != nullptr && (grouped || blockIdx.z == 0) && col < g.N) v[j] += g.bias[grp * g.N + col];
+          if (g.bias != nullptr && (grouped || tc.bz == 0) && col < g.N) v[j] += g.bias[grp * g.N + col];
           if (g.relu) v[j] = fmaxf(v[j], 0.f);
         }
         if (vec_ok) {
@@ -347,27 +412,38 @@ gemm_tc_kernel(const __grid_constant__ CUtensorMap mapA, const __grid_constant__
           }
         }
       }
+      // the accumulator buffer is in registers / smem now: hand it back so the MMA warp can start the tile after next
+      tc_fence_before();
+      __syncwarp();
+      if (lane == 0) mbar_arrive(&accum_empty[acc]);
       if (vec_ok) {
-        __syncwarp();                                        // a warp reads back only the 32 rows it staged itself
-        for (int r = 0; r < 32; ++r) {
+        constexpr int PER_ROW = BN / 4;                        // float4 per tile row
+        constexpr int ROWS_IT = 32 / PER_ROW > 0 ? 32 / PER_ROW : 1;   // rows one warp pass writes (BN = 64: two half-warps)
+        const int c4 = lane % PER_ROW, rsub = lane / PER_ROW;
+        for (int r0 = 0; r0 < 32; r0 += ROWS_IT) {
+          const int r = r0 + rsub;
           const int grow = m0 + q * 32 + r;
-          if (grow >= g.M) break;
-          const long long orow = out_row(g, grow);
-          for (int c4 = lane; c4 < BN / 4; c4 += 32) {
-            const int col = n0 + 4 * c4;
-            if (col < g.N)
-              *reinterpret_cast<float4*>(g.D + grp * g.d_goff + orow * g.ldd + col) =
-                  *reinterpret_cast<const float4*>(stage + r * PITCH + 4 * c4);
+          if (r < 32 && grow < g.M) {
+            const long long orow = out_row(g, grow);
+#pragma unroll
+            for (int cc = c4; cc < PER_ROW; cc += 32) {
+              const int col = n0 + 4 * cc;
+              if (col < g.N)
+                *reinterpret_cast<float4*>(g.D + grp * g.d_goff + orow * g.ldd + col) =
+                    *reinterpret_cast<const float4*>(stage + r * PITCH + 4 * cc);
+            }
           }
         }
+        __syncwarp();                                          // the staged rows are consumed before the next tile overwrites them
       }
+      ++t;
     }
     tc_fence_before();
   }
   __syncthreads();
   if (warp == 1) {
     tc_fence_after();
-    tmem_dealloc(tmem_base, kTmemCols);
+    tmem_dealloc(tmem_base, 2 * kTmemCols);
   }
 }
 
@@ -452,6 +528,157 @@ __global__ void __launch_bounds__(256) pack3x3_kernel(const float* __restrict__ 
   }
 }
 
+// ---- many small layout jobs in ONE launch.  A training step needs, per convolution, the forward packing of the filter, the
+// data-gradient packing and the un-packing of the weight gradient; as one launch each they are ~60 latency-bound kernels
+// of a ResNet-18 step.  The jobs of a whole model live in a device table (built once, the addresses never change), the
+// step runs "pack everything" once after the weights changed and "un-pack every gradient" once after the backward pass.
+struct PackJob {
+  const float* src;
+  float* dst;
+  long long total;      // elements of the iteration space
+  int kind;             // 0 / 1: pack3x3_kernel modes; 2: dst(OIHW) += src(packed), src = 0; 3: stride-2 data-gradient
+                        // classes (pack_dgrad_s2_kernel); 4: transpose src[K][C] -> dst[C][K]
+  int K, C, T, Rp, groups;
+  int chunk0;           // index of this job's first chunk of kPackChunk elements in the flat grid (prefix sum over the jobs)
+  int pad_;
+};
+constexpr int kPackChunk = 9216;   // elements per CTA: the flat grid gives every job CTAs in proportion to its size;
+                                   // 9216 = 32 filters x 32 channels x 9 taps, the smem tile of the coalesced forms below
+
+__device__ __forceinline__ void pack_job_elem(const PackJob& j, long long i) {
+  const int K = j.K, C = j.C, T = j.T, Rp = j.Rp;
+  if (j.kind == 0) {
+    const int c = (int)(i % Rp), tap = (int)((i / Rp) % T), k = (int)(i / ((long long)T * Rp));
+    j.dst[i] = c < C ? j.src[((long long)k * C + c) * T + tap] : 0.f;
+  } else if (j.kind == 1) {
+    const int k = (int)(i % Rp), tap = (int)((i / Rp) % T), cg = (int)(i / ((long long)T * Rp));
+    const int Kg = K / j.groups, grp = cg / C, c = cg - grp * C;
+    j.dst[i] = k < Kg ? j.src[(((long long)grp * Kg + k) * C + c) * T + (T - 1 - tap)] : 0.f;
+  } else if (j.kind == 2) {
+    const int c = (int)(i % C), tap = (int)((i / C) % T), k = (int)(i / ((long long)T * C));
+    float* srcw = const_cast<float*>(j.src);
+    j.dst[((long long)k * C + c) * T + tap] += srcw[i];
+    srcw[i] = 0.f;                                       // the split-K partial sums of the next step start from zero
+  } else if (j.kind == 3) {
+    // K = output channels per group (real), Rp = K rounded up to 32, C = input channels per group
+    const int Cw = C * j.groups;
+    const long long KC = (long long)Rp * Cw;
+    const int unit = (int)(i / KC);
+    const int cls = unit < 1 ? 0 : (unit < 3 ? 1 : (unit < 5 ? 2 : 3));
+    const int base = cls == 0 ? 0 : (cls == 1 ? 1 : (cls == 2 ? 3 : 5));
+    const int a = cls >> 1, b = cls & 1;
+    const int Tc = (a + 1) * (b + 1), fc = b + 1;
+    const long long jj = i - base * KC;
+    const int k = (int)(jj % Rp), t = (int)((jj / Rp) % Tc), c = (int)(jj / ((long long)Rp * Tc));
+    const int rr = t / fc, ss = t % fc;
+    const int r = a == 0 ? 1 : (rr == 0 ? 2 : 0), sx = b == 0 ? 1 : (ss == 0 ? 2 : 0);
+    const int grp = c / C, cl = c - grp * C;
+    j.dst[i] = k < K ? j.src[((((long long)grp * K + k) * C + cl) * 3 + r) * 3 + sx] : 0.f;
+  } else {
+    const int k = (int)(i % K), c = (int)(i / K);
+    j.dst[i] = j.src[(long long)k * C + c];
+  }
+}
+
+// 3x3 filters with K % 32 == 0 and C % 32 == 0 (kinds 5, 6, 7 = tiled forms of kinds 0, 1, 2): one CTA moves a tile of
+// 32 filters x 32 channels x 9 taps through shared memory, so that both the OIHW side ([k][c][tap]: 288 contiguous floats
+// per filter) and the packed side (32 contiguous channels / filters per tap) are read and written in whole 128-byte lines.
+// The element-wise forms gather with a stride of 9 floats and were most of the step's packing time.
+__device__ __forceinline__ void pack_tile_3x3(const PackJob& j, int tile, float* __restrict__ sm /* [32][289] */) {
+  const int K = j.K, C = j.C, cb = C / 32;
+  const int k0 = (tile / cb) * 32, c0 = (tile % cb) * 32;
+  const int tid = threadIdx.x;
+  constexpr int U = 12;                                           // loads in flight per thread (36 elements per thread and phase)
+  float v[U];
+  if (j.kind == 7) {
+    // src = dWk [k][tap][c] (cleared), dst = dW OIHW (+=)
+    float* __restrict__ srcw = const_cast<float*>(j.src);
+    for (int b = 0; b < 36; b += U) {
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int e = tid + (b + u) * 256;
+        const int c = e & 31, tap = (e >> 5) % 9, k = e / 288;
+        v[u] = srcw[((long long)(k0 + k) * 9 + tap) * C + c0 + c];
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int e = tid + (b + u) * 256;
+        const int c = e & 31, tap = (e >> 5) % 9, k = e / 288;
+        sm[k * 289 + c * 9 + tap] = v[u];
+        srcw[((long long)(k0 + k) * 9 + tap) * C + c0 + c] = 0.f;
+      }
+    }
+    __syncthreads();
+    float* __restrict__ dst = j.dst;
+    for (int b = 0; b < 36; b += U) {
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int e = tid + (b + u) * 256;
+        const int k = e / 288, r = e - k * 288;
+        v[u] = dst[((long long)(k0 + k) * C + c0) * 9 + r];
+      }
+#pragma unroll
+      for (int u = 0; u < U; ++u) {
+        const int e = tid + (b + u) * 256;
+        const int k = e / 288, r = e - k * 288;
+        dst[((long long)(k0 + k) * C + c0) * 9 + r] = v[u] + sm[k * 289 + r];
+      }
+    }
+    return;
+  }
+  const float* __restrict__ src = j.src;
+  for (int b = 0; b < 36; b += U) {                               // OIHW tile, 288 contiguous floats per filter
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int e = tid + (b + u) * 256;
+      const int k = e / 288, r = e - k * 288;
+      v[u] = src[((long long)(k0 + k) * C + c0) * 9 + r];
+    }
+#pragma unroll
+    for (int u = 0; u < U; ++u) {
+      const int e = tid + (b + u) * 256;
+      const int k = e / 288, r = e - k * 288;
+      sm[k * 289 + r] = v[u];
+    }
+  }
+  __syncthreads();
+  float* __restrict__ dst = j.dst;
+  if (j.kind == 5) {                                              // dst [k][tap][c]   (Rp == C)
+#pragma unroll 4
+    for (int e = tid; e < 32 * 9 * 32; e += 256) {
+      const int c = e & 31, tap = (e >> 5) % 9, k = e / 288;
+      dst[((long long)(k0 + k) * 9 + tap) * C + c0 + c] = sm[k * 289 + c * 9 + tap];
+    }
+  } else {                                                        // kind 6: dst [c][flipped tap][k]   (Rp == K)
+#pragma unroll 4
+    for (int e = tid; e < 32 * 9 * 32; e += 256) {
+      const int k = e & 31, tap = (e >> 5) % 9, c = e / 288;
+      dst[((long long)(c0 + c) * 9 + tap) * K + k0 + k] = sm[k * 289 + c * 9 + (8 - tap)];
+    }
+  }
+}
+
+__global__ void __launch_bounds__(256) pack_multi_kernel(const PackJob* __restrict__ jobs, int njobs) {
+  __shared__ float sm_tile[32 * 289];
+  __shared__ int s_job;
+  // the job of this chunk: the last one whose first chunk is <= blockIdx.x.  Every thread looks at one or a few table
+  // entries at once (one memory round trip; a binary search by every thread was six dependent loads per CTA)
+  for (int t = threadIdx.x; t < njobs; t += 256) {
+    const int first = jobs[t].chunk0;
+    const int next = t + 1 < njobs ? jobs[t + 1].chunk0 : 0x7fffffff;
+    if (first <= (int)blockIdx.x && (int)blockIdx.x < next) s_job = t;
+  }
+  __syncthreads();
+  const PackJob j = jobs[s_job];
+  if (j.kind >= 5) {                     // tiled forms: one chunk == one tile
+    pack_tile_3x3(j, blockIdx.x - j.chunk0, sm_tile);
+    return;
+  }
+  const long long begin = (long long)(blockIdx.x - j.chunk0) * kPackChunk;
+  const long long end = begin + kPackChunk < j.total ? begin + kPackChunk : j.total;
+  for (long long i = begin + threadIdx.x; i < end; i += 256) pack_job_elem(j, i);
+}
+
 template <int BN, int KIND>
 int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmArgs& g, int splits, cudaStream_t s) {
   static bool attr_set = false;
@@ -460,8 +687,12 @@ int launch(const CUtensorMap& ma, const CUtensorMap& mb, const GemmArgs& g, int 
                                     Smem<BN, KIND>::kTotal));
     attr_set = true;
   }
-  dim3 grid(fedb_ceil_div(g.M, BM), fedb_ceil_div(g.N, BN), splits);
-  gemm_tc_kernel<BN, KIND><<<grid, kThreads, Smem<BN, KIND>::kTotal, s>>>(ma, mb, g);
+  GemmArgs gp = g;
+  gp.gx = fedb_ceil_div(g.M, BM); gp.gy = fedb_ceil_div(g.N, BN); gp.gz = splits;
+  const long long tiles = (long long)gp.gx * gp.gy * gp.gz;
+  const int slots = fedb_num_sms() * Smem<BN, KIND>::kCtas;
+  const int ctas = (int)(tiles < slots ? tiles : slots);
+  gemm_tc_kernel<BN, KIND><<<ctas, kThreads, Smem<BN, KIND>::kTotal, s>>>(ma, mb, gp);
   FEDB_LAUNCH_OK();
   return 0;
 }
@@ -735,13 +966,16 @@ static int conv_wgrad_impl(const uint16_t* dY, const uint16_t* X, float* dWk, in
   g.d_goff = groups > 1 ? (long long)Cout * taps * Cin : 0;        // dWk of group g: [Cout][taps][Cin] after g such blocks
   static bool attr128 = false, attr64 = false;
   cudaStream_t s = (cudaStream_t)stream;
-  dim3 grid(fedb_ceil_div(Cout, BM), fedb_ceil_div(Cin, bnt) * taps * groups, splits);
+  g.gx = fedb_ceil_div(Cout, BM); g.gy = fedb_ceil_div(Cin, bnt) * taps * groups; g.gz = splits;
+  const long long tiles = (long long)g.gx * g.gy * g.gz;
+  const int slots = fedb_num_sms() * (bnt == 128 ? 1 : Smem<64, 1>::kCtas);
+  const int ctas = (int)(tiles < slots ? tiles : slots);
   if (bnt == 128) {
     if (!attr128) { FEDB_CHECK(cudaFuncSetAttribute(gemm_tc_kernel<128, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem<128, 1>::kTotal)); attr128 = true; }
-    gemm_tc_kernel<128, 1><<<grid, kThreads, Smem<128, 1>::kTotal, s>>>(ma, mb, g);
+    gemm_tc_kernel<128, 1><<<ctas, kThreads, Smem<128, 1>::kTotal, s>>>(ma, mb, g);
   } else {
     if (!attr64) { FEDB_CHECK(cudaFuncSetAttribute(gemm_tc_kernel<64, 1>, cudaFuncAttributeMaxDynamicSharedMemorySize, Smem<64, 1>::kTotal)); attr64 = true; }
-    gemm_tc_kernel<64, 1><<<grid, kThreads, Smem<64, 1>::kTotal, s>>>(ma, mb, g);
+    gemm_tc_kernel<64, 1><<<ctas, kThreads, Smem<64, 1>::kTotal, s>>>(ma, mb, g);
   }
   FEDB_LAUNCH_OK();
   return 0;
@@ -782,6 +1016,19 @@ extern "C" int fedb_pack_filter_grouped(const float* w_oihw, float* out, int K, 
   int blocks = fedb_ceil_div(total, 256);
   if (blocks > fedb_num_sms() * 8) blocks = fedb_num_sms() * 8;
   pack3x3_kernel<<<blocks, 256, 0, (cudaStream_t)stream>>>(w_oihw, out, K, C, mode, taps, Rp, groups);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+
+// jobs_dev: device array of njobs 56-byte records {src, dst, total, kind, K, C, T, Rp, groups, chunk0, pad}; chunk0 is the
+// running sum of ceil(total / FEDB_PACK_CHUNK) over the preceding jobs and total_chunks the sum over all of them (the
+// caller computes both once, when it builds the table)
+extern "C" int fedb_pack_multi(const void* jobs_dev, int njobs, int total_chunks, void* stream) {
+  static_assert(sizeof(PackJob) == 56, "PackJob layout is part of the ABI (fedb200/ops/cuda_gemm.py)");
+  static_assert(kPackChunk == FEDB_PACK_CHUNK, "FEDB_PACK_CHUNK in include/fedb200.h");
+  if (njobs <= 0 || total_chunks <= 0) return 0;
+  FEDB_REQUIRE(jobs_dev != nullptr, "fedb_pack_multi: null job table");
+  pack_multi_kernel<<<total_chunks, 256, 0, (cudaStream_t)stream>>>((const PackJob*)jobs_dev, njobs);
   FEDB_LAUNCH_OK();
   return 0;
 }

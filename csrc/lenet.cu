@@ -838,9 +838,14 @@ __device__ __forceinline__ void matvec_multi(const float* __restrict__ W, const 
   }
 }
 
-__global__ void __launch_bounds__(kThreads, 2) lenet_eval_kernel(const uint8_t* __restrict__ images, Params P,
-                                                               const int64_t* __restrict__ labels, int B,
-                                                               float* __restrict__ loss_rows, float* __restrict__ corr_rows) {
+// kQueue: the CTAs are persistent and pull chunks of kEvalS samples from an atomic counter until the test set is done.  Two
+// launches may share one counter: a small "background" grid that runs next to the training kernels of the following round
+// (the step kernel leaves 148 - 128 SMs idle) and a full-size "finisher" grid that takes whatever is left when the round
+// needs the result - every chunk is scored exactly once, by whoever gets it first.
+// (the chunk body is a separate, non-inlined function: inlined into the queue loop it spilled 400 bytes at 64 registers)
+__device__ __noinline__ void lenet_eval_chunk(const uint8_t* __restrict__ images, const Params& P,
+                                              const int64_t* __restrict__ labels, int B, float* __restrict__ loss_rows,
+                                              float* __restrict__ corr_rows, int chunk) {
   extern __shared__ __align__(16) float sm[];
   float* s_img = sm + SmE::img;
   float* s_w1 = sm + SmE::w1;
@@ -853,9 +858,8 @@ __global__ void __launch_bounds__(kThreads, 2) lenet_eval_kernel(const uint8_t* 
   float* s_h2 = sm + SmE::h2;
   float* s_lg = sm + SmE::lg;
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
-  const int n0 = blockIdx.x * kEvalS;
+  const int n0 = chunk * kEvalS;
   const int ns = min(kEvalS, B - n0);
-  if (ns <= 0) return;
 
   // ---- phase 0: conv weights into padded rows; images as 128-bit loads (HWC bytes), scattered into CHW planes
   {
@@ -967,6 +971,27 @@ __global__ void __launch_bounds__(kThreads, 2) lenet_eval_kernel(const uint8_t* 
   }
 }
 
+template <bool kQueue>
+__global__ void __launch_bounds__(kThreads, 2) lenet_eval_kernel(const uint8_t* __restrict__ images, const __grid_constant__ Params P,
+                                                               const int64_t* __restrict__ labels, int B,
+                                                               float* __restrict__ loss_rows, float* __restrict__ corr_rows,
+                                                               unsigned int* __restrict__ counter) {
+  const int nchunks = (B + kEvalS - 1) / kEvalS;
+  if constexpr (!kQueue) {
+    if ((int)blockIdx.x < nchunks) lenet_eval_chunk(images, P, labels, B, loss_rows, corr_rows, blockIdx.x);
+  } else {
+    __shared__ unsigned int s_chunk;
+    for (;;) {
+      __syncthreads();                                 // everybody is done with the previous chunk's shared memory
+      if (threadIdx.x == 0) s_chunk = atomicAdd(counter, 1u);
+      __syncthreads();
+      const int chunk = (int)s_chunk;
+      if (chunk >= nchunks) return;
+      lenet_eval_chunk(images, P, labels, B, loss_rows, corr_rows, chunk);
+    }
+  }
+}
+
 __global__ void __launch_bounds__(256) stats_kernel(Workspace W, int B, float* __restrict__ stats) {
   __shared__ float sl[256], sc[256];
   float l = 0.f, c = 0.f;
@@ -1002,7 +1027,8 @@ int ensure_smem() {
     FEDB_CHECK(cudaFuncSetAttribute(lenet_sample_kernel<true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
     FEDB_CHECK(cudaFuncSetAttribute(lenet_sample_kernel<false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
     FEDB_CHECK(cudaFuncSetAttribute(lenet_sample_kernel<false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kSmemBytes));
-    FEDB_CHECK(cudaFuncSetAttribute(lenet_eval_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kEvalSmemBytes));
+    FEDB_CHECK(cudaFuncSetAttribute(lenet_eval_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kEvalSmemBytes));
+    FEDB_CHECK(cudaFuncSetAttribute(lenet_eval_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kEvalSmemBytes));
     FEDB_CHECK(cudaFuncSetAttribute(update_kernel<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kUpdateSmemBytes));
     FEDB_CHECK(cudaFuncSetAttribute(update_kernel<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kUpdateSmemBytes));
     done = true;
@@ -1075,8 +1101,42 @@ extern "C" int fedb_lenet_eval(const fedb_lenet_t* net, const uint8_t* images_u8
   const Params P = make_params(net);
   cudaStream_t s = (cudaStream_t)stream;
   FEDB_REQUIRE(((uintptr_t)images_u8 & 15) == 0, "fedb_lenet_eval: images must be 16-byte aligned");
-  lenet_eval_kernel<<<(B + kEvalS - 1) / kEvalS, kThreads, kEvalSmemBytes, s>>>(images_u8, P, labels, B, W.loss_rows, W.corr_rows);
+  lenet_eval_kernel<false><<<(B + kEvalS - 1) / kEvalS, kThreads, kEvalSmemBytes, s>>>(images_u8, P, labels, B, W.loss_rows,
+                                                                                       W.corr_rows, nullptr);
   if (stats) stats_kernel<<<1, 256, 0, s>>>(W, B, stats);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+
+// Evaluation through a work queue (see lenet_eval_kernel<true>).  `counter` is one device word that the caller zeroes
+// before the FIRST launch of an evaluation; every launch that shares it scores the chunks it manages to take.  ctas: grid
+// size of this launch (a handful for the background launch, the whole machine for the finisher).  No statistics here:
+// call fedb_lenet_eval_stats once every launch of the evaluation has finished.
+extern "C" int fedb_lenet_eval_queue(const fedb_lenet_t* net, const uint8_t* images_u8, const int64_t* labels, int B,
+                                     void* workspace, uint32_t* counter, int ctas, void* stream) {
+  FEDB_REQUIRE(net && images_u8 && labels && workspace && counter && B > 0 && ctas > 0, "fedb_lenet_eval_queue: bad arguments");
+  if (int rc = ensure_smem()) return rc;
+  if (int rc = check_offsets(net)) return rc;
+  FEDB_REQUIRE(((uintptr_t)images_u8 & 15) == 0, "fedb_lenet_eval_queue: images must be 16-byte aligned");
+  float* loss_rows = (float*)workspace;
+  float* corr_rows = (float*)((char*)workspace + align_up(sizeof(float) * (size_t)B, 256));
+  const Params P = make_params(net);
+  const int nchunks = (B + kEvalS - 1) / kEvalS;
+  if (ctas > nchunks) ctas = nchunks;
+  lenet_eval_kernel<true><<<ctas, kThreads, kEvalSmemBytes, (cudaStream_t)stream>>>(images_u8, P, labels, B, loss_rows, corr_rows,
+                                                                                    counter);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+
+// stats[0] += mean loss, stats[1] += correct, stats[2] += B, stats[3] += 1 from the per-sample rows of the workspace
+extern "C" int fedb_lenet_eval_stats(void* workspace, int B, float* stats, void* stream) {
+  FEDB_REQUIRE(workspace && stats && B > 0, "fedb_lenet_eval_stats: bad arguments");
+  Workspace W;
+  memset(&W, 0, sizeof(W));
+  W.loss_rows = (float*)workspace;
+  W.corr_rows = (float*)((char*)workspace + align_up(sizeof(float) * (size_t)B, 256));
+  stats_kernel<<<1, 256, 0, (cudaStream_t)stream>>>(W, B, stats);
   FEDB_LAUNCH_OK();
   return 0;
 }

@@ -170,6 +170,15 @@ __global__ void __launch_bounds__(256) bn_partial_kernel(const float* __restrict
 // flight per thread.  BatchNorm is pure memory traffic (8 passes over the activation per training step), so this is
 // what decides its share of a zoo step.
 __device__ __forceinline__ float4 ldf4(const float* p) { return *reinterpret_cast<const float4*>(p); }
+// optional bf16 shadow of a result (the operand format of the tensor-core weight-gradient GEMMs): written by the
+// kernel that PRODUCES the activation / the output gradient, so no separate cast pass reads it again
+__device__ __forceinline__ void st_bf16x4(uint16_t* base, long long i4, float a, float b, float c, float d) {
+  __nv_bfloat162 lo = __floats2bfloat162_rn(a, b), hi = __floats2bfloat162_rn(c, d);
+  uint2 r;
+  r.x = *reinterpret_cast<uint32_t*>(&lo);
+  r.y = *reinterpret_cast<uint32_t*>(&hi);
+  reinterpret_cast<uint2*>(base)[i4] = r;
+}
 
 template <int TX, bool kBwd>
 __global__ void __launch_bounds__(256) bn_partial4_kernel(const float* __restrict__ x, const float* __restrict__ dy,
@@ -230,7 +239,7 @@ __global__ void __launch_bounds__(256) bn_partial4_kernel(const float* __restric
 __global__ void __launch_bounds__(256) bn_apply4_kernel(const float* __restrict__ x, float* __restrict__ y,
                                                        const float* __restrict__ mean, const float* __restrict__ invstd,
                                                        const float* __restrict__ gamma, const float* __restrict__ beta,
-                                                       long long total4, int C, int act) {
+                                                       long long total4, int C, int act, uint16_t* __restrict__ y16) {
   for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total4; i += (long long)gridDim.x * 256) {
     const int c = (int)((i * 4) % C);
     const float4 v = ldf4(x + i * 4), m = ldf4(mean + c), is = ldf4(invstd + c), g = ldf4(gamma + c), b = ldf4(beta + c);
@@ -240,6 +249,7 @@ __global__ void __launch_bounds__(256) bn_apply4_kernel(const float* __restrict_
     o.z = act_fwd(fmaf((v.z - m.z) * is.z, g.z, b.z), act);
     o.w = act_fwd(fmaf((v.w - m.w) * is.w, g.w, b.w), act);
     *reinterpret_cast<float4*>(y + i * 4) = o;
+    if (y16 != nullptr) st_bf16x4(y16, i, o.x, o.y, o.z, o.w);
   }
 }
 
@@ -248,7 +258,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply4_kernel(const float* __restr
                                                            const float* __restrict__ invstd, const float* __restrict__ gamma,
                                                            const float* __restrict__ beta, const float* __restrict__ dgamma,
                                                            const float* __restrict__ dbeta, long long total4, int C,
-                                                           float inv_rows, int act, int training) {
+                                                           float inv_rows, int act, int training, uint16_t* __restrict__ dx16) {
   for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < total4; i += (long long)gridDim.x * 256) {
     const int c = (int)((i * 4) % C);
     const float4 xv = ldf4(x + i * 4), dv = ldf4(dy + i * 4);
@@ -266,6 +276,7 @@ __global__ void __launch_bounds__(256) bn_bwd_apply4_kernel(const float* __restr
       o[k] = training ? gs[k] * iss[k] * (d - dbs[k] * inv_rows - xh * dgs[k] * inv_rows) : gs[k] * iss[k] * d;
     }
     *reinterpret_cast<float4*>(dx + i * 4) = make_float4(o[0], o[1], o[2], o[3]);
+    if (dx16 != nullptr) st_bf16x4(dx16, i, o[0], o[1], o[2], o[3]);
   }
 }
 
@@ -428,10 +439,13 @@ __global__ void __launch_bounds__(256) act_bwd4_kernel(const float4* __restrict_
   }
 }
 __global__ void __launch_bounds__(256) add_act4_kernel(const float4* __restrict__ a, const float4* __restrict__ b,
-                                                      float4* __restrict__ y, long long n4, int act) {
+                                                      float4* __restrict__ y, long long n4, int act,
+                                                      uint16_t* __restrict__ y16) {
   for (long long i = (long long)blockIdx.x * 256 + threadIdx.x; i < n4; i += (long long)gridDim.x * 256) {
     const float4 u = a[i], v = b[i];
-    y[i] = make_float4(act_fwd(u.x + v.x, act), act_fwd(u.y + v.y, act), act_fwd(u.z + v.z, act), act_fwd(u.w + v.w, act));
+    const float4 o = make_float4(act_fwd(u.x + v.x, act), act_fwd(u.y + v.y, act), act_fwd(u.z + v.z, act), act_fwd(u.w + v.w, act));
+    y[i] = o;
+    if (y16 != nullptr) st_bf16x4(y16, i, o.x, o.y, o.z, o.w);
   }
 }
 __device__ __host__ inline bool aligned16(const void* p) { return (reinterpret_cast<uintptr_t>(p) & 15) == 0; }
@@ -787,9 +801,10 @@ static int bn_chunks(long long rows, int C, long long scratch_floats, long long*
   return (int)((rows + *rows_per_chunk - 1) / *rows_per_chunk);
 }
 
-extern "C" int fedb_nn_bn_fwd(const float* x, float* y, float* mean, float* invstd, float* run_mean, float* run_var,
-                              const float* gamma, const float* beta, long long rows, int C, float eps, float momentum,
-                              int training, int act, float* scratch, long long scratch_floats, void* stream) {
+extern "C" int fedb_nn_bn_fwd16(const float* x, float* y, float* mean, float* invstd, float* run_mean, float* run_var,
+                                const float* gamma, const float* beta, long long rows, int C, float eps, float momentum,
+                                int training, int act, float* scratch, long long scratch_floats, uint16_t* y_bf16, void* stream) {
+  FEDB_REQUIRE(y_bf16 == nullptr || C % 4 == 0, "fedb_nn_bn_fwd16: the bf16 shadow needs C % 4 == 0");
   if (training) {
     FEDB_REQUIRE(scratch != nullptr && scratch_floats >= 2LL * C, "fedb_nn_bn_fwd: scratch of at least 2*C floats required");
     long long rpc = 0;
@@ -799,14 +814,21 @@ extern "C" int fedb_nn_bn_fwd(const float* x, float* y, float* mean, float* invs
     bn_finalize_kernel<<<fedb_ceil_div(C, 32), 256, 0, S_>>>(scratch, chunks, mean, invstd, run_mean, run_var, rows, C, eps, momentum);
   }
   else bn_eval_prep_kernel<<<fedb_ceil_div(C, 128), 128, 0, S_>>>(run_mean, run_var, mean, invstd, C, eps);
-  if (C % 4 == 0) bn_apply4_kernel<<<grid_for(rows * C / 4), 256, 0, S_>>>(x, y, mean, invstd, gamma, beta, rows * C / 4, C, act);
+  if (C % 4 == 0) bn_apply4_kernel<<<grid_for(rows * C / 4), 256, 0, S_>>>(x, y, mean, invstd, gamma, beta, rows * C / 4, C, act, y_bf16);
   else bn_apply_kernel<<<grid_for(rows * C), 256, 0, S_>>>(x, y, mean, invstd, gamma, beta, rows * C, C, act);
   FEDB_LAUNCH_OK();
   return 0;
 }
-extern "C" int fedb_nn_bn_bwd(const float* x, const float* dy, float* dx, const float* mean, const float* invstd,
-                              const float* gamma, const float* beta, float* dgamma, float* dbeta, long long rows, int C,
-                              int act, int training, float* scratch, long long scratch_floats, void* stream) {
+extern "C" int fedb_nn_bn_fwd(const float* x, float* y, float* mean, float* invstd, float* run_mean, float* run_var,
+                              const float* gamma, const float* beta, long long rows, int C, float eps, float momentum,
+                              int training, int act, float* scratch, long long scratch_floats, void* stream) {
+  return fedb_nn_bn_fwd16(x, y, mean, invstd, run_mean, run_var, gamma, beta, rows, C, eps, momentum, training, act, scratch,
+                          scratch_floats, nullptr, stream);
+}
+extern "C" int fedb_nn_bn_bwd16(const float* x, const float* dy, float* dx, const float* mean, const float* invstd,
+                                const float* gamma, const float* beta, float* dgamma, float* dbeta, long long rows, int C,
+                                int act, int training, float* scratch, long long scratch_floats, uint16_t* dx_bf16, void* stream) {
+  FEDB_REQUIRE(dx_bf16 == nullptr || C % 4 == 0, "fedb_nn_bn_bwd16: the bf16 shadow needs C % 4 == 0");
   FEDB_REQUIRE(scratch != nullptr && scratch_floats >= 2LL * C, "fedb_nn_bn_bwd: scratch of at least 2*C floats required");
   long long rpc = 0;
   const int chunks = bn_chunks(rows, C, scratch_floats, &rpc);
@@ -815,12 +837,19 @@ extern "C" int fedb_nn_bn_bwd(const float* x, const float* dy, float* dx, const 
   bn_bwd_finalize_kernel<<<fedb_ceil_div(C, 32), 256, 0, S_>>>(scratch, chunks, dgamma, dbeta, C);
   if (C % 4 == 0)
     bn_bwd_apply4_kernel<<<grid_for(rows * C / 4), 256, 0, S_>>>(x, dy, dx, mean, invstd, gamma, beta, dgamma, dbeta, rows * C / 4,
-                                                                C, 1.f / (float)rows, act, training);
+                                                                C, 1.f / (float)rows, act, training, dx_bf16);
   else
     bn_bwd_apply_kernel<<<grid_for(rows * C), 256, 0, S_>>>(x, dy, dx, mean, invstd, gamma, beta, dgamma, dbeta, rows * C, C,
                                                            1.f / (float)rows, act, training);
   FEDB_LAUNCH_OK();
   return 0;
+}
+
+extern "C" int fedb_nn_bn_bwd(const float* x, const float* dy, float* dx, const float* mean, const float* invstd,
+                              const float* gamma, const float* beta, float* dgamma, float* dbeta, long long rows, int C,
+                              int act, int training, float* scratch, long long scratch_floats, void* stream) {
+  return fedb_nn_bn_bwd16(x, dy, dx, mean, invstd, gamma, beta, dgamma, dbeta, rows, C, act, training, scratch, scratch_floats,
+                          nullptr, stream);
 }
 
 extern "C" int fedb_nn_act_fwd(const float* x, float* y, long long n, int act, void* stream) {
@@ -839,13 +868,18 @@ extern "C" int fedb_nn_act_bwd(const float* x, const float* dy, float* dx, long 
   FEDB_LAUNCH_OK();
   return 0;
 }
-extern "C" int fedb_nn_add_act(const float* a, const float* b, float* y, long long n, int act, void* stream) {
-  if (n % 4 == 0 && aligned16(a) && aligned16(b) && aligned16(y))
-    add_act4_kernel<<<grid_for(n / 4), 256, 0, S_>>>((const float4*)a, (const float4*)b, (float4*)y, n / 4, act);
+extern "C" int fedb_nn_add_act16(const float* a, const float* b, float* y, long long n, int act, uint16_t* y_bf16, void* stream) {
+  const bool vec = n % 4 == 0 && aligned16(a) && aligned16(b) && aligned16(y);
+  FEDB_REQUIRE(y_bf16 == nullptr || vec, "fedb_nn_add_act16: the bf16 shadow needs n % 4 == 0 and 16-byte aligned tensors");
+  if (vec)
+    add_act4_kernel<<<grid_for(n / 4), 256, 0, S_>>>((const float4*)a, (const float4*)b, (float4*)y, n / 4, act, y_bf16);
   else
     add_act_kernel<<<grid_for(n), 256, 0, S_>>>(a, b, y, n, act);
   FEDB_LAUNCH_OK();
   return 0;
+}
+extern "C" int fedb_nn_add_act(const float* a, const float* b, float* y, long long n, int act, void* stream) {
+  return fedb_nn_add_act16(a, b, y, n, act, nullptr, stream);
 }
 extern "C" int fedb_nn_scale(const float* x, const float* s, float* y, long long total, long long per_sample, int C, int mode,
                              void* stream) {

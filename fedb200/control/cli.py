@@ -99,6 +99,9 @@ def client_parser() -> argparse.ArgumentParser:
     p.add_argument("--codec", choices=("none", "fp8"), default="none",
                    help="peer plane meaning of -c: none = lossless fp32 words, fp8 = block-scaled e4m3 deltas")
     p.add_argument("--agg-timeout", type=float, default=20.0, help="peer plane: bound of the device-flag waits (s)")
+    p.add_argument("--profile", action="store_true",
+                   help="peer plane: NVTX ranges + device-timed phases of every round (train/agg/repl/eval ms, NVLink bytes, "
+                        "GB/s) as 'round_profile' records in --metrics; synchronises the GPU once per round")
     p.add_argument("--no-multicast", action="store_true",
                    help="peer plane: broadcast with unicast peer stores even where NVLS multicast is available")
     p.add_argument("--dump-root", default=".", help="peer plane: 'dump' descriptors may only write below this directory")
@@ -131,7 +134,7 @@ def client_main(argv=None) -> int:
                             device=dev.index if dev.index is not None else args.peer_rank, dataset=ds, seed=args.seed,
                             tag=args.peer_tag, lr=args.lr, batch_size=args.batch_size, augment=args.augment,
                             codec=args.codec, use_multicast=not (args.no_multicast or args.rejoin), timeout_ns=int(args.agg_timeout * 1e9),
-                            persistent_server=True, rejoin=args.rejoin, eval_mode="inline")
+                            persistent_server=True, rejoin=args.rejoin, eval_mode="inline", profile=args.profile)
         fed.trainer.cfg.checkpoint_path = tcfg.checkpoint_path
         serve_worker(fed.trainer, wcfg, sink=JsonlSink(args.metrics), peer_endpoint=PeerWorker(fed), block=True)
         return 0

@@ -195,15 +195,16 @@ class BackupNode(proto.TrainerServicer):
         os.replace(tmp, os.path.join(self.cfg.state_dir, "coordinator.json"))
 
     def _promote(self):
-        if self.role == "ACTING":
+        if self.role in ("ACTING", "PROMOTING"):
             return
-        self.role = "ACTING"
+        self.role = "PROMOTING"           # "ACTING" only once self.acting exists: observers read the two together
         self.promotions += 1
         self.term += 1
         _, _, state = Coordinator.load_persisted(self.cfg.state_dir)      # B6: reload the replica
         ccfg = replace(self.cfg.coordinator, state_dir=self.cfg.state_dir, backup_target=None)
         self.acting = Coordinator(ccfg, term=self.term, start_round=self.next_round, global_state=state,
                                   sink=self.sink)
+        self.role = "ACTING"
         self.sink.write("promoted", term=self.term, start_round=self.next_round)
         log.warning("primary is down: acting as primary, term %d, from round %d", self.term, self.next_round)
 

@@ -150,6 +150,9 @@ class WorkerServicer(proto.TrainerServicer):
                 except Exception as e:   # noqa: BLE001  (FedbError: the flag protocol gave up on a dead peer)
                     self.sink.write("aggregation_failed", address=self.cfg.address, error=str(e), round=self.round)
                     context.abort(grpc.StatusCode.ABORTED, f"aggregation failed: {e}")
+                prof = self.peer.take_profile() if hasattr(self.peer, "take_profile") else {}
+                if prof:                 # --profile: device-timed phases of this round on this worker's GPU
+                    self.sink.write("round_profile", address=self.cfg.address, round=self.round, term=self.term, **prof)
                 if ev is not None:
                     self.last_eval = ev
                     self.sink.write("eval", address=self.cfg.address, loss=ev.mean_loss, acc=ev.accuracy,

@@ -77,6 +77,8 @@ _SIGS = {
     "fedb_lenet_eval_bytes": (C.c_size_t, [C.c_int]),
     "fedb_lenet_train_step": (C.c_int, [C.POINTER(LeNetDesc), vp, vp, C.c_int, vp, vp, C.c_uint64, vp]),
     "fedb_lenet_eval": (C.c_int, [C.POINTER(LeNetDesc), vp, vp, C.c_int, vp, vp, vp]),
+    "fedb_lenet_eval_queue": (C.c_int, [C.POINTER(LeNetDesc), vp, vp, C.c_int, vp, vp, C.c_int, vp]),
+    "fedb_lenet_eval_stats": (C.c_int, [vp, C.c_int, vp, vp]),
     "fedb_lenet_forward": (C.c_int, [C.POINTER(LeNetDesc), vp, vp, C.c_int, vp, vp, vp]),
     "fedb_lenet_grad": (C.c_int, [C.POINTER(LeNetDesc), vp, vp, C.c_int, vp, vp, vp, vp]),
     "fedb_mem_supported": (C.c_int, [C.c_int, C.POINTER(C.c_int), C.POINTER(C.c_int), C.POINTER(C.c_int)]),

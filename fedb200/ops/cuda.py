@@ -287,6 +287,21 @@ class LeNetPlan:
                                     current_stream()), "fedb_lenet_eval")
         _lib.count_launch(2)
 
+    def eval_queue(self, images_u8: torch.Tensor, labels: torch.Tensor, counter: torch.Tensor, ctas: int,
+                   snapshot: bool = False) -> None:
+        """One launch of the work-queue evaluation (csrc/lenet.cu, lenet_eval_kernel<true>): ``ctas`` persistent CTAs score
+        chunks of the batch until ``counter`` (int32 device word, zeroed by the caller once per evaluation) runs out."""
+        B = images_u8.shape[0]
+        check(lib().fedb_lenet_eval_queue(C.byref(self._eval_desc if snapshot else self.desc), images_u8.data_ptr(),
+                                          labels.data_ptr(), B, self._eval_ws(B).data_ptr(), counter.data_ptr(), ctas,
+                                          current_stream()), "fedb_lenet_eval_queue")
+        _lib.count_launch()
+
+    def eval_queue_stats(self, B: int, stats: torch.Tensor) -> None:
+        check(lib().fedb_lenet_eval_stats(self._eval_ws(B).data_ptr(), B, stats.data_ptr(), current_stream()),
+              "fedb_lenet_eval_stats")
+        _lib.count_launch()
+
     def forward(self, images: torch.Tensor) -> torch.Tensor:
         B = images.shape[0]
         logits = torch.empty(B, 10, dtype=torch.float32, device=images.device)

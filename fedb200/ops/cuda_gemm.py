@@ -16,8 +16,140 @@ import torch
 from . import _lib
 from ._lib import check, current_stream, lib
 
+import os
+
 _fns = {}
 MIN_PIXELS = 128          # below one M tile the generic kernel is as good
+ENABLED = os.environ.get("FEDB200_TC", "1") != "0"      # 0: every convolution takes the generic fp32 kernels (debugging)
+
+
+class PackJob(C.Structure):
+    """One record of the device table walked by fedb_pack_multi (csrc/gemm_tc.cu: struct PackJob, 56 bytes)."""
+    _fields_ = [("src", C.c_void_p), ("dst", C.c_void_p), ("total", C.c_int64), ("kind", C.c_int32), ("K", C.c_int32),
+                ("C", C.c_int32), ("T", C.c_int32), ("Rp", C.c_int32), ("groups", C.c_int32), ("chunk0", C.c_int32),
+                ("pad_", C.c_int32)]
+
+
+PACK_CHUNK = 9216         # FEDB_PACK_CHUNK: elements per CTA of fedb_pack_multi
+
+
+_SCOPE = None             # the StepScope of the training step / evaluation pass that is running (None: no caching)
+
+
+def scope():
+    return _SCOPE
+
+
+class StepScope:
+    """Everything about a model's convolutions that is the same in every step, kept across steps.
+
+    Outside a scope every convolution call packs its filter for the tensor-core kernel, casts its operands to bf16 for
+    the weight gradient, zero-fills a packed gradient and un-packs it again - about eight small launches per layer and
+    step.  Inside a scope (the engine opens one around every training step and around every evaluation pass):
+      * packed filters live in persistent buffers; ``begin()`` refreshes ALL of them with one launch
+        (fedb_pack_multi) after the weights changed - a layer met for the first time is packed on the spot and joins
+        the table;
+      * weight gradients are accumulated by the split-K kernels into persistent packed buffers and
+        ``end_backward()`` adds ALL of them into the gradient arena (and clears them) with one launch;
+      * gradients go straight into the arena views (``param.grad``) instead of through autograd's accumulation;
+      * BatchNorm / residual-add kernels leave a bf16 shadow of their output next to it (``tensor._fedb_bf16``), the
+        operand format of the weight-gradient GEMM, so no cast pass re-reads the activation.
+    The addresses in the job tables never change, so a captured CUDA graph replays them.  Weights must not change
+    between ``begin()`` and the last use of the step (they do not: SGD runs after ``end_backward()``)."""
+
+    def __init__(self, device, train: bool):
+        self.device, self.train = torch.device(device), train
+        self.pack, self.pack_jobs = {}, []
+        self.unpack, self.unpack_jobs = {}, []
+        self._tables = {}
+        self._retired = []          # tables a captured graph may still read
+        self._prev = None
+
+    def __enter__(self):
+        global _SCOPE
+        self._prev, _SCOPE = _SCOPE, self
+        return self
+
+    def __exit__(self, *exc):
+        global _SCOPE
+        _SCOPE = self._prev
+        return False
+
+    # ---- tables
+    def _table(self, which, jobs):
+        tab = self._tables.get(which)
+        if tab is None or tab[1] != len(jobs):
+            chunks = 0
+            for j in jobs:                               # prefix sum: where each job's CTAs start in the flat grid
+                j.chunk0 = chunks
+                chunks += (j.total + PACK_CHUNK - 1) // PACK_CHUNK
+            raw = bytes((PackJob * len(jobs))(*jobs))
+            dev = torch.frombuffer(bytearray(raw), dtype=torch.uint8).to(self.device)
+            if tab is not None:
+                self._retired.append(tab[0])
+            tab = (dev, len(jobs), chunks)
+            self._tables[which] = tab
+        return tab
+
+    def sync_tables(self) -> None:
+        """Uploads the job tables now (a plain H2D copy): call after a warm-up pass and BEFORE capturing a graph."""
+        if self.pack_jobs:
+            self._table("pack", self.pack_jobs)
+        if self.unpack_jobs:
+            self._table("unpack", self.unpack_jobs)
+
+    def _run(self, which, jobs):
+        if not jobs:
+            return
+        dev, n, chunks = self._table(which, jobs)
+        check(_f("fedb_pack_multi")(dev.data_ptr(), n, chunks, current_stream()), "fedb_pack_multi")
+        _lib.count_launch()
+
+    def begin(self) -> None:
+        """The weights may have changed since the last step / pass: refresh every packed filter (one launch)."""
+        self._run("pack", self.pack_jobs)
+
+    def end_backward(self) -> None:
+        """Packed weight gradients -> += gradient arena, packed buffers cleared (one launch)."""
+        self._run("unpack", self.unpack_jobs)
+
+    # ---- registration
+    def packed(self, w, kind: int, K: int, Cc: int, T: int, Rp: int, groups: int, n_out: int) -> torch.Tensor:
+        key = (w.data_ptr(), kind, K, Cc, T, Rp, groups)
+        t = self.pack.get(key)
+        if t is None:
+            if kind in (0, 1) and T == 9 and groups == 1 and K % 32 == 0 and Cc % 32 == 0:
+                kind += 5                                # coalesced 32 x 32 x 9 tiles (no padding in either layout)
+            t = torch.empty(n_out, dtype=torch.float32, device=w.device)
+            job = PackJob(w.data_ptr(), t.data_ptr(), n_out, kind, K, Cc, T, Rp, groups, 0, 0)
+            self.pack[key] = t
+            self.pack_jobs.append(job)
+            first = PackJob(w.data_ptr(), t.data_ptr(), n_out, kind, K, Cc, T, Rp, groups, 0, 0)   # a table of one, now
+            one = torch.frombuffer(bytearray(bytes(first)), dtype=torch.uint8).to(self.device)
+            check(_f("fedb_pack_multi")(one.data_ptr(), 1, (n_out + PACK_CHUNK - 1) // PACK_CHUNK, current_stream()),
+                  "fedb_pack_multi")
+            _lib.count_launch()
+            self._retired.append(one)
+        return t
+
+    def wgrad_buffer(self, grad: torch.Tensor, K: int, Cc: int, T: int) -> torch.Tensor:
+        """Persistent zeroed [K][T][Cc] accumulator whose content ``end_backward()`` adds into ``grad`` (OIHW)."""
+        key = (grad.data_ptr(), K, Cc, T)
+        t = self.unpack.get(key)
+        if t is None:
+            t = torch.zeros(K * T * Cc, dtype=torch.float32, device=grad.device)
+            self.unpack[key] = t
+            kind = 7 if (T == 9 and K % 32 == 0 and Cc % 32 == 0) else 2
+            self.unpack_jobs.append(PackJob(t.data_ptr(), grad.data_ptr(), K * T * Cc, kind, K, Cc, T, 0, 1, 0, 0))
+        return t
+
+
+def bf16_of(t: torch.Tensor):
+    """The bf16 shadow a producer kernel left next to ``t`` (None when there is none)."""
+    s16 = getattr(t, "_fedb_bf16", None)
+    if s16 is not None and s16.numel() == t.numel():
+        return s16
+    return None
 
 
 def _f(name):
@@ -36,6 +168,7 @@ def _f(name):
             "fedb_conv_tf32": [vp, vp, vp, vp, i, i, i, i, i, i, i, i, i, vp],
             "fedb_conv_wgrad_bf16": [vp, vp, vp, i, i, i, i, i, i, i, i, i, vp],
             "fedb_pack_filter": [vp, vp, i, i, i, i, vp],
+            "fedb_pack_multi": [vp, i, i, vp],
             "fedb_pack_dgrad_s2": [vp, vp, i, i, vp],
             "fedb_im2col_small": [vp, vp, vp, i, i, i, i, i, i, i, vp],
             "fedb_conv_tf32_g": [vp, vp, vp, vp, i, i, i, i, i, i, i, i, i, ll, ll, vp],
@@ -76,9 +209,11 @@ def cast_bf16(x: torch.Tensor) -> torch.Tensor:
 
 def cast_bf16_rows(x: torch.Tensor, rows: int, C: int):
     """bf16 copy of an fp32 [rows][C] matrix (an NHWC activation flattened over pixels) and its row pitch in elements:
-    C itself when that already is a 16-byte pitch, else C rounded up to 8 with zero columns."""
+    C itself when that already is a 16-byte pitch, else C rounded up to 8 with zero columns.  A shadow left by the
+    kernel that produced ``x`` is used as it is."""
     if C % 8 == 0:
-        return cast_bf16(x), C
+        s16 = bf16_of(x)
+        return (s16 if s16 is not None else cast_bf16(x)), C
     Cp = (C + 7) // 8 * 8
     out = torch.empty(rows * Cp, dtype=torch.bfloat16, device=x.device)
     check(_f("fedb_cast_bf16_pad")(x.data_ptr(), out.data_ptr(), rows, C, Cp, current_stream()), "fedb_cast_bf16_pad")
@@ -87,6 +222,8 @@ def cast_bf16_rows(x: torch.Tensor, rows: int, C: int):
 
 
 def transpose(w2d: torch.Tensor, rows: int, cols: int) -> torch.Tensor:
+    if _SCOPE is not None:
+        return _SCOPE.packed(w2d, 4, rows, cols, 1, 0, 1, rows * cols)
     out = torch.empty(rows * cols, dtype=torch.float32, device=w2d.device)
     check(_f("fedb_transpose")(w2d.data_ptr(), out.data_ptr(), rows, cols, current_stream()), "fedb_transpose")
     _lib.count_launch()
@@ -145,6 +282,8 @@ def pack_filter(w, mode: int, taps: int) -> torch.Tensor:
     """mode 0: OIHW -> [K][tap][C padded to 32] (forward); mode 1: -> [C][flipped tap][K padded to 32] (data gradient)."""
     K, Cc = w.shape[0], w.shape[1]
     n = K * taps * _pad32(Cc) if mode == 0 else Cc * 9 * _pad32(K)
+    if _SCOPE is not None and (mode == 0 or taps == 9):
+        return _SCOPE.packed(w, mode, K, Cc, taps, _pad32(Cc) if mode == 0 else _pad32(K), 1, n)
     out = torch.empty(n, dtype=torch.float32, device=w.device)
     check(_f("fedb_pack_filter")(w.data_ptr(), out.data_ptr(), K, Cc, mode, taps, current_stream()), "fedb_pack_filter")
     _lib.count_launch()
@@ -300,6 +439,8 @@ def _grouped_wgrad(x, dy, dw, db, shp, Cg, Kg) -> bool:
 
 
 def conv_forward(x, w, bias, y, shp) -> bool:
+    if not ENABLED:
+        return False
     gg = _group_geometry(shp, "fwd")
     if gg is not None:
         return _grouped_forward(x, w, bias, y, shp, *gg)
@@ -333,6 +474,8 @@ def conv_forward(x, w, bias, y, shp) -> bool:
 
 
 def conv_dgrad(dy, w, dx, shp) -> bool:
+    if not ENABLED:
+        return False
     gg = _group_geometry(shp, "dgrad")
     if gg is not None:
         return _grouped_dgrad(dy, w, dx, shp, *gg)
@@ -347,7 +490,9 @@ def conv_dgrad(dy, w, dx, shp) -> bool:
         # stride 2: four parity classes of dX, each a dense stride-1 implicit GEMM over dY, scattered by the epilogue
         N, H, W, Cc, K, _, _, P, Q = shp[:9]
         fs = st[0]
-        if fs == 3:
+        if fs == 3 and _SCOPE is not None:
+            wc = _SCOPE.packed(w, 3, K, Cc, 9, _pad32(K), 1, 9 * _pad32(K) * Cc)
+        elif fs == 3:
             wc = torch.empty(9 * _pad32(K) * Cc, dtype=torch.float32, device=w.device)
             check(_f("fedb_pack_dgrad_s2")(w.data_ptr(), wc.data_ptr(), K, Cc, current_stream()), "fedb_pack_dgrad_s2")
             _lib.count_launch()
@@ -366,7 +511,11 @@ def conv_dgrad(dy, w, dx, shp) -> bool:
     return True
 
 
-def conv_wgrad(x, dy, dw, db, shp) -> bool:
+def conv_wgrad(x, dy, dw, db, shp, direct: bool = False) -> bool:
+    """``direct``: ``dw`` is the parameter's slot in the gradient arena itself (stable address), so inside a training
+    scope the packed accumulator can be kept and un-packed by the step's single ``end_backward()`` launch."""
+    if not ENABLED:
+        return False
     gg = _group_geometry(shp, "wgrad")
     if gg is not None:
         return _grouped_wgrad(x, dy, dw, db, shp, *gg)
@@ -389,15 +538,17 @@ def conv_wgrad(x, dy, dw, db, shp) -> bool:
         pix = N * H * W
         tiles = ((K + 127) // 128) * ((Cc + 127) // 128) * 9
         splits = max(1, min(pix // 256, 444 // max(tiles, 1)))
-        dwk = torch.zeros(K * 9 * Cc, dtype=torch.float32, device=x.device)
+        kept = _SCOPE is not None and _SCOPE.train and direct
+        dwk = _SCOPE.wgrad_buffer(dw, K, Cc, 9) if kept else torch.zeros(K * 9 * Cc, dtype=torch.float32, device=x.device)
         # keep both alive: two temporaries would share one allocation; channel counts that are not multiples of 8 get
         # zero columns so that the bf16 rows keep a 16-byte pitch
         (dy16, kp), (x16, cp) = cast_bf16_rows(dy, pix, K), cast_bf16_rows(x, pix, Cc)
         check(_f("fedb_conv_wgrad_bf16_g")(dy16.data_ptr(), x16.data_ptr(), dwk.data_ptr(), N, H, W, Cc, K, 3, 1, 1,
                                            splits, kp, cp, current_stream()), "fedb_conv_wgrad_bf16_g")
         _lib.count_launch()
-        check(_f("fedb_pack3x3")(dwk.data_ptr(), dw.data_ptr(), K, Cc, 2, current_stream()), "fedb_pack3x3")   # += into OIHW
-        _lib.count_launch()
+        if not kept:
+            check(_f("fedb_pack3x3")(dwk.data_ptr(), dw.data_ptr(), K, Cc, 2, current_stream()), "fedb_pack3x3")   # += into OIHW
+            _lib.count_launch()
         if db is not None:
             db += dy.sum(dim=(0, 2, 3))
         return True
@@ -409,11 +560,13 @@ def conv_wgrad(x, dy, dw, db, shp) -> bool:
         tiles = ((K + 127) // 128) * ((Cc + 127) // 128) * taps
         splits = max(1, min(pix // 256, 444 // max(tiles, 1)))
         (dy16, kp), (x16, cp) = cast_bf16_rows(dy, pix, K), cast_bf16_rows(x, N * H * W, Cc)
-        dwk = torch.zeros(K * taps * Cc, dtype=torch.float32, device=x.device) if taps > 1 else dw
+        kept = _SCOPE is not None and _SCOPE.train and direct and taps > 1
+        dwk = dw if taps == 1 else (_SCOPE.wgrad_buffer(dw, K, Cc, taps) if kept else
+                                    torch.zeros(K * taps * Cc, dtype=torch.float32, device=x.device))
         check(_f("fedb_conv_wgrad_bf16_g")(dy16.data_ptr(), x16.data_ptr(), dwk.data_ptr(), N, H, W, Cc, K, fs, stride, pad,
                                            splits, kp, cp, current_stream()), "fedb_conv_wgrad_bf16_g")
         _lib.count_launch()
-        if taps > 1:
+        if taps > 1 and not kept:
             check(_f("fedb_pack_filter")(dwk.data_ptr(), dw.data_ptr(), K, Cc, 2, taps, current_stream()), "fedb_pack_filter")
             _lib.count_launch()
         if db is not None:

@@ -1,5 +1,5 @@
 """Autograd bindings of the generic NHWC kernels (csrc/nn_generic.cu) and the tcgen05 GEMM/conv
-paths (csrc/gemm_tc.cu, csrc/conv_tc.cu) - the op set behind ``fedb200.ops.functional`` on CUDA.
+paths (csrc/gemm_tc.cu) - the op set behind ``fedb200.ops.functional`` on CUDA.
 
 Layout contract: activations are 4-D tensors in ``channels_last`` memory format (NHWC bytes, NCHW
 shape), fp32.  Every function makes its inputs channels_last-contiguous (a no-op when they already
@@ -34,11 +34,11 @@ def _bind():
         "fedb_nn_conv_fwd": [_vp, _vp, _vp, _vp, ip, _vp],
         "fedb_nn_conv_dgrad": [_vp, _vp, _vp, ip, _vp],
         "fedb_nn_conv_wgrad": [_vp, _vp, _vp, _vp, ip, _vp],
-        "fedb_nn_bn_fwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _f, _f, _i, _i, _vp, _ll, _vp],
-        "fedb_nn_bn_bwd": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _i, _i, _vp, _ll, _vp],
+        "fedb_nn_bn_fwd16": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _f, _f, _i, _i, _vp, _ll, _vp, _vp],
+        "fedb_nn_bn_bwd16": [_vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _vp, _ll, _i, _i, _i, _vp, _ll, _vp, _vp],
         "fedb_nn_act_fwd": [_vp, _vp, _ll, _i, _vp],
         "fedb_nn_act_bwd": [_vp, _vp, _vp, _ll, _i, _vp],
-        "fedb_nn_add_act": [_vp, _vp, _vp, _ll, _i, _vp],
+        "fedb_nn_add_act16": [_vp, _vp, _vp, _ll, _i, _vp, _vp],
         "fedb_nn_scale": [_vp, _vp, _vp, _ll, _ll, _i, _i, _vp],
         "fedb_nn_scale_bwd_gate": [_vp, _vp, _vp, _i, _i, _i, _vp],
         "fedb_nn_bernoulli_mask": [_vp, _ll, _f, C.c_uint64, _vp, _vp],
@@ -75,6 +75,31 @@ def _ints(*v):
     return (C.c_int * len(v))(*v)
 
 
+def _train_scope():
+    """The training-step scope of cuda_gemm when one is open (engine's step), else None."""
+    from . import cuda_gemm
+    sc = cuda_gemm.scope()
+    return sc if (sc is not None and sc.train) else None
+
+
+def _direct_grad(p):
+    """Inside a training scope parameter gradients are written straight into ``p.grad`` - the parameter's slot of the
+    gradient arena, zeroed at the start of the step - and autograd is handed None: no temporary, no accumulation
+    kernel.  Outside (plain ``loss.backward()`` of user code) the gradient is returned as usual."""
+    if p is None or _train_scope() is None:
+        return None
+    g = p.grad
+    return g if (g is not None and g.is_contiguous() and g.dtype == torch.float32) else None
+
+
+def _shadow(t: torch.Tensor):
+    """bf16 buffer for the shadow copy a producer kernel writes next to its fp32 result (training scope only; the
+    flat size must allow 8-byte stores)."""
+    if _train_scope() is None or t.dim() != 4 or t.shape[1] % 8 != 0:
+        return None
+    return torch.empty(t.numel(), dtype=torch.bfloat16, device=t.device)
+
+
 # ------------------------------------------------------------------------------------ convolution
 def _conv_shape(x, w, stride, padding, groups):
     N, Cc, H, W = x.shape
@@ -103,8 +128,9 @@ class _Conv2d(torch.autograd.Function):
         shp = _conv_shape(x, w, stride, padding, groups)
         N, H, W, Cc, K, R, S, P, Q = shp[:9]
         y = torch.empty((N, K, P, Q), dtype=torch.float32, device=x.device, memory_format=CL)
-        from . import cuda_tc
+        from . import cuda_gemm as cuda_tc
         ctx.dw = _is_depthwise(shp)
+        ctx.gw, ctx.gb = _direct_grad(w), _direct_grad(bias)
         if ctx.dw:
             ctx.tc = False
             _call("fedb_dw_conv_fwd_k", x.data_ptr(), w.data_ptr(), _p(bias), y.data_ptr(), _dw_shape(shp), R, current_stream())
@@ -117,29 +143,38 @@ class _Conv2d(torch.autograd.Function):
             _call("fedb_nn_conv_fwd", x.data_ptr(), wt.data_ptr(), _p(bias), y.data_ptr(), _ints(*shp), current_stream())
         ctx.save_for_backward(x, w)
         ctx.shp, ctx.has_bias = shp, bias is not None
+        from .cuda_gemm import bf16_of
+        ctx.x16 = bf16_of(x)                 # shadow left by the producer of x: kept for the weight gradient
         return y
 
     @staticmethod
     def backward(ctx, dy):
         x, w = ctx.saved_tensors
+        if ctx.x16 is not None:
+            x._fedb_bf16 = ctx.x16
         shp = ctx.shp
         N, H, W, Cc, K, R, S, P, Q = shp[:9]
         groups = shp[13]
         dy = _cl(dy)
         dx = dw = db = None
-        from . import cuda_tc
+        from . import cuda_gemm as cuda_tc
+        direct = ctx.gw is not None and (not ctx.has_bias or ctx.gb is not None)
         if ctx.dw:
             if ctx.needs_input_grad[0]:
                 dx = torch.empty_like(x, memory_format=CL)
                 _call("fedb_dw_conv_dgrad_k", dy.data_ptr(), w.data_ptr(), dx.data_ptr(), _dw_shape(shp), R, current_stream())
             if ctx.needs_input_grad[1]:
-                dw = torch.zeros_like(w)
+                dw = ctx.gw if direct else torch.zeros_like(w)
                 ds = _dw_shape(shp)
                 _bind()
                 scratch = torch.empty(int(lib().fedb_dw_conv_wgrad_scratch_k(ds, R)), dtype=torch.float32, device=x.device)
                 _call("fedb_dw_conv_wgrad_k", x.data_ptr(), dy.data_ptr(), dw.data_ptr(), scratch.data_ptr(), ds, R,
                       current_stream(), launches=2)
                 db = dy.sum(dim=(0, 2, 3)) if ctx.has_bias else None
+                if direct:
+                    if db is not None:
+                        ctx.gb += db
+                    dw = db = None
             return dx, dw, db, None, None, None
         if ctx.needs_input_grad[0]:
             dx = torch.empty_like(x, memory_format=CL)
@@ -148,10 +183,12 @@ class _Conv2d(torch.autograd.Function):
                 _call("fedb_nn_weight_transpose", w.data_ptr(), 0, wt2.data_ptr(), K, Cc // groups, R, S, current_stream())
                 _call("fedb_nn_conv_dgrad", dy.data_ptr(), wt2.data_ptr(), dx.data_ptr(), _ints(*shp), current_stream())
         if ctx.needs_input_grad[1]:
-            dw = torch.zeros_like(w)
-            db = torch.zeros(K, dtype=torch.float32, device=x.device) if ctx.has_bias else None
-            if not cuda_tc.conv_wgrad(x, dy, dw, db, shp):
+            dw = ctx.gw if direct else torch.zeros_like(w)
+            db = (ctx.gb if direct else torch.zeros(K, dtype=torch.float32, device=x.device)) if ctx.has_bias else None
+            if not cuda_tc.conv_wgrad(x, dy, dw, db, shp, direct=direct):
                 _call("fedb_nn_conv_wgrad", x.data_ptr(), dy.data_ptr(), dw.data_ptr(), _p(db), _ints(*shp), current_stream())
+            if direct:
+                dw = db = None
         return dx, dw, db, None, None, None
 
 
@@ -170,11 +207,15 @@ class _BatchNorm(torch.autograd.Function):
         mean = torch.empty(Cc, dtype=torch.float32, device=x.device)
         invstd = torch.empty(Cc, dtype=torch.float32, device=x.device)
         scratch = torch.empty(2 * Cc * _BN_CHUNKS, dtype=torch.float32, device=x.device) if training else None
-        _call("fedb_nn_bn_fwd", x.data_ptr(), y.data_ptr(), mean.data_ptr(), invstd.data_ptr(), run_mean.data_ptr(),
+        y16 = _shadow(y) if training else None
+        _call("fedb_nn_bn_fwd16", x.data_ptr(), y.data_ptr(), mean.data_ptr(), invstd.data_ptr(), run_mean.data_ptr(),
               run_var.data_ptr(), gamma.data_ptr(), beta.data_ptr(), rows, Cc, eps, momentum, int(training), act,
-              _p(scratch), 2 * Cc * _BN_CHUNKS, current_stream(), launches=3 if training else 2)
+              _p(scratch), 2 * Cc * _BN_CHUNKS, _p(y16), current_stream(), launches=3 if training else 2)
         ctx.save_for_backward(x, gamma, beta, mean, invstd)
         ctx.act, ctx.rows, ctx.training = act, rows, bool(training)
+        ctx.gg, ctx.gbeta = _direct_grad(gamma), _direct_grad(beta)
+        if y16 is not None:
+            y._fedb_bf16 = y16
         return y
 
     @staticmethod
@@ -183,12 +224,19 @@ class _BatchNorm(torch.autograd.Function):
         dy = _cl(dy)
         Cc = x.shape[1]
         dx = torch.empty_like(x, memory_format=CL)
-        dgamma = torch.empty(Cc, dtype=torch.float32, device=x.device)
-        dbeta = torch.empty(Cc, dtype=torch.float32, device=x.device)
+        # each BatchNorm is used once per step, so writing its two gradients into the (zeroed) arena slots IS accumulating
+        direct = ctx.gg is not None and ctx.gbeta is not None
+        dgamma = ctx.gg if direct else torch.empty(Cc, dtype=torch.float32, device=x.device)
+        dbeta = ctx.gbeta if direct else torch.empty(Cc, dtype=torch.float32, device=x.device)
         scratch = torch.empty(2 * Cc * _BN_CHUNKS, dtype=torch.float32, device=x.device)
-        _call("fedb_nn_bn_bwd", x.data_ptr(), dy.data_ptr(), dx.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
+        dx16 = _shadow(dx)
+        _call("fedb_nn_bn_bwd16", x.data_ptr(), dy.data_ptr(), dx.data_ptr(), mean.data_ptr(), invstd.data_ptr(),
               gamma.data_ptr(), beta.data_ptr(), dgamma.data_ptr(), dbeta.data_ptr(), ctx.rows, Cc, ctx.act,
-              int(ctx.training), scratch.data_ptr(), 2 * Cc * _BN_CHUNKS, current_stream(), launches=3)
+              int(ctx.training), scratch.data_ptr(), 2 * Cc * _BN_CHUNKS, _p(dx16), current_stream(), launches=3)
+        if dx16 is not None:
+            dx._fedb_bf16 = dx16
+        if direct:
+            return dx, None, None, None, None, None, None, None, None
         return dx, dgamma, dbeta, None, None, None, None, None, None
 
 
@@ -247,7 +295,10 @@ class _AddAct(torch.autograd.Function):
         a = _cl(a)
         b = _match(b, a)
         y = torch.empty_like(a)
-        _call("fedb_nn_add_act", a.data_ptr(), b.data_ptr(), y.data_ptr(), a.numel(), act, current_stream())
+        y16 = _shadow(y)
+        _call("fedb_nn_add_act16", a.data_ptr(), b.data_ptr(), y.data_ptr(), a.numel(), act, _p(y16), current_stream())
+        if y16 is not None:
+            y._fedb_bf16 = y16
         if act:
             ctx.save_for_backward(y)
         ctx.act = act
@@ -469,11 +520,11 @@ class _Linear(torch.autograd.Function):
         B, Kd = x.shape
         J = w.shape[0]
         y = torch.empty((B, J), dtype=torch.float32, device=x.device)
-        from . import cuda_tc
-        if not cuda_tc.linear_forward(x, w, bias, y, act):
-            _call("fedb_nn_linear_fwd", x.data_ptr(), w.data_ptr(), _p(bias), y.data_ptr(), B, Kd, J, act, current_stream())
+        # classifier heads of the zoo are [batch, <=512] x [10, <=512]: far below a tensor-core tile, CUDA-core kernels
+        _call("fedb_nn_linear_fwd", x.data_ptr(), w.data_ptr(), _p(bias), y.data_ptr(), B, Kd, J, act, current_stream())
         ctx.save_for_backward(x, w, y if act else None)
         ctx.act, ctx.has_bias = act, bias is not None
+        ctx.gw, ctx.gb = _direct_grad(w), _direct_grad(bias)
         return y
 
     @staticmethod
@@ -487,10 +538,13 @@ class _Linear(torch.autograd.Function):
         B, Kd = x.shape
         J = w.shape[0]
         dx = torch.empty_like(x) if ctx.needs_input_grad[0] else None
-        dw = torch.zeros_like(w) if ctx.needs_input_grad[1] else None
-        db = torch.zeros(J, dtype=torch.float32, device=x.device) if (ctx.has_bias and dw is not None) else None
+        direct = ctx.gw is not None and (not ctx.has_bias or ctx.gb is not None) and ctx.needs_input_grad[1]
+        dw = (ctx.gw if direct else torch.zeros_like(w)) if ctx.needs_input_grad[1] else None
+        db = (ctx.gb if direct else torch.zeros(J, dtype=torch.float32, device=x.device)) if (ctx.has_bias and dw is not None) else None
         _call("fedb_nn_linear_bwd", dy.data_ptr(), x.data_ptr(), w.data_ptr(), _p(dx), _p(dw), _p(db), B, Kd, J,
               current_stream(), launches=2)
+        if direct:
+            dw = db = None
         return dx, dw, db, None
 
 

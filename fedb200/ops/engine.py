@@ -75,6 +75,11 @@ class CudaEngine:
         for sh in self._shards.values():
             sh["graph"] = None
         self._eval_graph = None
+        # per-model caches of the convolution glue (packed filters, packed gradient accumulators): they hold addresses of
+        # the arena, so they start over with it
+        from . import cuda_gemm
+        self.scope = cuda_gemm.StepScope(self.dev, train=True)
+        self.eval_scope = cuda_gemm.StepScope(self.dev, train=False)
         with torch.cuda.device(self.dev):
             if self.is_lenet:
                 self.plan = K.LeNetPlan(arena, self.cfg.lr, self.cfg.momentum, self.cfg.weight_decay,
@@ -101,13 +106,70 @@ class CudaEngine:
                 self.snap = Arena(self.arena.manifest, self.dev)
                 self.plan.bind_eval_params(self.snap.f32)
             else:
+                from . import cuda_gemm
                 self.eval_model = models.build(self.cfg.model).to(self.dev)
                 self.snap = Arena.adopt(self.eval_model, self.dev)
                 self.eval_model.eval()
+                self.snap_scope = cuda_gemm.StepScope(self.dev, train=False)
             self.eval_stream = torch.cuda.Stream(device=self.dev)
             self.eval_copy_stream = torch.cuda.Stream(device=self.dev)
             self.eval_stats_prev = torch.zeros(4, dtype=torch.float32, device=self.dev)
         self._eval_graph = None
+
+    # ---- LeNet: the overlapped evaluation as a work queue shared by a background launch and a finisher
+    def queue_eval_available(self, upload: bool) -> bool:
+        """The fused LeNet kernels and a test set that is already on the device (with ``upload`` it rode in the training
+        pass's graph; without, the resident copy of an earlier round is scored, as ``eval_pass`` does)."""
+        return self.is_lenet and self.snap is not None and (self._test_resident or not upload) and self._test_dev is not None
+
+    def queue_eval_start(self) -> None:
+        """On the evaluation stream, after the snapshot: zero the chunk counter and start the background CTAs - as many
+        as the training step leaves SMs idle (its sample kernel runs one CTA per sample of a batch, 128 of 148 SMs), so
+        they never take an SM from it."""
+        if not hasattr(self, "_q_counter"):
+            self._q_counter = torch.zeros(1, dtype=torch.int32, device=self.dev)
+            props = torch.cuda.get_device_properties(self.dev)
+            self._sms = props.multi_processor_count
+        imgs, labels = self._test_images(), self._test_dev[1]
+        self._q = (imgs, labels, int(imgs.shape[0]))
+        self._test_resident = False
+        self._q_counter.zero_()
+        import os
+        idle = max(self._sms - self.cfg.batch_size, 0)
+        idle = int(os.environ.get("FEDB200_EVAL_BG_CTAS", idle))
+        if idle > 0:
+            self.plan.eval_queue(imgs, labels, self._q_counter, idle, snapshot=True)
+
+    def queue_eval_finish(self) -> None:
+        """On the training stream, when the result is needed: a full-size launch takes the chunks that are left (none
+        when the background CTAs had a whole local pass to themselves)."""
+        imgs, labels, n = self._q
+        self.plan.eval_queue(imgs, labels, self._q_counter, 2 * self._sms, snapshot=True)
+
+    def join_overlapped_eval(self, keep: bool = False) -> None:
+        """The current stream waits for the evaluation in flight on the second stream (a queue evaluation is first helped
+        to its end by a full-size launch, then reduced).  In steady state it ended long ago (it is a fraction of a local
+        pass); the wait is what makes it safe to overwrite the snapshot and, two rounds later, the half of the test-set
+        double buffer it read.  ``keep`` parks the finished counters in ``eval_stats_prev`` for the round's result copy.
+        Idempotent."""
+        ev = getattr(self, "_eval_done", None)
+        if ev is None:
+            return
+        cur = torch.cuda.current_stream(self.dev)
+        queued = getattr(self, "_q", None) is not None
+        if queued:
+            self.queue_eval_finish()         # takes what the background CTAs have not scored yet, at full width
+        cur.wait_event(ev)
+        if queued:
+            self.queue_eval_stats()
+        if keep:
+            self.eval_stats_prev.copy_(self.eval_stats, non_blocking=True)
+
+    def queue_eval_stats(self) -> None:
+        """After BOTH launches have ended: fixed-order reduction of the per-sample rows into ``eval_stats``."""
+        self.eval_stats.zero_()
+        self.plan.eval_queue_stats(self._q[2], self.eval_stats)
+        self._q = None
 
     def snapshot(self) -> None:
         """arena -> snapshot on the current stream (one K-BCAST launch over local memory)."""
@@ -239,12 +301,15 @@ class CudaEngine:
 
     def _generic_step(self, x_u8, y, seed):
         a, cfg = self.arena, self.cfg
-        x = K.prepare_batch(x_u8, nhwc=True, augment=cfg.augment, seed=seed, seed_dev=self.seed_dev)
-        a.grad.zero_()
-        out = self.t.model(x)
-        dlogits = torch.empty_like(out)
-        K.cross_entropy_raw(out.detach().contiguous(), y, dlogits, None, self.stats)
-        out.backward(dlogits)
+        with self.scope as sc:
+            sc.begin()                                   # every packed filter of the model, one launch
+            x = K.prepare_batch(x_u8, nhwc=True, augment=cfg.augment, seed=seed, seed_dev=self.seed_dev)
+            a.grad.zero_()
+            out = self.t.model(x)
+            dlogits = torch.empty_like(out)
+            K.cross_entropy_raw(out.detach().contiguous(), y, dlogits, None, self.stats)
+            out.backward(dlogits)
+            sc.end_backward()                            # every packed weight gradient into the arena, one launch
         n = a.manifest.n_param
         K.sgd_step(a.f32[:n], a.grad, a.momentum, cfg.lr, cfg.momentum, cfg.weight_decay)
 
@@ -270,6 +335,7 @@ class CudaEngine:
                 sh["graph"] = graphs
                 if key not in graphs:
                     self._issue_steps(sh, upload, with_test)   # warm-up (also sizes every workspace)
+                    self.scope.sync_tables()
                     torch.cuda.synchronize(self.dev)
                     g = torch.cuda.CUDAGraph()
                     # the warm-up already trained one pass; that is a real pass, so count it and
@@ -334,8 +400,7 @@ class CudaEngine:
 
     def read_round_stats(self):
         """Train + eval counters of a round in ONE pinned D2H copy (32 bytes) and one sync."""
-        if self.eval_stream is not None:
-            torch.cuda.current_stream(self.dev).wait_stream(self.eval_stream)
+        self.join_overlapped_eval()
         self._pinned_stats[:4].copy_(self.stats, non_blocking=True)
         self._pinned_stats[4:].copy_(self.eval_stats, non_blocking=True)
         torch.cuda.current_stream(self.dev).synchronize()
@@ -400,15 +465,22 @@ class CudaEngine:
                 graphs = self._eval_graph if self._eval_graph is not None else {}
                 self._eval_graph = graphs
                 gkey = (copy, self._slot, snapshot)          # graph key: which half of the double buffer is read
-                with torch.no_grad():
+                esc = self.snap_scope if (snapshot and self.eval_model is not None) else self.eval_scope
+
+                def run_pass():
+                    esc.begin()                              # the weights changed since the last pass: repack once,
+                    self._streamed(pairs, bounds, work, copy, side=side)     # not once per batch and layer
+
+                with torch.no_grad(), esc:
                     if self.cfg.use_cuda_graph and gkey in graphs:
                         graphs[gkey].replay()
                     else:
-                        self._streamed(pairs, bounds, work, copy, side=side)
+                        run_pass()
                         if self.cfg.use_cuda_graph:
+                            esc.sync_tables()
                             torch.cuda.synchronize(self.dev)
                             g = torch.cuda.CUDAGraph()
                             with _quiet_gc(), torch.cuda.graph(g, stream=torch.cuda.Stream(device=self.dev)):
-                                self._streamed(pairs, bounds, work, copy, side=side)
+                                run_pass()
                             graphs[gkey] = g
             return self.read_stats("eval") if sync else None

@@ -23,6 +23,7 @@ import torch
 
 from ..ops import _lib
 from ..ops import cuda as K
+from ..utils.metrics import device_phase
 from .arena import Arena, split_ranges
 from .mem import PeerGroup, PeerLayout
 
@@ -65,6 +66,9 @@ class FedGroup:
         self._side_ctrl = K.new_ctrl(trainer.device)      # completion counter of the side-stream copy kernel
         self._common_base = False
         self._repl_pending = False
+        self.timer = None                 # DeviceTimer when the owner profiles (GpuFederation(profile=True))
+        self.nvlink_bytes_last = 0        # algorithmic bytes this rank moved over NVLink in its last K-AGG (+ K-REPL)
+        self._wait_ev = None
         self._remapped = False            # a restarted peer's new memory is not bound to the multicast object
         if codec == "fp8":
             dev = trainer.device
@@ -135,12 +139,13 @@ class FedGroup:
                       base=self.base.data_ptr())
         elif self.nvls_reduce and mc_dst:
             kw = dict(mc_src=mc_dst)
-        K.fedavg_raw([bufs[r].client_f32_ptr() for r in live], dst, begin, end,
-                     ctrl_local=self.peers.me.ctrl_ptr,
-                     src_i64=[bufs[r].client_i64_ptr() for r in live], dst_i64=dst_i64,
-                     n_i64=self.man.n_i64 if me == 0 else 0, weights=weights, mc_dst=mc_dst,
-                     sync_mode=1, rank=me, world=len(live), ctrl_peer=[bufs[r].ctrl_ptr for r in live],
-                     timeout_ns=self.timeout_ns, **kw)
+        # bytes this rank pulls (every peer's copy of its shard) and pushes (its reduced shard to every peer; once through
+        # the switch with multicast): the denominator of the achieved-GB/s figures
+        shard_bytes = (end - begin) * (1 if use_codec else 4)
+        n_peer = len(live) - 1
+        self.nvlink_bytes_last = shard_bytes * n_peer + (end - begin) * 4 * (1 if mc_dst else n_peer + (1 if fused_repl else 0))
+        with device_phase(self.timer, "agg"):
+            self._launch_agg(bufs, live, me, dst, dst_i64, begin, end, weights, mc_dst, kw)
         if self.codec == "fp8":
             # the new global model is the base of the next round's deltas
             self.base.copy_(self.trainer.arena.f32[:self.man.n_f32])
@@ -156,7 +161,9 @@ class FedGroup:
             to_replica = self.repl_mode == "overlap" and self.backup_rank != self.primary_rank and bk.base != 0
             d32 = [me_buf.aux_f32_ptr()] + ([bk.aux_f32_ptr()] if to_replica else [])
             d64 = [me_buf.aux_i64_ptr()] + ([bk.aux_i64_ptr()] if to_replica else [])
-            with torch.cuda.stream(self.side_stream):
+            if to_replica:
+                self.nvlink_bytes_last += self.man.n_f32 * 4
+            with torch.cuda.stream(self.side_stream), device_phase(self.timer, "repl", self.side_stream):
                 K.fedavg_raw([me_buf.client_f32_ptr()], d32, 0, self.man.n_f32, ctrl_local=self._side_ctrl.data_ptr(),
                              src_i64=[me_buf.client_i64_ptr()], dst_i64=d64, n_i64=self.man.n_i64,
                              version=self.round, dst_ctrl=[0] + ([bk.ctrl_ptr] if to_replica else []),
@@ -164,11 +171,22 @@ class FedGroup:
             self._repl_done.record(self.side_stream)
             self._repl_pending = True
 
+    def _launch_agg(self, bufs, live, me, dst, dst_i64, begin, end, weights, mc_dst, kw) -> None:
+        K.fedavg_raw([bufs[r].client_f32_ptr() for r in live], dst, begin, end,
+                     ctrl_local=self.peers.me.ctrl_ptr,
+                     src_i64=[bufs[r].client_i64_ptr() for r in live], dst_i64=dst_i64,
+                     n_i64=self.man.n_i64 if me == 0 else 0, weights=weights, mc_dst=mc_dst,
+                     sync_mode=1, rank=me, world=len(live), ctrl_peer=[bufs[r].ctrl_ptr for r in live],
+                     timeout_ns=self.timeout_ns, **kw)
+
     def before_local_pass(self) -> None:
         """The side-stream copy READS the primary's client arena; the next local pass WRITES it.  Evaluation may
         overlap the copy, training may not: callers invoke this right before they enqueue a training pass."""
         if self._repl_pending:
-            torch.cuda.current_stream(self.device).wait_event(self._repl_done)
+            # "repl_wait" is what the replication still costs the round: the part of the side-stream copy that was NOT
+            # hidden behind the evaluation / the host's work since the aggregation (hidden fraction = 1 - wait / repl)
+            with device_phase(self.timer, "repl_wait"):
+                torch.cuda.current_stream(self.device).wait_event(self._repl_done)
             self._repl_pending = False
 
     def check(self) -> None:

@@ -21,6 +21,7 @@ import torch
 from ..control.trainer import LocalTrainer, TrainerConfig
 from ..ops import _lib
 from ..utils import data as D
+from ..utils.metrics import DeviceTimer, device_phase
 from ..ops import cuda as K
 from .group import FedGroup
 from .mem import PeerGroup, PeerLayout, tensor_from_ptr
@@ -99,11 +100,15 @@ class GpuFederation:
     def __init__(self, model: str = "LeNet", rank: int = 0, world: int = 1, device: Optional[int] = None,
                  dataset: Optional[D.ImageDataset] = None, seed: Optional[int] = None, tag: Optional[str] = None,
                  lr: float = 0.1, batch_size: int = 128, augment: bool = False, evaluate: bool = True,
-                 test_allgather: Optional[bool] = None, eval_mode: str = "overlap", **group_kw):
+                 test_allgather: Optional[bool] = None, eval_mode: str = "inline", profile: bool = False, **group_kw):
         """``eval_mode``: where the evaluation of a round's global model runs (every client scores the whole test set
-        every round in all modes, N8).  "overlap" (default): on a second stream, from a snapshot of the global model,
-        concurrently with the next round's local pass - ``run_round_async`` then reports it one round late;
-        "inline": on the round's critical path, as the reference does (src/client.py:30)."""
+        every round in all modes, N8).  "inline" (default): on the round's critical path, as the reference does
+        (src/client.py:30).  "overlap": on a second stream, from a snapshot of the global model, concurrently with the
+        next round's local pass - ``run_round_async`` then reports it one round late.  Measured on B200 (LeNet,
+        profiles/README.md): while ANY kernel of another stream is resident, every kernel boundary of the training
+        stream costs about 3 us more, and a LeNet pass has two boundaries per 31 us step - the overlap loses more than
+        the 0.42 ms evaluation it hides (79.1 -> 74.8 rounds/s at N = 1), so it is opt-in, for models whose kernels are
+        long enough not to care."""
         device = rank if device is None else device
         torch.cuda.set_device(device)
         if eval_mode not in ("overlap", "inline"):
@@ -118,7 +123,11 @@ class GpuFederation:
         tag = tag or os.environ.get("MASTER_PORT", "solo") + f"-{os.getppid()}"
         self.group = FedGroup(self.trainer, rank, world, tag, dist_barrier=dist_min_barrier(), **group_kw)
         self.rounds = 0
-        self._eval_done = None            # event: the overlapped evaluation of the previous round has finished
+        # profile=True: NVTX ranges + CUDA-event pairs around the phases of every round (train / agg / repl / repl_wait /
+        # eval); take_profile() turns them into one record (device milliseconds, NVLink bytes, GB/s).  Costs a device
+        # synchronisation per record, so it is off in timed runs.
+        self.timer = DeviceTimer() if profile else None
+        self.group.timer = self.timer
         self._eval_round = 0              # round whose global model the newest finished/enqueued evaluation scores
         if self.eval_mode == "overlap":
             self.engine.enable_snapshot_eval()
@@ -142,7 +151,8 @@ class GpuFederation:
         live = self.group.live
         batches = self.trainer.shard(live.index(self.rank), self.world) if self.rank in live else []
         self.group.before_local_pass()
-        self.engine.train_pass(batches, upload=upload, sync=False, with_test=self.evaluate)
+        with device_phase(self.timer, "train"):
+            self.engine.train_pass(batches, upload=upload, sync=False, with_test=self.evaluate)
         if self.eval_mode == "overlap":
             self._join_eval(keep=True)
         self.group.aggregate()
@@ -150,38 +160,53 @@ class GpuFederation:
             if self.eval_mode == "overlap":
                 self._launch_overlapped_eval(upload)
             else:
-                self.engine.eval_pass(upload=upload, sync=False)
+                with device_phase(self.timer, "eval"):
+                    self.engine.eval_pass(upload=upload, sync=False)
         self.rounds += 1
         if not sync:
             return None
+        if self.eval_mode == "overlap":
+            self._join_eval()                # a synchronous caller wants THIS round's score: finish it now
         out = self.engine.read_round_stats()
         self.group.check()
         return out
 
     # ---- evaluation on a second stream (eval_mode="overlap")
     def _join_eval(self, keep: bool = False) -> None:
-        """The main stream waits for the previous round's evaluation.  In steady state it ended long ago (it is a
-        fraction of a local pass); the wait is what makes it safe to overwrite the snapshot and, two rounds later, the
-        half of the test-set double buffer it read - a rank only announces itself to K-AGG after this point.  ``keep``
-        parks the finished counters so that the round's result copy can pick them up."""
-        if self._eval_done is None:
-            return
-        cur = torch.cuda.current_stream(self.engine.dev)
-        cur.wait_event(self._eval_done)
-        if keep:
-            self.engine.eval_stats_prev.copy_(self.engine.eval_stats, non_blocking=True)
+        """See ``CudaEngine.join_overlapped_eval``: a rank only announces itself to K-AGG after this point."""
+        self.engine.join_overlapped_eval(keep=keep)
 
     def _launch_overlapped_eval(self, upload: bool) -> None:
         eng = self.engine
         cur = torch.cuda.current_stream(eng.dev)
         eng.snapshot()                                   # the new global model, before the next pass trains on it
-        if self._eval_done is None:
-            self._eval_done, self._snap_ready = torch.cuda.Event(), torch.cuda.Event()
+        if getattr(eng, "_eval_done", None) is None:
+            eng._eval_done, self._snap_ready = torch.cuda.Event(), torch.cuda.Event()
         self._snap_ready.record(cur)
         with torch.cuda.stream(eng.eval_stream):
             eng.eval_stream.wait_event(self._snap_ready)
-            eng.eval_pass(upload=upload, sync=False, snapshot=True)
-            self._eval_done.record(eng.eval_stream)
+            with device_phase(self.timer, "eval", eng.eval_stream):
+                if eng.queue_eval_available(upload):
+                    eng.queue_eval_start()               # LeNet: background CTAs on the SMs the training step leaves idle
+                else:
+                    eng.eval_pass(upload=upload, sync=False, snapshot=True)
+            eng._eval_done.record(eng.eval_stream)
+
+    def take_profile(self) -> dict:
+        """Device-timed phases since the last call (synchronises): milliseconds per phase, the NVLink bytes of this rank's
+        last aggregation and the rate they were moved at, and how much of the replication was hidden."""
+        if self.timer is None:
+            return {}
+        ms = self.timer.ms(reset=True)
+        out = {f"{k}_ms": round(v, 4) for k, v in ms.items()}
+        g = self.group
+        out.update(rank=self.rank, rounds=self.rounds, live=len(g.live), nvlink_bytes=g.nvlink_bytes_last,
+                   arena_bytes=g.man.n_f32 * 4)
+        if ms.get("agg"):
+            out["agg_gbps"] = round(g.nvlink_bytes_last / (ms["agg"] * 1e-3) / 1e9, 2)
+        if ms.get("repl"):
+            out["repl_hidden_fraction"] = round(max(0.0, 1.0 - ms.get("repl_wait", 0.0) / ms["repl"]), 4)
+        return out
 
     def drain(self, sync: bool = True):
         """Waits (on the stream; on the host too when ``sync``) for the evaluation that is still in flight and returns
@@ -288,7 +313,8 @@ class PeerWorker:
             fed.group.round = int(round_id)
         batches = fed.trainer.shard(rank, world)
         fed.group.before_local_pass()
-        st = fed.engine.train_pass(batches, upload=True, sync=True, with_test=True)
+        with device_phase(fed.timer, "train"):
+            st = fed.engine.train_pass(batches, upload=True, sync=True, with_test=True)
         fed.group.aggregate()
         return st
 
@@ -297,7 +323,13 @@ class PeerWorker:
         torch.cuda.current_stream(self.device).synchronize()
         self.fed.group.side_stream.synchronize()     # holder: global model + replica of this round are complete
         self.fed.group.check()                       # raises FedbError when a peer never showed up
-        return self.fed.engine.eval_pass(upload=True, sync=True) if evaluate else None
+        if not evaluate:
+            return None
+        with device_phase(self.fed.timer, "eval"):
+            return self.fed.engine.eval_pass(upload=True, sync=True)
+
+    def take_profile(self) -> dict:
+        return self.fed.take_profile()
 
     def reset(self, epoch: int) -> None:
         torch.cuda.set_device(self.device)

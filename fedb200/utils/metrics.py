@@ -108,6 +108,21 @@ class DeviceTimer:
             b.record(stream)
             self._events.setdefault(name, []).append((a, b))
 
-    def ms(self) -> Dict[str, float]:
+    def ms(self, reset: bool = False) -> Dict[str, float]:
         self._torch.cuda.synchronize()
-        return {k: sum(a.elapsed_time(b) for a, b in v) for k, v in self._events.items()}
+        out = {k: sum(a.elapsed_time(b) for a, b in v) for k, v in self._events.items()}
+        if reset:
+            self._events = {}
+        return out
+
+
+@contextlib.contextmanager
+def device_phase(timer: Optional["DeviceTimer"], name: str, stream=None):
+    """``with device_phase(timer, "agg"):`` - an NVTX range plus a CUDA-event pair on ``stream`` when a timer is given
+    (profiling on), nothing at all otherwise.  The phases of a federated round (train / agg / repl / eval) are wrapped in
+    it by ``GpuFederation`` and ``FedGroup``."""
+    if timer is None:
+        yield
+        return
+    with nvtx_range(name), timer.phase(name, stream):
+        yield

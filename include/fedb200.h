@@ -181,6 +181,15 @@ int fedb_lenet_train_step(const fedb_lenet_t* net, const uint8_t* images_u8, con
                           int B, void* workspace, float* stats, uint64_t step_seed, void* stream);
 int fedb_lenet_eval(const fedb_lenet_t* net, const uint8_t* images_u8, const int64_t* labels, int B,
                     void* workspace, float* stats, void* stream);
+/* The same evaluation through a WORK QUEUE, so that it can run off the round's critical path: persistent CTAs pull chunks
+ * of samples from `counter` (one device word, zeroed by the caller before the first launch of an evaluation).  A small
+ * background launch (ctas = idle SMs) scores the global model next to the next round's training kernels; a full-size
+ * launch on the training stream takes whatever is left when the result is needed; fedb_lenet_eval_stats then reduces
+ * the per-sample rows in a fixed order (the numbers do not depend on who scored which chunk).
+ * reference: src/client.py:30 + src/main.py:167-191 evaluate inside SendModel, on the critical path. */
+int fedb_lenet_eval_queue(const fedb_lenet_t* net, const uint8_t* images_u8, const int64_t* labels, int B, void* workspace,
+                          uint32_t* counter, int ctas, void* stream);
+int fedb_lenet_eval_stats(void* workspace, int B, float* stats, void* stream);
 /* forward only, logits out (tests) */
 int fedb_lenet_forward(const fedb_lenet_t* net, const uint8_t* images_u8, const float* images_f32,
                        int B, void* workspace, float* logits, void* stream);
@@ -271,6 +280,17 @@ int fedb_conv3x3_wgrad_bf16(const uint16_t* dY, const uint16_t* X, float* dWk, i
 /* mode 0: OIHW -> [K][tap][C]; mode 1: OIHW -> [C][flipped tap][K] (data gradient); mode 2: [K][tap][C] -> OIHW */
 int fedb_pack_filter(const float* w_oihw, float* out, int K, int C, int mode, int taps, void* stream);
 int fedb_pack3x3(const float* w_oihw, float* out, int K, int C, int mode, void* stream);
+/* All filter (un)packings of a model in ONE launch.  jobs_dev: device array of njobs 56-byte records
+ *   { const float* src; float* dst; int64 total; int32 kind, K, C, T, Rp, groups, chunk0, pad; }
+ * chunk0 = sum over the preceding jobs of ceil(total / FEDB_PACK_CHUNK); total_chunks = that sum over all jobs (one CTA
+ * per chunk, so every job gets CTAs in proportion to its size).
+ * kind 0 / 1 = fedb_pack_filter modes 0 / 1 (Rp: padded reduction width), 2 = dst(OIHW) += src([K][tap][C]) and src is
+ * cleared (weight gradients after the backward pass), 3 = fedb_pack_dgrad_s2 classes, 4 = transpose [K][C] -> [C][K];
+ * 5 / 6 / 7 = kinds 0 / 1 / 2 for 3x3 filters with K % 32 == 0 and C % 32 == 0, moved as 32 x 32 x 9 tiles through shared
+ * memory (total must then be K * C * 9, i.e. no padding).
+ * The reference has no counterpart (its convolutions are torch.nn.Conv2d, src/models). */
+#define FEDB_PACK_CHUNK 9216
+int fedb_pack_multi(const void* jobs_dev, int njobs, int total_chunks, void* stream);
 /* im2col for tiny reductions (Cin*fs*fs <= 32, the 3-channel stems): NHWC x -> [pixels][32] fp32 and/or [pixels][64] bf16,
  * column = OIHW flattening of the filter, zero padded; the convolution and its weight gradient become plain GEMMs */
 int fedb_im2col_small(const float* x, float* out_f32, uint16_t* out_bf16, int N, int H, int W, int C, int fs, int stride,
@@ -300,6 +320,15 @@ int fedb_nn_bn_fwd(const float* x, float* y, float* mean, float* invstd, float* 
 int fedb_nn_bn_bwd(const float* x, const float* dy, float* dx, const float* mean, const float* invstd, const float* gamma,
                    const float* beta, float* dgamma, float* dbeta, long long rows, int C, int act, int training, float* scratch,
                    long long scratch_floats, void* stream);
+/* Same, plus an optional bf16 copy of the result (y / dx) written by the same kernel: the operand of the tensor-core
+ * weight-gradient GEMM of the neighbouring convolution, so no separate cast pass re-reads the tensor.  C % 4 == 0. */
+int fedb_nn_bn_fwd16(const float* x, float* y, float* mean, float* invstd, float* run_mean, float* run_var, const float* gamma,
+                     const float* beta, long long rows, int C, float eps, float momentum, int training, int act, float* scratch,
+                     long long scratch_floats, uint16_t* y_bf16, void* stream);
+int fedb_nn_bn_bwd16(const float* x, const float* dy, float* dx, const float* mean, const float* invstd, const float* gamma,
+                     const float* beta, float* dgamma, float* dbeta, long long rows, int C, int act, int training, float* scratch,
+                     long long scratch_floats, uint16_t* dx_bf16, void* stream);
+int fedb_nn_add_act16(const float* a, const float* b, float* y, long long n, int act, uint16_t* y_bf16, void* stream);
 int fedb_nn_act_fwd(const float* x, float* y, long long n, int act, void* stream);
 int fedb_nn_act_bwd(const float* x, const float* dy, float* dx, long long n, int act, void* stream);
 int fedb_nn_add_act(const float* a, const float* b, float* y, long long n, int act, void* stream);

@@ -22,7 +22,7 @@ def _need_gpu():
 def _generic_kernels_only(request):
     """These tests pin down the fp32 generic kernels at fp32 tolerances; the tcgen05 routing (TF32 / BF16
     operands) is switched off here and covered by test_gpu_gemm_tc.py and the ``tc`` zoo cases below."""
-    from fedb200.ops import cuda_tc
+    from fedb200.ops import cuda_gemm as cuda_tc
     old = cuda_tc.ENABLED
     cuda_tc.ENABLED = "tensorcores" in request.keywords
     yield

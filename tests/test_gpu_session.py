@@ -75,6 +75,26 @@ def test_overlapped_eval_of_a_zoo_model_scores_the_snapshot():
     fed.close()
 
 
+def test_profile_records_device_phases():
+    """profile=True: the round's phases are bracketed by CUDA events (and NVTX ranges); take_profile() returns their
+    device times, the NVLink byte count of the aggregation and resets."""
+    fed = _fed(5, profile=True, eval_mode="inline")
+    fed.run_round(upload=True, sync=True)
+    fed.run_round(upload=True, sync=True)
+    p = fed.take_profile()
+    assert p["train_ms"] > 0 and p["agg_ms"] > 0 and p["eval_ms"] > 0 and p["repl_ms"] > 0
+    assert p["rounds"] == 2 and p["nvlink_bytes"] == 0 and p["arena_bytes"] == fed.group.man.n_f32 * 4   # world = 1: nothing crosses
+    assert 0.0 <= p["repl_hidden_fraction"] <= 1.0
+    fed.run_round(upload=False, sync=True)
+    p2 = fed.take_profile()
+    assert 0 < p2["train_ms"] < p["train_ms"]            # one round after the reset, against two before it
+    plain = _fed(5)
+    plain.run_round()
+    assert plain.take_profile() == {}
+    fed.close()
+    plain.close()
+
+
 def test_standalone_trainer_on_gpu_follows_the_cpu_run(tmp_path):
     """python -m fedb200.main on cuda: two epochs with the cosine schedule (the learning rate changes between epochs, so
     the captured pass is dropped and captured again) track the CPU run of the same seed."""

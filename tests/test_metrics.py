@@ -38,3 +38,11 @@ def test_jsonl_sink_keeps_and_writes_records(tmp_path):
 def test_nvtx_range_is_a_no_op_without_cuda():
     with nvtx_range("phase"):
         pass
+
+
+def test_device_phase_is_a_no_op_without_a_timer():
+    from fedb200.utils.metrics import device_phase
+    ran = []
+    with device_phase(None, "agg"):
+        ran.append(1)
+    assert ran == [1]

@@ -49,7 +49,7 @@ def spawn_worker(rank, port, tag, work, rejoin=False):
     cmd = [sys.executable, "-m", "fedb200.client", "-a", f"127.0.0.1:{port}", "--plane", "peer", "--model", "LeNet",
            "--device", f"cuda:{rank}", "--peer-rank", str(rank), "--peer-world", str(WORLD), "--peer-tag", tag,
            "--dataset-size", "2048", "--test-size", "500", "--seed", str(10 + rank), "--agg-timeout", "4",
-           "--dump-root", work, "--metrics", os.path.join(work, f"worker{rank}.jsonl")]
+           "--dump-root", work, "--metrics", os.path.join(work, f"worker{rank}.jsonl"), "--profile"]
     if rejoin:
         cmd.append("--rejoin")
     log = open(os.path.join(work, f"worker{rank}{'-re' if rejoin else ''}.log"), "w")
@@ -125,6 +125,11 @@ def main():
         assert list(glob["net"].keys())[0] == "conv1.weight" and glob["acc"] == 1
         assert backup.next_round == 3                                          # replica metadata followed
         st = check_roles(c, work, list(range(WORLD)), "p1")
+        prof = [json.loads(line) for line in open(os.path.join(work, "worker0.jsonl")) if '"round_profile"' in line]
+        assert prof and all(k in prof[-1] for k in ("train_ms", "agg_ms", "eval_ms", "nvlink_bytes", "agg_gbps")), prof[-1:]
+        print("device-timed phases of the last round on worker 0:",
+              {k: prof[-1][k] for k in ("train_ms", "agg_ms", "repl_ms", "eval_ms", "nvlink_bytes", "agg_gbps", "repl_hidden_fraction")
+               if k in prof[-1]})
         print("phase 1 ok: 3 descriptor rounds,", [round(r["total_s"], 3) for r in rounds],
               f"multicast: {str(st[0]['multicast']).lower()}, replica version {st[1 % WORLD]['replica_version']}")
 

@@ -1,20 +1,39 @@
-"""Aggregates an `ncu --metrics gpu__time_duration.sum --csv` launch list by kernel name (shares, not absolutes)."""
+"""Aggregates an `ncu --metrics gpu__time_duration.sum --csv` launch list by kernel name (shares, not absolutes).
+
+  python tools/launch_summary.py [--last-step N_STEPS] file.csv ...
+
+--last-step N: the run consisted of N equal steps; only the launches of the last one are counted (steady state: the first
+step of an eager run also packs filters one by one and sizes workspaces)."""
 import collections
 import csv
 import sys
 
-for path in sys.argv[1:]:
+args = sys.argv[1:]
+steps = 0
+if args and args[0] == "--last-step":
+    steps = int(args[1])
+    args = args[2:]
+for path in args:
     rows = list(csv.reader(open(path)))
     hdr = [r for r in rows if "Kernel Name" in r][0]
     k, v = hdr.index("Kernel Name"), hdr.index("Metric Value")
-    agg, cnt = collections.Counter(), collections.Counter()
+    launches = []
     for r in rows:
         if len(r) == len(hdr) and r[v].replace(".", "").isdigit():
-            n = r[k].split("(")[0].replace("void ", "").replace("<unnamed>::", "")[-70:]
-            agg[n] += float(r[v])
-            cnt[n] += 1
+            launches.append((r[k].split("(")[0].replace("void ", "").replace("<unnamed>::", "")[-70:], float(r[v])))
+    if steps > 1:
+        # the last step starts at the last launch of the step's first kernel (the input pipeline's prepare_kernel)
+        starts = [i for i, (n, _) in enumerate(launches) if "prepare_kernel" in n]
+        launches = launches[starts[-1] - 1 if starts and starts[-1] > 0 else 0:]
+    agg, cnt = collections.Counter(), collections.Counter()
+    for n, t in launches:
+        agg[n] += t
+        cnt[n] += 1
     tot = sum(agg.values())
-    print(f"## {path}: {sum(cnt.values())} launches, {tot / 1e3:.1f} us in kernels")
-    print("| kernel | launches | us | share |\n|---|---|---|---|")
-    for n, t in agg.most_common(16):
-        print(f"| `{n}` | {cnt[n]} | {t / 1e3:.1f} | {100 * t / tot:.1f} % |")
+    try:
+        print(f"## {path}: {sum(cnt.values())} launches, {tot / 1e3:.1f} us in kernels" + (" (last step)" if steps > 1 else ""))
+        print("| kernel | launches | us | share |\n|---|---|---|---|")
+        for n, t in agg.most_common(24):
+            print(f"| `{n}` | {cnt[n]} | {t / 1e3:.1f} | {100 * t / tot:.1f} % |")
+    except BrokenPipeError:
+        pass
