@@ -91,7 +91,9 @@ def run_reference(n_workers: int, rounds: int, warmup: int, model: str = "LeNet"
                 extra += ["--torch-seed", str(worker_seeds[i])]
             spawn("worker", extra, wenv)
         cenv = dict(env)
-        cenv["CUDA_VISIBLE_DEVICES"] = ""
+        # R-gpu: the workers' checkpoints hold CUDA tensors, which the reference's coordinator un-pickles with a plain
+        # torch.load (src/server.py:158-160) - it needs a visible GPU for that, or it dies in its receive thread and hangs
+        cenv["CUDA_VISIBLE_DEVICES"] = "0" if gpu_workers else ""
         for port in wports:
             if not _wait_port(port, 600):
                 raise RuntimeError(f"reference worker on port {port} did not come up (see {work}/reference.log)")

@@ -6,11 +6,18 @@
 
 namespace {
 
-template <bool kShadow>
+// kStep: the "end of step" form used by the zoo engine - the gradient is cleared as it is consumed (the next step's
+// backward pass accumulates into zeros without a separate fill) and the BatchNorm step counters (num_batches_tracked, the
+// whole int64 segment of the arena) advance by one here instead of by one tiny launch per BatchNorm layer.
+template <bool kShadow, bool kStep = false>
 __global__ void __launch_bounds__(256) sgd_kernel(float* __restrict__ p, const float* __restrict__ g,
                                                  float* __restrict__ v, uint16_t* __restrict__ shadow,
-                                                 long long n4, float lr, float mu, float wd) {
+                                                 long long n4, float lr, float mu, float wd,
+                                                 long long* __restrict__ counters = nullptr, long long n_counters = 0) {
   const long long stride = (long long)gridDim.x * blockDim.x;
+  if constexpr (kStep) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_counters; i += stride) counters[i] += 1;
+  }
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n4; i += stride) {
     float4 pp = reinterpret_cast<float4*>(p)[i];
     const float4 gg = reinterpret_cast<const float4*>(g)[i];
@@ -26,6 +33,7 @@ __global__ void __launch_bounds__(256) sgd_kernel(float* __restrict__ p, const f
 #undef FEDB_SGD1
     reinterpret_cast<float4*>(p)[i] = pp;
     reinterpret_cast<float4*>(v)[i] = vv;
+    if constexpr (kStep) reinterpret_cast<float4*>(const_cast<float*>(g))[i] = make_float4(0.f, 0.f, 0.f, 0.f);
     if constexpr (kShadow) {
       __nv_bfloat162 lo = __floats2bfloat162_rn(pp.x, pp.y), hi = __floats2bfloat162_rn(pp.z, pp.w);
       uint2 r;
@@ -67,6 +75,19 @@ extern "C" int fedb_sgd_step(float* param, const float* grad, float* momentum, u
   else
     sgd_kernel<false><<<blocks, 256, 0, (cudaStream_t)stream>>>(param, grad, momentum, nullptr, n / 4, lr, mu,
                                                                 weight_decay);
+  FEDB_LAUNCH_OK();
+  return 0;
+}
+
+extern "C" int fedb_sgd_step_end(float* param, float* grad, float* momentum, int64_t n, float lr, float mu,
+                                 float weight_decay, int64_t* counters, int64_t n_counters, void* stream) {
+  FEDB_REQUIRE(n % 4 == 0, "fedb_sgd_step_end: n must be a multiple of 4 (arena segments are padded)");
+  FEDB_REQUIRE(n_counters == 0 || counters != nullptr, "fedb_sgd_step_end: null counter segment");
+  if (n == 0) return 0;
+  int blocks = fedb_ceil_div(n / 4, 256);
+  if (blocks > fedb_num_sms() * 8) blocks = fedb_num_sms() * 8;
+  sgd_kernel<false, true><<<blocks, 256, 0, (cudaStream_t)stream>>>(param, grad, momentum, nullptr, n / 4, lr, mu, weight_decay,
+                                                                    (long long*)counters, (long long)n_counters);
   FEDB_LAUNCH_OK();
   return 0;
 }

@@ -68,6 +68,7 @@ _SIGS = {
     "fedb_codec_encode": (C.c_int, [vp, vp, vp, vp, vp, C.c_int64, vp]),
     "fedb_codec_decode": (C.c_int, [vp, vp, vp, vp, C.c_int64, vp]),
     "fedb_sgd_step": (C.c_int, [vp, vp, vp, vp, C.c_int64, C.c_float, C.c_float, C.c_float, vp]),
+    "fedb_sgd_step_end": (C.c_int, [vp, vp, vp, C.c_int64, C.c_float, C.c_float, C.c_float, vp, C.c_int64, vp]),
     "fedb_adam_step": (C.c_int, [vp, vp, vp, vp, C.c_int64, C.c_float, C.c_float, C.c_float, C.c_float,
                                  C.c_float, vp, vp]),
     "fedb_cross_entropy": (C.c_int, [vp, vp, vp, vp, vp, C.c_int, C.c_int, vp]),

@@ -148,6 +148,15 @@ def sgd_step(param: torch.Tensor, grad: torch.Tensor, momentum: torch.Tensor, lr
     _lib.count_launch()
 
 
+def sgd_step_end(param: torch.Tensor, grad: torch.Tensor, momentum: torch.Tensor, lr: float, mu: float,
+                 weight_decay: float, counters: Optional[torch.Tensor] = None) -> None:
+    """SGD step that also clears ``grad`` and advances the arena's int64 counters (BatchNorm steps) by one."""
+    nc = 0 if counters is None else counters.numel()
+    check(lib().fedb_sgd_step_end(param.data_ptr(), grad.data_ptr(), momentum.data_ptr(), param.numel(), lr, mu,
+                                  weight_decay, ptr(counters) if nc else 0, nc, current_stream()), "fedb_sgd_step_end")
+    _lib.count_launch()
+
+
 def adam_step(param, grad, m, v, step_dev: torch.Tensor, lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8,
               weight_decay=0.0) -> None:
     check(lib().fedb_adam_step(param.data_ptr(), grad.data_ptr(), m.data_ptr(), v.data_ptr(), param.numel(),

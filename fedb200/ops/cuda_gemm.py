@@ -64,6 +64,7 @@ class StepScope:
         self._tables = {}
         self._retired = []          # tables a captured graph may still read
         self._prev = None
+        self.fused_counters = False  # True: the step's SGD kernel advances the BatchNorm counters (engine), not each layer
 
     def __enter__(self):
         global _SCOPE

@@ -246,7 +246,9 @@ def batch_norm(x, bn, act="none"):
     y = _BatchNorm.apply(x, bn.weight, bn.bias, bn.running_mean, bn.running_var, bn.training,
                          bn.momentum if bn.momentum is not None else 0.1, bn.eps, ACT[act])
     if bn.training:
-        bn.num_batches_tracked += 1
+        sc = _train_scope()
+        if sc is None or not sc.fused_counters:      # inside the engine's step the end-of-step SGD kernel counts for all
+            bn.num_batches_tracked += 1
     return y
 
 

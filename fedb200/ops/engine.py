@@ -78,6 +78,7 @@ class CudaEngine:
         # per-model caches of the convolution glue (packed filters, packed gradient accumulators): they hold addresses of
         # the arena, so they start over with it
         from . import cuda_gemm
+        self._grad_clean = False
         self.scope = cuda_gemm.StepScope(self.dev, train=True)
         self.eval_scope = cuda_gemm.StepScope(self.dev, train=False)
         with torch.cuda.device(self.dev):
@@ -302,16 +303,21 @@ class CudaEngine:
     def _generic_step(self, x_u8, y, seed):
         a, cfg = self.arena, self.cfg
         with self.scope as sc:
+            sc.fused_counters = True
             sc.begin()                                   # every packed filter of the model, one launch
             x = K.prepare_batch(x_u8, nhwc=True, augment=cfg.augment, seed=seed, seed_dev=self.seed_dev)
-            a.grad.zero_()
+            if not self._grad_clean:                     # afterwards every step's SGD kernel leaves the gradient zeroed
+                a.grad.zero_()
+                self._grad_clean = True
             out = self.t.model(x)
             dlogits = torch.empty_like(out)
             K.cross_entropy_raw(out.detach().contiguous(), y, dlogits, None, self.stats)
             out.backward(dlogits)
             sc.end_backward()                            # every packed weight gradient into the arena, one launch
         n = a.manifest.n_param
-        K.sgd_step(a.f32[:n], a.grad, a.momentum, cfg.lr, cfg.momentum, cfg.weight_decay)
+        # the int64 segment holds the BatchNorm step counters, densely from 0 (its tail is alignment padding)
+        n_ctr = sum(e.numel for e in a.manifest.entries if e.segment == "i64")
+        K.sgd_step_end(a.f32[:n], a.grad, a.momentum, cfg.lr, cfg.momentum, cfg.weight_decay, counters=a.i64[:n_ctr])
 
     def train_pass(self, batches: List[int], upload: bool = True, sync: bool = True, with_test: bool = False):
         """One local pass over the shard.  ``upload``: this pass's inputs are copied from pinned memory inside the

@@ -119,6 +119,10 @@ int fedb_codec_decode(float* out, const float* base, const uint8_t* q, const flo
  * reference: src/main.py:99-100,151 */
 int fedb_sgd_step(float* param, const float* grad, float* momentum, uint16_t* shadow_bf16, int64_t n,
                   float lr, float mu, float weight_decay, void* stream);
+/* End-of-step form: same update, and in the same pass the gradient is cleared (the next backward pass accumulates into
+ * zeros) and every int64 counter of the arena (BatchNorm's num_batches_tracked) advances by one. */
+int fedb_sgd_step_end(float* param, float* grad, float* momentum, int64_t n, float lr, float mu, float weight_decay,
+                      int64_t* counters, int64_t n_counters, void* stream);
 int fedb_adam_step(float* param, const float* grad, float* m, float* v, int64_t n, float lr, float beta1,
                    float beta2, float eps, float weight_decay, const int32_t* step_dev, void* stream);
 
