@@ -712,7 +712,8 @@ int run_gemm(int kind, const void* A, const void* B, float* D, const float* bias
   FEDB_REQUIRE(M > 0 && N > 0 && K > 0, "gemm_tc: empty problem");
   FEDB_REQUIRE(splits >= 1, "gemm_tc: splits >= 1");
   FEDB_REQUIRE(!(relu && (splits > 1 || accumulate)), "gemm_tc: ReLU cannot be fused into a partial sum");
-  const int bn = N >= 128 ? 128 : (N > 32 ? 64 : 32);
+  int bn = N >= 128 ? 128 : (N > 32 ? 64 : 32);
+  if (kind == 0 && bn == 128 && splits == 1 && (long long)fedb_ceil_div(M, BM) * fedb_ceil_div(N, 128) < fedb_num_sms()) bn = 64;
   const int bk = kind == 0 ? Kind<0>::kBK : Kind<1>::kBK;
   CUtensorMap ma, mb;
   if (kind == 0) {       // A [M][K], B [N][K], fp32
@@ -798,7 +799,10 @@ static int conv_tf32_impl(const float* X, const float* Wk, float* Y, const float
   // bounds), the packed filter carries explicit zeros (fedb_pack_filter); a 1x1 filter needs no packing at all
   const int cin_pad = (Cin + 31) / 32 * 32;
   const int M = N * P * Q, K = fs * fs * cin_pad;
-  const int bnt = Cout >= 128 ? 128 : (Cout > 32 ? 64 : 32);
+  int bnt = Cout >= 128 ? 128 : (Cout > 32 ? 64 : 32);
+  // few pixels, many channels (the 8x8 / 4x4 stages): 128-wide tiles would leave most SMs without a tile while each tile walks
+  // a K loop of thousands; 64-wide tiles double the tile count and halve the MMA time per tile
+  if (bnt == 128 && (long long)fedb_ceil_div(M, BM) * fedb_ceil_div(Cout, 128) * groups < fedb_num_sms()) bnt = 64;
   CUtensorMap ma, mb;
   if (int rc = make_map_nhwc(&ma, X, 4, N, H, W, groups > 1 ? (int)xpitch : Cin, bw, bh, bn, stride, xpitch)) return rc;
   if (fs == 1) { if (int rc = make_map_2d(&mb, Wk, 4, (long long)Cout * groups, Cin, Cin, 32, bnt)) return rc; }
@@ -879,7 +883,8 @@ static int conv_dgrad_s2_impl(const float* dY, const float* Wcls, float* dX, int
   if (bh > P) bh = P;
   const int bn = 128 / (bw * bh);
   FEDB_REQUIRE(bw * bh * bn == 128 && (bn == 1 || bh == P), "fedb_conv_dgrad_s2_tf32: unsupported tile geometry");
-  const int bnt = Cin >= 128 ? 128 : (Cin > 32 ? 64 : 32);
+  int bnt = Cin >= 128 ? 128 : (Cin > 32 ? 64 : 32);
+  if (bnt == 128 && (long long)fedb_ceil_div(N * P * Q, BM) * fedb_ceil_div(Cin, 128) * groups < fedb_num_sms()) bnt = 64;
   CUtensorMap ma, mb;
   if (int rc = make_map_nhwc(&ma, dY, 4, N, P, Q, groups > 1 ? (int)dypitch : Cout, bw, bh, bn, 1, dypitch)) return rc;
   const int ncls = fs == 3 ? 4 : 1;

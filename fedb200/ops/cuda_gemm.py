@@ -20,6 +20,9 @@ import os
 
 _fns = {}
 MIN_PIXELS = 128          # below one M tile the generic kernel is as good
+WGRAD_TILES = int(os.environ.get("FEDB200_WGRAD_TILES", "148"))   # split-K weight gradients aim at this many tiles: the GEMM is
+                          # persistent (one CTA per SM walks the tiles), so ONE wave is ideal - more splits only add
+                          # red.global.add traffic to L2 (7 M atomics for a 128-channel 3x3 layer at 444 tiles: 50 -> ~30 us)
 ENABLED = os.environ.get("FEDB200_TC", "1") != "0"      # 0: every convolution takes the generic fp32 kernels (debugging)
 
 
@@ -398,7 +401,7 @@ def _grouped_wgrad_by_group(x, dy, dw, db, shp, Cg, Kg) -> bool:
     taps, pix, pix_in = R * R, N * P * Q, N * H * W
     kp, cp = (Kg + 7) // 8 * 8, (Cg + 7) // 8 * 8
     tiles = ((Kg + 127) // 128) * ((Cg + 127) // 128) * taps
-    splits = max(1, min(pix // 256, 444 // max(tiles, 1)))
+    splits = max(1, min(pix // 256, WGRAD_TILES // max(tiles, 1)))
     cast = _f("fedb_cast_bf16_pad_p")
     for g in range(groups):
         dy16 = torch.empty(pix * kp, dtype=torch.bfloat16, device=x.device)
@@ -425,7 +428,7 @@ def _grouped_wgrad(x, dy, dw, db, shp, Cg, Kg) -> bool:
         return _grouped_wgrad_by_group(x, dy, dw, db, shp, Cg, Kg) if groups <= MAX_SPLIT_GROUPS else False
     taps, pix = R * R, N * P * Q
     tiles = ((Kg + 127) // 128) * ((Cg + 127) // 128) * taps * groups
-    splits = max(1, min(pix // 256, 444 // max(tiles, 1)))
+    splits = max(1, min(pix // 256, WGRAD_TILES // max(tiles, 1)))
     dy16, x16 = cast_bf16(dy), cast_bf16(x)
     dwk = torch.zeros(K * taps * Cg, dtype=torch.float32, device=x.device) if taps > 1 else dw
     check(_f("fedb_conv_wgrad_bf16_grouped")(dy16.data_ptr(), x16.data_ptr(), dwk.data_ptr(), N, H, W, Cc, K, groups, R, sh, ph,
@@ -528,7 +531,7 @@ def conv_wgrad(x, dy, dw, db, shp, direct: bool = False) -> bool:
         _, xcol16 = _im2col(x, shp, False, True)
         dy16, kp = cast_bf16_rows(dy, pix, K)
         dwp = torch.zeros(K * 64, dtype=torch.float32, device=x.device)
-        splits = max(1, min(pix // 256, 296))
+        splits = max(1, min(pix // 256, WGRAD_TILES))
         gemm_bf16_tn(dy16, xcol16, dwp, K, 64, pix, kp, 64, 64, splits=splits, accumulate=True)  # dWp[K][64] = dY^T Xcol
         _channel_copy(dwp, dw, K, 64, Cc * R * S, Cc * R * S, accumulate=True)                     # += into OIHW
         if db is not None:
@@ -538,7 +541,7 @@ def conv_wgrad(x, dy, dw, db, shp, direct: bool = False) -> bool:
         N, H, W, Cc, K = shp[:5]
         pix = N * H * W
         tiles = ((K + 127) // 128) * ((Cc + 127) // 128) * 9
-        splits = max(1, min(pix // 256, 444 // max(tiles, 1)))
+        splits = max(1, min(pix // 256, WGRAD_TILES // max(tiles, 1)))
         kept = _SCOPE is not None and _SCOPE.train and direct
         dwk = _SCOPE.wgrad_buffer(dw, K, Cc, 9) if kept else torch.zeros(K * 9 * Cc, dtype=torch.float32, device=x.device)
         # keep both alive: two temporaries would share one allocation; channel counts that are not multiples of 8 get
@@ -559,7 +562,7 @@ def conv_wgrad(x, dy, dw, db, shp, direct: bool = False) -> bool:
         fs, stride, pad = st
         taps, pix = fs * fs, N * shp[7] * shp[8]
         tiles = ((K + 127) // 128) * ((Cc + 127) // 128) * taps
-        splits = max(1, min(pix // 256, 444 // max(tiles, 1)))
+        splits = max(1, min(pix // 256, WGRAD_TILES // max(tiles, 1)))
         (dy16, kp), (x16, cp) = cast_bf16_rows(dy, pix, K), cast_bf16_rows(x, N * H * W, Cc)
         kept = _SCOPE is not None and _SCOPE.train and direct and taps > 1
         dwk = dw if taps == 1 else (_SCOPE.wgrad_buffer(dw, K, Cc, taps) if kept else
@@ -580,7 +583,7 @@ def conv_wgrad(x, dy, dw, db, shp, direct: bool = False) -> bool:
     # dW[K,C] = dY[pix,K]^T X[pix,C]: reduction over pixels, split across CTAs so that small layers
     # (few output tiles) still fill the machine; partial tiles are reduced with red.global.add
     tiles = ((K + 127) // 128) * ((Cc + 127) // 128)
-    splits = max(1, min(pix // 256, 296 // max(tiles, 1)))
+    splits = max(1, min(pix // 256, WGRAD_TILES // max(tiles, 1)))
     (dy16, kp), (x16, cp) = cast_bf16_rows(dy, pix, K), cast_bf16_rows(x, pix, Cc)
     gemm_bf16_tn(dy16, x16, dw, K, Cc, pix, kp, cp, Cc, splits=splits, accumulate=True)
     if db is not None:

@@ -34,8 +34,9 @@ def main():
     ds = D.synthetic_cifar(a.n_train, a.n_test, seed=0)
     fed = GpuFederation(model=a.model, rank=rank, world=world, device=local, dataset=ds, seed=1000 + rank, profile=True,
                         eval_mode=a.eval, tag=f"prof-{os.environ.get('MASTER_PORT', 'solo')}-{os.getppid()}")
-    for _ in range(2):                       # warm-up: uploads, graph capture
-        fed.run_round(upload=True, sync=True)
+    fed.run_round(upload=True, sync=True)    # warm-up: brings the inputs over ...
+    for _ in range(2):                       # ... and captures the resident-input graphs that the measured rounds replay
+        fed.run_round(upload=False, sync=True)
     fed.take_profile()
     recs = []
     for _ in range(a.rounds):
