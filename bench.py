@@ -114,7 +114,9 @@ def run_reference_arm(a) -> dict:
             "gpu_launches": 0,
             "config": {"model": a.model, "clients": a.gpus, "global_batch": a.batch_size * a.gpus, "seq_len": None,
                        "parallelism": f"fedavg{a.gpus}", "train_samples": a.n_train, "test_samples": a.n_test,
-                       "local_epochs": 1, "workers": "gpu+DataParallel-identity shim" if a.ref_gpu_workers
+                       "local_epochs": 1, "eval_in_round": True, "eval": "inline (on the round's critical path)",
+                       "augment": True, "codec": "none",
+                       "workers": "gpu+DataParallel-identity shim" if a.ref_gpu_workers
                        else "cpu (the only mode in which the unmodified reference works, SURVEY B4)",
                        "path": "baseline/_ref/fedref_src via baseline/ref_launcher.py (sources byte-identical)"}}
 

@@ -354,3 +354,10 @@ extern "C" int fedb_copy_async(void* dst, const void* src, uint64_t bytes, void*
   FEDB_CHECK(cudaMemcpyAsync(dst, src, bytes, cudaMemcpyDefault, (cudaStream_t)stream));
   return 0;
 }
+
+// Zero-fill as a memset node of the stream / graph (no kernel launch): gradients of a stride-2 1x1 data gradient, counters.
+extern "C" int fedb_zero_async(void* dst, uint64_t bytes, void* stream) {
+  if (bytes == 0) return 0;
+  FEDB_CHECK(cudaMemsetAsync(dst, 0, bytes, (cudaStream_t)stream));
+  return 0;
+}

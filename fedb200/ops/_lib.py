@@ -94,6 +94,7 @@ _SIGS = {
     "fedb_fd_serve": (C.c_int, [C.c_char_p, C.POINTER(C.c_int), C.c_int, C.c_int, C.c_int]),
     "fedb_fd_fetch": (C.c_int, [C.c_char_p, C.POINTER(C.c_int), C.c_int, C.c_int]),
     "fedb_copy_async": (C.c_int, [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p]),
+    "fedb_zero_async": (C.c_int, [C.c_void_p, C.c_uint64, C.c_void_p]),
     "fedb_push_copy": (C.c_int, [C.c_void_p, C.POINTER(C.c_void_p), C.c_int, C.c_void_p, C.c_uint64, C.c_void_p]),
 }
 

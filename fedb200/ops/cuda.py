@@ -157,6 +157,13 @@ def sgd_step_end(param: torch.Tensor, grad: torch.Tensor, momentum: torch.Tensor
     _lib.count_launch()
 
 
+def zero_(t: torch.Tensor) -> torch.Tensor:
+    """Zero-fill of a contiguous tensor as a memset on the current stream (a memset node under graph capture)."""
+    assert t.is_contiguous() or (t.dim() == 4 and t.is_contiguous(memory_format=torch.channels_last))
+    check(lib().fedb_zero_async(t.data_ptr(), t.numel() * t.element_size(), current_stream()), "fedb_zero_async")
+    return t
+
+
 def adam_step(param, grad, m, v, step_dev: torch.Tensor, lr=1e-3, beta1=0.9, beta2=0.999, eps=1e-8,
               weight_decay=0.0) -> None:
     check(lib().fedb_adam_step(param.data_ptr(), grad.data_ptr(), m.data_ptr(), v.data_ptr(), param.numel(),

@@ -478,7 +478,9 @@ class _Slice(torch.autograd.Function):
     def backward(ctx, dy):
         dy = _cl(dy)
         N, _, H, W = dy.shape
-        dx = torch.empty((N, ctx.C, H, W), dtype=torch.float32, device=dy.device, memory_format=CL).zero_()
+        dx = torch.empty((N, ctx.C, H, W), dtype=torch.float32, device=dy.device, memory_format=CL)
+        from .cuda import zero_
+        zero_(dx)
         _chcopy(dy, dx, 0, ctx.lo, ctx.hi - ctx.lo)
         return dx, None, None
 

@@ -134,7 +134,7 @@ class CudaEngine:
         imgs, labels = self._test_images(), self._test_dev[1]
         self._q = (imgs, labels, int(imgs.shape[0]))
         self._test_resident = False
-        self._q_counter.zero_()
+        K.zero_(self._q_counter)
         import os
         idle = max(self._sms - self.cfg.batch_size, 0)
         idle = int(os.environ.get("FEDB200_EVAL_BG_CTAS", idle))
@@ -168,7 +168,7 @@ class CudaEngine:
 
     def queue_eval_stats(self) -> None:
         """After BOTH launches have ended: fixed-order reduction of the per-sample rows into ``eval_stats``."""
-        self.eval_stats.zero_()
+        K.zero_(self.eval_stats)
         self.plan.eval_queue_stats(self._q[2], self.eval_stats)
         self._q = None
 
@@ -307,7 +307,7 @@ class CudaEngine:
             sc.begin()                                   # every packed filter of the model, one launch
             x = K.prepare_batch(x_u8, nhwc=True, augment=cfg.augment, seed=seed, seed_dev=self.seed_dev)
             if not self._grad_clean:                     # afterwards every step's SGD kernel leaves the gradient zeroed
-                a.grad.zero_()
+                K.zero_(a.grad)
                 self._grad_clean = True
             out = self.t.model(x)
             dlogits = torch.empty_like(out)
@@ -334,7 +334,7 @@ class CudaEngine:
                 self._slot ^= 1                               # this round's set goes into the other half
                 self._tex_on = self._tex.enabled()
             key = (upload, with_test, self._slot if with_test else -1, self._tex_on if with_test else False)
-            self.stats.zero_()
+            K.zero_(self.stats)
             self.seed_dev += 1
             if self.cfg.use_cuda_graph:
                 graphs = sh["graph"] if sh["graph"] is not None else {}
@@ -428,7 +428,7 @@ class CudaEngine:
             self._test_resident = False
             if copy:
                 self.h2d_bytes_last += self._test_bytes()
-            self.eval_stats.zero_()
+            K.zero_(self.eval_stats)
             n = ds.test_x.shape[0]
             if self.is_lenet:
                 step = chunk if copy else n

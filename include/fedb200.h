@@ -227,6 +227,8 @@ int fedb_fd_serve(const char* path, const int* fds, int n_fds, int n_clients, in
 int fedb_fd_fetch(const char* path, int* out_fds, int n_fds, int timeout_ms);
 /* cudaMemcpyAsync(cudaMemcpyDefault) on `stream`: pinned host <-> device <-> peer; capturable as a memcpy node */
 int fedb_copy_async(void* dst, const void* src, uint64_t bytes, void* stream);
+/* Zero-fill of `bytes` at dst as a memset on the stream (inside a captured graph: a memset node, no kernel). */
+int fedb_zero_async(void* dst, uint64_t bytes, void* stream);
 
 /* ------------------------------------------------------------------ tensor-core GEMM / convolution (csrc/gemm_tc.cu)
  * tcgen05.mma with TMEM accumulators, operands staged by TMA through a 4-stage mbarrier ring, 128x128 output tiles,
