@@ -180,12 +180,27 @@ __device__ __forceinline__ void st_bf16x4(uint16_t* base, long long i4, float a,
   reinterpret_cast<uint2*>(base)[i4] = r;
 }
 
+// What the LAST block of a channel group does with the reduced sums when the second pass is fused into this kernel (few
+// chunks: the small late layers, where a separate finalize launch costs more than its work): forward -> mean, invstd and the
+// running statistics; backward -> dbeta, dgamma.
+struct BnFinal {
+  int fused;                 // 0: the caller launches bn_finalize_kernel / bn_bwd_finalize_kernel
+  float* out_a;              // fwd: mean      bwd: dbeta
+  float* out_b;              // fwd: invstd    bwd: dgamma
+  float* run_mean;
+  float* run_var;
+  float eps, momentum;
+};
+// completion counters of the fused second pass, one per channel group; zero between launches (the last block resets its own).
+// One training stream per device uses them at a time (the engine's); evaluation-mode BatchNorm never does.
+__device__ unsigned int g_bn_group_done[256];
+
 template <int TX, bool kBwd>
 __global__ void __launch_bounds__(256) bn_partial4_kernel(const float* __restrict__ x, const float* __restrict__ dy,
                                                          const float* __restrict__ mean, const float* __restrict__ invstd,
                                                          const float* __restrict__ gamma, const float* __restrict__ beta,
                                                          float* __restrict__ scratch, long long rows, int C, int act,
-                                                         long long rows_per_chunk) {
+                                                         long long rows_per_chunk, BnFinal fin) {
   constexpr int TY = 256 / TX;
   __shared__ float4 s_a[TY][TX], s_b[TY][TX];
   const int tx = threadIdx.x % TX, ty = threadIdx.x / TX;
@@ -234,6 +249,56 @@ __global__ void __launch_bounds__(256) bn_partial4_kernel(const float* __restric
     *reinterpret_cast<float4*>(scratch + ((long long)blockIdx.y * 2 + 0) * C + c) = sa;
     *reinterpret_cast<float4*>(scratch + ((long long)blockIdx.y * 2 + 1) * C + c) = sb;
   }
+  if (!fin.fused) return;
+  // ---- fused second pass: the block that finishes last for this channel group adds the chunks in chunk order
+  __shared__ int s_last;
+  __threadfence();
+  __syncthreads();
+  if (threadIdx.x == 0) s_last = atomicAdd(&g_bn_group_done[blockIdx.x], 1u) == gridDim.y - 1;
+  __syncthreads();
+  if (!s_last) return;
+  __threadfence();
+  constexpr int NCH = TX * 4, PER = 256 / NCH;                 // channels of the group, threads per channel
+  float* ra = reinterpret_cast<float*>(&s_a[0][0]);            // [PER][NCH] partial sums (the arrays are free again)
+  float* rb = reinterpret_cast<float*>(&s_b[0][0]);
+  const int chl = threadIdx.x % NCH, part = threadIdx.x / NCH;
+  const int ch = blockIdx.x * NCH + chl;
+  const int chunks = gridDim.y;
+  float a0 = 0.f, a1 = 0.f, b0 = 0.f, b1 = 0.f;
+  if (ch < C) {
+    int k = part;
+    for (; k + PER < chunks; k += 2 * PER) {
+      const float x0 = __ldcg(scratch + ((long long)k * 2 + 0) * C + ch), y0 = __ldcg(scratch + ((long long)k * 2 + 1) * C + ch);
+      const float x1 = __ldcg(scratch + ((long long)(k + PER) * 2 + 0) * C + ch);
+      const float y1 = __ldcg(scratch + ((long long)(k + PER) * 2 + 1) * C + ch);
+      a0 += x0; b0 += y0; a1 += x1; b1 += y1;
+    }
+    if (k < chunks) { a0 += __ldcg(scratch + ((long long)k * 2 + 0) * C + ch); b0 += __ldcg(scratch + ((long long)k * 2 + 1) * C + ch); }
+  }
+  ra[part * NCH + chl] = a0 + a1;
+  rb[part * NCH + chl] = b0 + b1;
+  __syncthreads();
+  if (part == 0 && ch < C) {
+    float sum = 0.f, sq = 0.f;
+#pragma unroll
+    for (int q = 0; q < PER; ++q) { sum += ra[q * NCH + chl]; sq += rb[q * NCH + chl]; }
+    if (!kBwd) {
+      const float m = sum / (float)rows;
+      float var = sq / (float)rows - m * m;
+      var = var < 0.f ? 0.f : var;
+      fin.out_a[ch] = m;
+      fin.out_b[ch] = rsqrtf(var + fin.eps);
+      if (fin.run_mean != nullptr) {
+        const float unbiased = rows > 1 ? var * (float)rows / (float)(rows - 1) : var;
+        fin.run_mean[ch] = (1.f - fin.momentum) * fin.run_mean[ch] + fin.momentum * m;
+        fin.run_var[ch] = (1.f - fin.momentum) * fin.run_var[ch] + fin.momentum * unbiased;
+      }
+    } else {
+      fin.out_a[ch] = sum;       // dbeta
+      fin.out_b[ch] = sq;        // dgamma
+    }
+  }
+  if (threadIdx.x == 0) g_bn_group_done[blockIdx.x] = 0;
 }
 
 __global__ void __launch_bounds__(256) bn_apply4_kernel(const float* __restrict__ x, float* __restrict__ y,
@@ -777,15 +842,20 @@ extern "C" int fedb_nn_conv_wgrad(const float* x, const float* dy, float* dw, fl
 // how many row chunks for a [rows x C] reduction so that ~4 blocks land on every SM (bounded by the scratch size)
 static int bn_tx(int C) { const int c4 = C / 4; return c4 >= 32 ? 32 : (c4 >= 16 ? 16 : 8); }
 
+constexpr int kBnFuseMaxChunks = 64;      // up to this many chunks the last block of a channel group does the second pass itself
+
+// returns true when the second pass ran inside the kernel (the caller then skips its finalize launch)
 template <bool kBwd>
-static void bn_partial4(const float* x, const float* dy, const float* mean, const float* invstd, const float* gamma,
+static bool bn_partial4(const float* x, const float* dy, const float* mean, const float* invstd, const float* gamma,
                         const float* beta, float* scratch, long long rows, int C, int act, long long rpc, int chunks,
-                        cudaStream_t s) {
+                        BnFinal fin, cudaStream_t s) {
   const int tx = bn_tx(C);
   dim3 grid(fedb_ceil_div(C / 4, tx), chunks);
-  if (tx == 32) bn_partial4_kernel<32, kBwd><<<grid, 256, 0, s>>>(x, dy, mean, invstd, gamma, beta, scratch, rows, C, act, rpc);
-  else if (tx == 16) bn_partial4_kernel<16, kBwd><<<grid, 256, 0, s>>>(x, dy, mean, invstd, gamma, beta, scratch, rows, C, act, rpc);
-  else bn_partial4_kernel<8, kBwd><<<grid, 256, 0, s>>>(x, dy, mean, invstd, gamma, beta, scratch, rows, C, act, rpc);
+  fin.fused = (chunks <= kBnFuseMaxChunks && grid.x <= 256 && fin.out_a != nullptr) ? 1 : 0;
+  if (tx == 32) bn_partial4_kernel<32, kBwd><<<grid, 256, 0, s>>>(x, dy, mean, invstd, gamma, beta, scratch, rows, C, act, rpc, fin);
+  else if (tx == 16) bn_partial4_kernel<16, kBwd><<<grid, 256, 0, s>>>(x, dy, mean, invstd, gamma, beta, scratch, rows, C, act, rpc, fin);
+  else bn_partial4_kernel<8, kBwd><<<grid, 256, 0, s>>>(x, dy, mean, invstd, gamma, beta, scratch, rows, C, act, rpc, fin);
+  return fin.fused != 0;
 }
 
 static int bn_chunks(long long rows, int C, long long scratch_floats, long long* rows_per_chunk) {
@@ -809,9 +879,13 @@ extern "C" int fedb_nn_bn_fwd16(const float* x, float* y, float* mean, float* in
     FEDB_REQUIRE(scratch != nullptr && scratch_floats >= 2LL * C, "fedb_nn_bn_fwd: scratch of at least 2*C floats required");
     long long rpc = 0;
     const int chunks = bn_chunks(rows, C, scratch_floats, &rpc);
-    if (C % 4 == 0) bn_partial4<false>(x, nullptr, nullptr, nullptr, nullptr, nullptr, scratch, rows, C, 0, rpc, chunks, S_);
-    else bn_partial_kernel<<<dim3(fedb_ceil_div(C, 32), chunks), 256, 0, S_>>>(x, scratch, rows, C, rpc);
-    bn_finalize_kernel<<<fedb_ceil_div(C, 32), 256, 0, S_>>>(scratch, chunks, mean, invstd, run_mean, run_var, rows, C, eps, momentum);
+    bool done = false;
+    if (C % 4 == 0) {
+      BnFinal fin = {0, mean, invstd, run_mean, run_var, eps, momentum};
+      done = bn_partial4<false>(x, nullptr, nullptr, nullptr, nullptr, nullptr, scratch, rows, C, 0, rpc, chunks, fin, S_);
+    } else bn_partial_kernel<<<dim3(fedb_ceil_div(C, 32), chunks), 256, 0, S_>>>(x, scratch, rows, C, rpc);
+    if (!done)
+      bn_finalize_kernel<<<fedb_ceil_div(C, 32), 256, 0, S_>>>(scratch, chunks, mean, invstd, run_mean, run_var, rows, C, eps, momentum);
   }
   else bn_eval_prep_kernel<<<fedb_ceil_div(C, 128), 128, 0, S_>>>(run_mean, run_var, mean, invstd, C, eps);
   if (C % 4 == 0) bn_apply4_kernel<<<grid_for(rows * C / 4), 256, 0, S_>>>(x, y, mean, invstd, gamma, beta, rows * C / 4, C, act, y_bf16);
@@ -832,9 +906,12 @@ extern "C" int fedb_nn_bn_bwd16(const float* x, const float* dy, float* dx, cons
   FEDB_REQUIRE(scratch != nullptr && scratch_floats >= 2LL * C, "fedb_nn_bn_bwd: scratch of at least 2*C floats required");
   long long rpc = 0;
   const int chunks = bn_chunks(rows, C, scratch_floats, &rpc);
-  if (C % 4 == 0) bn_partial4<true>(x, dy, mean, invstd, gamma, beta, scratch, rows, C, act, rpc, chunks, S_);
-  else bn_bwd_partial_kernel<<<dim3(fedb_ceil_div(C, 32), chunks), 256, 0, S_>>>(x, dy, mean, invstd, gamma, beta, scratch, rows, C, act, rpc);
-  bn_bwd_finalize_kernel<<<fedb_ceil_div(C, 32), 256, 0, S_>>>(scratch, chunks, dgamma, dbeta, C);
+  bool done = false;
+  if (C % 4 == 0) {
+    BnFinal fin = {0, dbeta, dgamma, nullptr, nullptr, 0.f, 0.f};
+    done = bn_partial4<true>(x, dy, mean, invstd, gamma, beta, scratch, rows, C, act, rpc, chunks, fin, S_);
+  } else bn_bwd_partial_kernel<<<dim3(fedb_ceil_div(C, 32), chunks), 256, 0, S_>>>(x, dy, mean, invstd, gamma, beta, scratch, rows, C, act, rpc);
+  if (!done) bn_bwd_finalize_kernel<<<fedb_ceil_div(C, 32), 256, 0, S_>>>(scratch, chunks, dgamma, dbeta, C);
   if (C % 4 == 0)
     bn_bwd_apply4_kernel<<<grid_for(rows * C / 4), 256, 0, S_>>>(x, dy, dx, mean, invstd, gamma, beta, dgamma, dbeta, rows * C / 4,
                                                                 C, 1.f / (float)rows, act, training, dx_bf16);
