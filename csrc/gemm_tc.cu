@@ -545,6 +545,37 @@ struct PackJob {
 constexpr int kPackChunk = 9216;   // elements per CTA: the flat grid gives every job CTAs in proportion to its size;
                                    // 9216 = 32 filters x 32 channels x 9 taps, the smem tile of the coalesced forms below
 
+// value of element i of a gather job (kinds 0, 1, 3, 4: dst[i] = ...)
+__device__ __forceinline__ float pack_job_value(const PackJob& j, long long i) {
+  const int K = j.K, C = j.C, T = j.T, Rp = j.Rp;
+  if (j.kind == 0) {
+    const int c = (int)(i % Rp), tap = (int)((i / Rp) % T), k = (int)(i / ((long long)T * Rp));
+    return c < C ? j.src[((long long)k * C + c) * T + tap] : 0.f;
+  }
+  if (j.kind == 1) {
+    const int k = (int)(i % Rp), tap = (int)((i / Rp) % T), cg = (int)(i / ((long long)T * Rp));
+    const int Kg = K / j.groups, grp = cg / C, c = cg - grp * C;
+    return k < Kg ? j.src[(((long long)grp * Kg + k) * C + c) * T + (T - 1 - tap)] : 0.f;
+  }
+  if (j.kind == 3) {
+    const int Cw = C * j.groups;
+    const long long KC = (long long)Rp * Cw;
+    const int unit = (int)(i / KC);
+    const int cls = unit < 1 ? 0 : (unit < 3 ? 1 : (unit < 5 ? 2 : 3));
+    const int base = cls == 0 ? 0 : (cls == 1 ? 1 : (cls == 2 ? 3 : 5));
+    const int a = cls >> 1, b = cls & 1;
+    const int Tc = (a + 1) * (b + 1), fc = b + 1;
+    const long long jj = i - base * KC;
+    const int k = (int)(jj % Rp), t = (int)((jj / Rp) % Tc), c = (int)(jj / ((long long)Rp * Tc));
+    const int rr = t / fc, ss = t % fc;
+    const int r = a == 0 ? 1 : (rr == 0 ? 2 : 0), sx = b == 0 ? 1 : (ss == 0 ? 2 : 0);
+    const int grp = c / C, cl = c - grp * C;
+    return k < K ? j.src[((((long long)grp * K + k) * C + cl) * 3 + r) * 3 + sx] : 0.f;
+  }
+  const int k = (int)(i % K), c = (int)(i / K);
+  return j.src[(long long)k * C + c];
+}
+
 __device__ __forceinline__ void pack_job_elem(const PackJob& j, long long i) {
   const int K = j.K, C = j.C, T = j.T, Rp = j.Rp;
   if (j.kind == 0) {
@@ -585,75 +616,74 @@ __device__ __forceinline__ void pack_job_elem(const PackJob& j, long long i) {
 // per filter) and the packed side (32 contiguous channels / filters per tap) are read and written in whole 128-byte lines.
 // The element-wise forms gather with a stride of 9 floats and were most of the step's packing time.
 __device__ __forceinline__ void pack_tile_3x3(const PackJob& j, int tile, float* __restrict__ sm /* [32][289] */) {
+  // Every warp owns four of the tile's 32 rows and walks them with compile-time trip counts: no per-element index division
+  // (the first version spent its time on e / 288 and % 9), 36 independent loads per thread and phase.
   const int K = j.K, C = j.C, cb = C / 32;
   const int k0 = (tile / cb) * 32, c0 = (tile % cb) * 32;
-  const int tid = threadIdx.x;
-  constexpr int U = 12;                                           // loads in flight per thread (36 elements per thread and phase)
-  float v[U];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  float v[36];
   if (j.kind == 7) {
     // src = dWk [k][tap][c] (cleared), dst = dW OIHW (+=)
     float* __restrict__ srcw = const_cast<float*>(j.src);
-    for (int b = 0; b < 36; b += U) {
 #pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int e = tid + (b + u) * 256;
-        const int c = e & 31, tap = (e >> 5) % 9, k = e / 288;
-        v[u] = srcw[((long long)(k0 + k) * 9 + tap) * C + c0 + c];
-      }
+    for (int q = 0; q < 4; ++q) {
+      float* row = srcw + ((long long)(k0 + warp * 4 + q) * 9) * C + c0 + lane;
 #pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int e = tid + (b + u) * 256;
-        const int c = e & 31, tap = (e >> 5) % 9, k = e / 288;
-        sm[k * 289 + c * 9 + tap] = v[u];
-        srcw[((long long)(k0 + k) * 9 + tap) * C + c0 + c] = 0.f;
+      for (int tap = 0; tap < 9; ++tap) v[q * 9 + tap] = row[(long long)tap * C];
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      float* row = srcw + ((long long)(k0 + warp * 4 + q) * 9) * C + c0 + lane;
+#pragma unroll
+      for (int tap = 0; tap < 9; ++tap) {
+        sm[(warp * 4 + q) * 289 + lane * 9 + tap] = v[q * 9 + tap];
+        row[(long long)tap * C] = 0.f;
       }
     }
     __syncthreads();
     float* __restrict__ dst = j.dst;
-    for (int b = 0; b < 36; b += U) {
 #pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int e = tid + (b + u) * 256;
-        const int k = e / 288, r = e - k * 288;
-        v[u] = dst[((long long)(k0 + k) * C + c0) * 9 + r];
-      }
+    for (int q = 0; q < 4; ++q) {
+      const float* row = dst + ((long long)(k0 + warp * 4 + q) * C + c0) * 9 + lane;
 #pragma unroll
-      for (int u = 0; u < U; ++u) {
-        const int e = tid + (b + u) * 256;
-        const int k = e / 288, r = e - k * 288;
-        dst[((long long)(k0 + k) * C + c0) * 9 + r] = v[u] + sm[k * 289 + r];
-      }
+      for (int i = 0; i < 9; ++i) v[q * 9 + i] = row[32 * i];
+    }
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      float* row = dst + ((long long)(k0 + warp * 4 + q) * C + c0) * 9 + lane;
+#pragma unroll
+      for (int i = 0; i < 9; ++i) row[32 * i] = v[q * 9 + i] + sm[(warp * 4 + q) * 289 + lane + 32 * i];
     }
     return;
   }
   const float* __restrict__ src = j.src;
-  for (int b = 0; b < 36; b += U) {                               // OIHW tile, 288 contiguous floats per filter
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int e = tid + (b + u) * 256;
-      const int k = e / 288, r = e - k * 288;
-      v[u] = src[((long long)(k0 + k) * C + c0) * 9 + r];
-    }
+  for (int q = 0; q < 4; ++q) {                                   // OIHW tile, 288 contiguous floats per filter
+    const float* row = src + ((long long)(k0 + warp * 4 + q) * C + c0) * 9 + lane;
 #pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int e = tid + (b + u) * 256;
-      const int k = e / 288, r = e - k * 288;
-      sm[k * 289 + r] = v[u];
-    }
+    for (int i = 0; i < 9; ++i) v[q * 9 + i] = row[32 * i];
   }
+#pragma unroll
+  for (int q = 0; q < 4; ++q)
+#pragma unroll
+    for (int i = 0; i < 9; ++i) sm[(warp * 4 + q) * 289 + lane + 32 * i] = v[q * 9 + i];
   __syncthreads();
   float* __restrict__ dst = j.dst;
-  if (j.kind == 5) {                                              // dst [k][tap][c]   (Rp == C)
-#pragma unroll 4
-    for (int e = tid; e < 32 * 9 * 32; e += 256) {
-      const int c = e & 31, tap = (e >> 5) % 9, k = e / 288;
-      dst[((long long)(k0 + k) * 9 + tap) * C + c0 + c] = sm[k * 289 + c * 9 + tap];
+  if (j.kind == 5) {                                              // dst [k][tap][c]   (Rp == C): lane = channel
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int k = warp * 4 + q;
+      float* row = dst + ((long long)(k0 + k) * 9) * C + c0 + lane;
+#pragma unroll
+      for (int tap = 0; tap < 9; ++tap) row[(long long)tap * C] = sm[k * 289 + lane * 9 + tap];
     }
-  } else {                                                        // kind 6: dst [c][flipped tap][k]   (Rp == K)
-#pragma unroll 4
-    for (int e = tid; e < 32 * 9 * 32; e += 256) {
-      const int k = e & 31, tap = (e >> 5) % 9, c = e / 288;
-      dst[((long long)(c0 + c) * 9 + tap) * K + k0 + k] = sm[k * 289 + c * 9 + (8 - tap)];
+  } else {                                                        // kind 6: dst [c][flipped tap][k]   (Rp == K): lane = filter
+#pragma unroll
+    for (int q = 0; q < 4; ++q) {
+      const int c = warp * 4 + q;
+      float* row = dst + ((long long)(c0 + c) * 9) * K + k0 + lane;
+#pragma unroll
+      for (int tap = 0; tap < 9; ++tap) row[(long long)tap * K] = sm[lane * 289 + c * 9 + (8 - tap)];
     }
   }
 }
@@ -676,7 +706,24 @@ __global__ void __launch_bounds__(256) pack_multi_kernel(const PackJob* __restri
   }
   const long long begin = (long long)(blockIdx.x - j.chunk0) * kPackChunk;
   const long long end = begin + kPackChunk < j.total ? begin + kPackChunk : j.total;
-  for (long long i = begin + threadIdx.x; i < end; i += 256) pack_job_elem(j, i);
+  if (j.kind == 2) {
+    for (long long i = begin + threadIdx.x; i < end; i += 256) pack_job_elem(j, i);
+    return;
+  }
+  // pure gathers (dst[i] = f(src)): four independent elements per thread in flight
+  for (long long i0 = begin + threadIdx.x; i0 < end; i0 += 4 * 256) {
+    float v[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long i = i0 + u * 256;
+      v[u] = i < end ? pack_job_value(j, i) : 0.f;
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const long long i = i0 + u * 256;
+      if (i < end) j.dst[i] = v[u];
+    }
+  }
 }
 
 template <int BN, int KIND>

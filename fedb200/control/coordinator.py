@@ -196,7 +196,8 @@ class Coordinator:
                         self.members.readmit(w, ch)
                         if self.round > 0 and survivors:
                             # the lowest live rank holds the global model (fedb200/parallel/group.py: _assign_roles)
-                            holder = min(list(self.cfg.workers).index(o) for o in survivors)
+                            from ..parallel.arena import assign_roles
+                            holder, _ = assign_roles([list(self.cfg.workers).index(o) for o in survivors])
                             self._send_model_to(w, desc.encode("pull", src=holder))
                         self._need_reset = True
                         continue

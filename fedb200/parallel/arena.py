@@ -191,3 +191,18 @@ def split_ranges(n: int, parts: int, granule: int = TOTAL_ALIGN) -> List[Tuple[i
     """Contiguous, granule-aligned shards of [0, n) - the two-shot K-AGG ownership map."""
     per = _round_up(math.ceil(n / parts), granule)
     return [(min(i * per, n), min((i + 1) * per, n)) for i in range(parts)]
+
+
+def assign_roles(live, pref_primary: int = 0, pref_backup: int = 1):
+    """(holder of the server's global model, holder of its replica) for a live set on the GPU plane.  The preferred ranks
+    while they are live, else the lowest live ranks; with a single live rank both roles fall to it.  Pure function of
+    its arguments: every rank (and the coordinator, which names the holder in its ``pull`` descriptor) computes the same
+    answer from the same live list.  The reference has no such notion - its server process owns the model - but it does
+    re-admit ANY worker (src/server.py:78-101), so no worker rank may be special here."""
+    lv = sorted(live)
+    if not lv:
+        raise ValueError("empty live set")
+    primary = pref_primary if pref_primary in lv else lv[0]
+    rest = [r for r in lv if r != primary]
+    backup = (pref_backup if pref_backup in rest else rest[0]) if rest else primary
+    return primary, backup

@@ -24,7 +24,7 @@ import torch
 from ..ops import _lib
 from ..ops import cuda as K
 from ..utils.metrics import device_phase
-from .arena import Arena, split_ranges
+from .arena import Arena, assign_roles, split_ranges
 from .mem import PeerGroup, PeerLayout
 
 
@@ -97,12 +97,8 @@ class FedGroup:
         preferred ranks while they are live, else the lowest live ranks.  Every rank derives the same answer from the
         same live list, and the holder refreshes both copies from its own client arena right after each K-AGG, so a
         newly appointed holder is up to date after the first committed round of its tenure."""
-        lv = self.live
-        if not lv:
-            return
-        self.primary_rank = self._pref_primary if self._pref_primary in lv else lv[0]
-        rest = [r for r in lv if r != self.primary_rank]
-        self.backup_rank = (self._pref_backup if self._pref_backup in rest else rest[0]) if rest else self.primary_rank
+        if self.live:
+            self.primary_rank, self.backup_rank = assign_roles(self.live, self._pref_primary, self._pref_backup)
 
     # ------------------------------------------------------------------ one aggregation
     def aggregate(self, weights: Optional[Sequence[float]] = None) -> None:

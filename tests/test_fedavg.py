@@ -99,3 +99,39 @@ def test_arena_keeps_module_live():
     m(x).sum().backward()
     assert m.fc3.bias.grad.data_ptr() == a.grad_view("fc3.bias").data_ptr()
     assert float(a.grad.abs().sum()) > 0
+
+
+def test_roles_follow_the_live_set():
+    """No rank is special on the GPU plane: the global model and its replica move to the lowest live ranks."""
+    from fedb200.parallel.arena import assign_roles
+    assert assign_roles(range(8)) == (0, 1)
+    assert assign_roles([1, 2, 3]) == (1, 2)              # rank 0 (the usual host of the global model) is gone
+    assert assign_roles([0, 2, 3]) == (0, 2)              # the usual backup is gone
+    assert assign_roles([2, 3, 7]) == (2, 3)              # both are gone
+    assert assign_roles([5]) == (5, 5)                    # a single survivor holds both
+    assert assign_roles([0, 1, 2], pref_primary=2, pref_backup=0) == (2, 0)
+    assert assign_roles([0, 1], pref_primary=1, pref_backup=1) == (1, 0)
+    import pytest
+    with pytest.raises(ValueError):
+        assign_roles([])
+
+
+def test_fs_min_barrier_is_an_allreduce_min(tmp_path):
+    """The rendezvous of gRPC-driven workers (no torch.distributed group): every rank ends with the minimum flag."""
+    import threading
+    from fedb200.parallel.mem import fs_min_barrier
+    world, out = 3, {}
+
+    def rank_body(r):
+        bar = fs_min_barrier(str(tmp_path), "t", r, world, timeout_s=20)
+        f = torch.tensor([1])
+        bar(f)                                  # stage 1: everybody says 1
+        first = int(f)
+        f = torch.tensor([0 if r == 1 else 1])
+        bar(f)                                  # stage 2: rank 1 says 0
+        out[r] = (first, int(f))
+
+    ts = [threading.Thread(target=rank_body, args=(r,)) for r in range(world)]
+    [t.start() for t in ts]
+    [t.join(30) for t in ts]
+    assert out == {0: (1, 0), 1: (1, 0), 2: (1, 0)}
