@@ -358,6 +358,8 @@ def _pack_grouped(w, mode: int, taps: int, groups: int) -> torch.Tensor:
     K, Cg = w.shape[0], w.shape[1]
     Kg = K // groups
     n = K * taps * _pad32(Cg) if mode == 0 else groups * Cg * taps * (Kg if taps == 1 else _pad32(Kg))
+    if _SCOPE is not None and mode == 1:
+        return _SCOPE.packed(w, 1, K, Cg, taps, Kg if taps == 1 else _pad32(Kg), groups, n)
     out = torch.empty(n, dtype=torch.float32, device=w.device)
     check(_f("fedb_pack_filter_grouped")(w.data_ptr(), out.data_ptr(), K, Cg, groups, mode, taps, current_stream()),
           "fedb_pack_filter_grouped")
@@ -382,7 +384,9 @@ def _grouped_dgrad(dy, w, dx, shp, Cg, Kg) -> bool:
                                            current_stream()), "fedb_conv_tf32_grouped")
         _lib.count_launch()
         return True
-    if R == 3:
+    if R == 3 and _SCOPE is not None:
+        wk = _SCOPE.packed(w, 3, Kg, Cg, 9, _pad32(Kg), groups, 9 * Cc * _pad32(Kg))
+    elif R == 3:
         wk = torch.empty(9 * Cc * _pad32(Kg), dtype=torch.float32, device=w.device)
         check(_f("fedb_pack_dgrad_s2_grouped")(w.data_ptr(), wk.data_ptr(), K, Cg, groups, current_stream()),
               "fedb_pack_dgrad_s2_grouped")
@@ -427,19 +431,23 @@ def _grouped_wgrad_by_group(x, dy, dw, db, shp, Cg, Kg) -> bool:
     return True
 
 
-def _grouped_wgrad(x, dy, dw, db, shp, Cg, Kg) -> bool:
+def _grouped_wgrad(x, dy, dw, db, shp, Cg, Kg, direct: bool = False) -> bool:
     N, H, W, Cc, K, R, S, P, Q, sh, sw, ph, pw, groups = shp
     if Cg % 8 or Kg % 8:                                 # no 16-byte bf16 group offsets inside the whole tensors
         return _grouped_wgrad_by_group(x, dy, dw, db, shp, Cg, Kg) if groups <= MAX_SPLIT_GROUPS else False
     taps, pix = R * R, N * P * Q
     tiles = ((Kg + 127) // 128) * ((Cg + 127) // 128) * taps * groups
     splits = max(1, min(pix // 256, WGRAD_TILES // max(tiles, 1)))
-    dy16, x16 = cast_bf16(dy), cast_bf16(x)
-    dwk = torch.zeros(K * taps * Cg, dtype=torch.float32, device=x.device) if taps > 1 else dw
+    dy16, x16 = bf16_of(dy), bf16_of(x)                  # shadows left by the producers (BatchNorm / residual kernels)
+    dy16 = cast_bf16(dy) if dy16 is None else dy16
+    x16 = cast_bf16(x) if x16 is None else x16
+    kept = _SCOPE is not None and _SCOPE.train and direct and taps > 1
+    dwk = dw if taps == 1 else (_SCOPE.wgrad_buffer(dw, K, Cg, taps) if kept else
+                                torch.zeros(K * taps * Cg, dtype=torch.float32, device=x.device))
     check(_f("fedb_conv_wgrad_bf16_grouped")(dy16.data_ptr(), x16.data_ptr(), dwk.data_ptr(), N, H, W, Cc, K, groups, R, sh, ph,
                                              splits, current_stream()), "fedb_conv_wgrad_bf16_grouped")
     _lib.count_launch()
-    if taps > 1:
+    if taps > 1 and not kept:
         check(_f("fedb_pack_filter")(dwk.data_ptr(), dw.data_ptr(), K, Cg, 2, taps, current_stream()), "fedb_pack_filter")
         _lib.count_launch()
     if db is not None:
@@ -527,7 +535,7 @@ def conv_wgrad(x, dy, dw, db, shp, direct: bool = False) -> bool:
         return False
     gg = _group_geometry(shp, "wgrad")
     if gg is not None:
-        return _grouped_wgrad(x, dy, dw, db, shp, *gg)
+        return _grouped_wgrad(x, dy, dw, db, shp, *gg, direct=direct)
     if shp[13] > 1:
         return False
     if _small_reduction(shp):
