@@ -148,6 +148,13 @@ class StepScope:
         return t
 
 
+def _wgrad_tiles(cin: int) -> int:
+    """Tile target of a split-K weight gradient: one wave.  Inputs narrower than 128 channels run 64-column tiles, two CTAs per
+    SM (csrc/gemm_tc.cu, FEDB_GEMM_CTAS_SMALL), so their wave is twice as many tiles (measured: the 64-channel layers of
+    ResNet-18 need 65 us at 144 tiles and 52 us at 296)."""
+    return WGRAD_TILES * (2 if cin < 128 else 1)
+
+
 def _zero(t: torch.Tensor) -> None:
     from . import cuda as K
     K.zero_(t)
@@ -554,7 +561,7 @@ def conv_wgrad(x, dy, dw, db, shp, direct: bool = False) -> bool:
         N, H, W, Cc, K = shp[:5]
         pix = N * H * W
         tiles = ((K + 127) // 128) * ((Cc + 127) // 128) * 9
-        splits = max(1, min(pix // 256, WGRAD_TILES // max(tiles, 1)))
+        splits = max(1, min(pix // 256, _wgrad_tiles(Cc) // max(tiles, 1)))
         kept = _SCOPE is not None and _SCOPE.train and direct
         dwk = _SCOPE.wgrad_buffer(dw, K, Cc, 9) if kept else torch.zeros(K * 9 * Cc, dtype=torch.float32, device=x.device)
         # keep both alive: two temporaries would share one allocation; channel counts that are not multiples of 8 get
@@ -575,7 +582,7 @@ def conv_wgrad(x, dy, dw, db, shp, direct: bool = False) -> bool:
         fs, stride, pad = st
         taps, pix = fs * fs, N * shp[7] * shp[8]
         tiles = ((K + 127) // 128) * ((Cc + 127) // 128) * taps
-        splits = max(1, min(pix // 256, WGRAD_TILES // max(tiles, 1)))
+        splits = max(1, min(pix // 256, _wgrad_tiles(Cc) // max(tiles, 1)))
         (dy16, kp), (x16, cp) = cast_bf16_rows(dy, pix, K), cast_bf16_rows(x, N * H * W, Cc)
         kept = _SCOPE is not None and _SCOPE.train and direct and taps > 1
         dwk = dw if taps == 1 else (_SCOPE.wgrad_buffer(dw, K, Cc, taps) if kept else
