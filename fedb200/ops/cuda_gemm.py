@@ -14,7 +14,7 @@ import ctypes as C
 import torch
 
 from . import _lib
-from ._lib import check, current_stream, lib
+from ._lib import check, current_stream
 
 import os
 

@@ -21,7 +21,6 @@ from typing import Dict, List, Optional, Tuple
 
 import torch
 
-from ..utils import data as D
 from . import _lib
 from . import cuda as K
 

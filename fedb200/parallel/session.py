@@ -128,7 +128,6 @@ class GpuFederation:
         # synchronisation per record, so it is off in timed runs.
         self.timer = DeviceTimer() if profile else None
         self.group.timer = self.timer
-        self._eval_round = 0              # round whose global model the newest finished/enqueued evaluation scores
         if self.eval_mode == "overlap":
             self.engine.enable_snapshot_eval()
         # evaluation-set all-gather over NVLink: on by default for rank-symmetric multi-GPU sessions (torchrun); workers
