@@ -26,14 +26,16 @@ __global__ void __launch_bounds__(256) codec_encode_kernel(const float* __restri
   for (long long b = warp; b < nblocks; b += nwarps) {
     const long long i = b * 32 + lane;
     float d = 0.f;
-    if (i < n) d = (cur[i] - base[i]) + residual[i];
+    // every operation is rounded on its own (no fma contraction): the result is defined by the formula alone, which is
+    // what lets fedb200/parallel/codec.py be a bit-exact oracle
+    if (i < n) d = __fadd_rn(__fsub_rn(cur[i], base[i]), residual[i]);
     const float amax = warp_max(fabsf(d));
-    const float s = amax > 0.f ? amax / kE4M3Max : 1.f;
-    const __nv_fp8_e4m3 f8(d / s);
-    const float back = static_cast<float>(f8) * s;
+    const float s = amax > 0.f ? __fdiv_rn(amax, kE4M3Max) : 1.f;
+    const __nv_fp8_e4m3 f8(__fdiv_rn(d, s));
+    const float back = __fmul_rn(static_cast<float>(f8), s);
     if (i < n) {
       q[i] = f8.__x;
-      residual[i] = d - back;
+      residual[i] = __fsub_rn(d, back);
     }
     if (lane == 0) scale[b] = s;
   }
@@ -46,7 +48,7 @@ __global__ void __launch_bounds__(256) codec_decode_kernel(float* __restrict__ o
   for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < n; i += stride) {
     __nv_fp8_e4m3 f8;
     f8.__x = q[i];
-    out[i] = base[i] + static_cast<float>(f8) * scale[i >> 5];
+    out[i] = __fadd_rn(base[i], __fmul_rn(static_cast<float>(f8), scale[i >> 5]));
   }
 }
 

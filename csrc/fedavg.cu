@@ -71,7 +71,7 @@ __device__ __forceinline__ float4 dequant4(const uint8_t* q, const float* scale,
   __nv_fp8x4_e4m3 v;
   v.__x = packed;
   float4 f = static_cast<float4>(v);
-  return make_float4(f.x * s, f.y * s, f.z * s, f.w * s);
+  return make_float4(__fmul_rn(f.x, s), __fmul_rn(f.y, s), __fmul_rn(f.z, s), __fmul_rn(f.w, s));   // no fma contraction
 }
 __device__ __forceinline__ uint2 pack_bf16x4(float4 v) {
   __nv_bfloat162 lo = __floats2bfloat162_rn(v.x, v.y);

@@ -135,3 +135,36 @@ def test_fs_min_barrier_is_an_allreduce_min(tmp_path):
     [t.start() for t in ts]
     [t.join(30) for t in ts]
     assert out == {0: (1, 0), 1: (1, 0), 2: (1, 0)}
+
+
+def test_codec_oracle_error_feedback_and_bounds():
+    """CPU restatement of K-CODEC: e4m3 keeps 3 mantissa bits (error <= 2^-4 of the block maximum), what a round drops is
+    carried to the next one, and a constant signal converges to the exact value on average."""
+    from fedb200.parallel import codec
+    torch.manual_seed(0)
+    n = 32 * 40 + 7                                   # a ragged tail block
+    base = torch.randn(n)
+    cur = base + 0.01 * torch.randn(n)
+    res = torch.zeros(n)
+    q, s = codec.encode(cur, base, res)
+    assert q.dtype == torch.uint8 and q.numel() == n and s.numel() == 41
+    out = codec.decode(base, q, s)
+    delta = cur - base
+    amax = torch.nn.functional.pad(delta.abs(), (0, 25)).view(-1, 32).amax(1, keepdim=True).expand(-1, 32).reshape(-1)[:n]
+    assert float(((out - cur).abs() / amax).max()) <= 2 ** -4 + 1e-6
+    torch.testing.assert_close((out - base) + res, delta, rtol=0, atol=1e-6)      # nothing is lost, only postponed
+    # the same delta sent for many rounds: the running mean of what arrives converges to it (no accumulating bias)
+    res = torch.zeros(n)
+    got = torch.zeros(n)
+    for _ in range(64):
+        q, s = codec.encode(cur, base, res)
+        got += codec.decode(base, q, s) - base
+    assert float(((got / 64 - delta).abs() / amax).max()) < 2 ** -4 / 16
+    # an all-zero block encodes to zeros with scale 1 and decodes to the base
+    q, s = codec.encode(base, base, torch.zeros(n))
+    assert int(q.sum()) == 0 and torch.equal(s, torch.ones_like(s)) and torch.equal(codec.decode(base, q, s), base)
+    # K-AGG's fused decode: mean of the decoded deltas on top of the base
+    curs = [base + 0.01 * torch.randn(n) for _ in range(3)]
+    enc = [codec.encode(c, base, torch.zeros(n)) for c in curs]
+    want = base + ((codec.decode(base, *enc[0]) - base) + (codec.decode(base, *enc[1]) - base) + (codec.decode(base, *enc[2]) - base)) / 3
+    torch.testing.assert_close(codec.fedavg_decoded(base, [e[0] for e in enc], [e[1] for e in enc]), want, rtol=0, atol=1e-6)

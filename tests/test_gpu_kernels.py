@@ -186,6 +186,43 @@ def test_codec_error_feedback_and_fused_decode(K):
     assert float((two_round_mean - (curs[0] - base) - r_before / 2).abs().mean()) <= float(one_round_err)
 
 
+def test_codec_kernels_match_the_cpu_oracle_bit_for_bit(K):
+    """K-CODEC encode / decode / fused decode in K-AGG against fedb200/parallel/codec.py: same bytes, same scales, same
+    residuals (e4m3 round-to-nearest-even, IEEE division), over two rounds of error feedback and a ragged tail block."""
+    from fedb200.parallel import codec
+    torch.manual_seed(3)
+    n = 32 * 257 + 20
+    base = torch.randn(n)
+    curs = [base + 0.02 * torch.randn(n) * torch.rand(n).pow(4) for _ in range(3)]     # wide dynamic range inside blocks
+    res_cpu = [torch.zeros(n) for _ in curs]
+    res_gpu = [torch.zeros(n, device=DEV) for _ in curs]
+    base_d = base.to(DEV)
+    nb = (n + 31) // 32
+    for rnd in range(2):
+        qs_d, ss_d, qs_c, ss_c = [], [], [], []
+        for cur, rc, rg in zip(curs, res_cpu, res_gpu):
+            cur = cur + 0.001 * rnd
+            q_c, s_c = codec.encode(cur, base, rc)
+            q_d = torch.zeros(n, dtype=torch.uint8, device=DEV)
+            s_d = torch.zeros(nb, device=DEV)
+            K.codec_encode(cur.to(DEV), base_d, rg, q_d, s_d)
+            torch.cuda.synchronize()
+            assert torch.equal(s_d.cpu(), s_c), f"scales, round {rnd}"
+            assert torch.equal(q_d.cpu(), q_c), f"fp8 bytes, round {rnd}"
+            assert torch.equal(rg.cpu(), rc), f"residual, round {rnd}"
+            out_d = torch.empty(n, device=DEV)
+            K.codec_decode(out_d, base_d, q_d, s_d)
+            assert torch.equal(out_d.cpu(), codec.decode(base, q_c, s_c))
+            qs_d.append(q_d), ss_d.append(s_d), qs_c.append(q_c), ss_c.append(s_c)
+        n4 = n // 4 * 4                                  # K-AGG ranges are multiples of four elements
+        ctrl = K.new_ctrl(DEV)
+        agg = torch.zeros(n, device=DEV)
+        K.fedavg_raw([], [agg.data_ptr()], 0, n4, ctrl_local=ctrl.data_ptr(), src_q=[q.data_ptr() for q in qs_d],
+                     src_scale=[x.data_ptr() for x in ss_d], base=base_d.data_ptr())
+        torch.cuda.synchronize()
+        assert torch.equal(agg[:n4].cpu(), codec.fedavg_decoded(base, qs_c, ss_c)[:n4]), f"fused decode, round {rnd}"
+
+
 def test_sgd_matches_torch(K):
     torch.manual_seed(0)
     n = 8192
