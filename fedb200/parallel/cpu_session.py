@@ -26,7 +26,12 @@ from .fedavg import fedavg_flat_cpu
 class CpuFederation:
     def __init__(self, model: str = "LeNet", rank: Optional[int] = None, world: Optional[int] = None,
                  dataset: Optional[D.ImageDataset] = None, seed: Optional[int] = None, lr: float = 0.1, batch_size: int = 128,
-                 augment: bool = False, evaluate: bool = True, weighted: bool = False, max_batches: Optional[int] = None):
+                 augment: bool = False, evaluate: bool = True, weighted: bool = False, max_batches: Optional[int] = None,
+                 codec: str = "none"):
+        """``codec="fp8"``: the lossy, opt-in meaning of ``-c`` (block-scaled e4m3 deltas against the last global model, error
+        feedback; ``fedb200/parallel/codec.py`` - the very arithmetic of K-CODEC on the GPU plane): one byte + 1/32 scale per
+        weight crosses the wire instead of four bytes.  The first aggregation is lossless and establishes the common base
+        (the workers start from different random models, N6); int64 counters always travel exactly."""
         if world is None:
             world = dist.get_world_size() if dist.is_initialized() else 1
         if rank is None:
@@ -40,6 +45,12 @@ class CpuFederation:
         self.trainer = LocalTrainer(cfg, ds)
         self.live: List[int] = list(range(world))
         self.rounds = 0
+        if codec not in ("none", "fp8"):
+            raise ValueError(f"codec {codec!r} (none | fp8)")
+        self.codec = codec
+        self._base = None                 # last global model: what the deltas are relative to (identical on every rank)
+        self._residual = None             # what quantisation dropped so far on THIS rank (error feedback)
+        self.bytes_sent_last = 0
 
     # ------------------------------------------------------------------ membership
     def set_live(self, live: Sequence[int]) -> None:
@@ -59,15 +70,35 @@ class CpuFederation:
         (gloo needs every process) but their buffers are ignored and their arenas stay untouched."""
         a = self.trainer.arena
         man = a.manifest
-        f32s = self._gather(a.f32[:man.n_f32])
+        n = man.n_f32
+        if self.codec == "fp8" and self._base is not None and not self.weighted:
+            from . import codec as C
+            q, s = C.encode(a.f32[:n], self._base, self._residual)
+            qs, ss = self._gather(q), self._gather(s)
+            i64s = self._gather(a.i64[:man.n_i64])
+            self.bytes_sent_last = q.numel() + s.numel() * 4 + man.n_i64 * 8
+            if self.rank in self.live:
+                with torch.no_grad():
+                    a.f32[:n].copy_(C.fedavg_decoded(self._base, [qs[r] for r in self.live], [ss[r] for r in self.live]))
+                    i64 = i64s[self.live[0]].clone()
+                    for r in self.live[1:]:
+                        i64 += i64s[r]
+                    a.i64[:man.n_i64].copy_((i64.to(torch.float32) / float(len(self.live))).trunc().to(torch.int64))
+                self._base = a.f32[:n].detach().clone()
+            return
+        f32s = self._gather(a.f32[:n])
         i64s = self._gather(a.i64[:man.n_i64])
+        self.bytes_sent_last = n * 4 + man.n_i64 * 8
         weights = None
         if self.weighted:
             counts = self._gather(torch.tensor([samples], dtype=torch.int64))
             weights = [int(counts[r][0]) for r in self.live]
         if self.rank in self.live:
             fedavg_flat_cpu([f32s[r] for r in self.live], [i64s[r] for r in self.live], weights,
-                            a.f32[:man.n_f32], a.i64[:man.n_i64])
+                            a.f32[:n], a.i64[:man.n_i64])
+            if self.codec == "fp8":
+                self._base = a.f32[:n].detach().clone()
+                self._residual = torch.zeros(n)
 
     # ------------------------------------------------------------------ one round
     def run_round(self):
